@@ -1,0 +1,113 @@
+/*
+ * plr2_b200.h — C-ABI of the B200-native DenseFusion dense-fusion + pose-loss hot path.
+ *
+ * This is the drop-in boundary. Every entry point takes plain device pointers,
+ * sizes and a cudaStream_t (passed as void*), returns an int status and never throws:
+ *     0  ok      <0  invalid argument (PLR2_E_*)      >0  a cudaError_t value
+ * No entry point allocates: scratch is passed by the caller (see the *_workspace_bytes queries).
+ * All launches are asynchronous on `stream`; nothing here synchronises the host.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo root):
+ *   plr2_knn_f32            <- knn(ref, query, idx)            lib/knn/src/knn.h:12-61, src/vision.cpp:3-5,
+ *                              knn_device                       lib/knn/src/cuda/knn.cu:217-263
+ *   plr2_pose_loss_fwd      <- loss_calculation                 lib/loss.py:12-49 (+ ADD-S branch :39-46)
+ *   plr2_pose_loss_bwd      <- autograd of the above            (torch autograd in the reference)
+ *   plr2_pose_select        <- best-vote select + re-centre     lib/loss.py:52-69
+ *   plr2_refine_loss_fwd/bwd<- loss_calculation (refiner)       lib/loss_refiner.py:12-62
+ *   plr2_gather_emb         <- torch.gather at `choose`         lib/network.py:98-102
+ *   plr2_linear_*           <- Conv1d(k=1)/Linear + ReLU chain  lib/network.py:53-68,107-121,151-168,193-200
+ *   plr2_posenet_* / plr2_refiner_*  <- PoseNet.forward / PoseRefineNet.forward  lib/network.py:95-132,187-206
+ */
+#ifndef PLR2_B200_H
+#define PLR2_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PLR2_ABI_VERSION 1
+
+#define PLR2_E_NULLPTR   (-1)
+#define PLR2_E_SHAPE     (-2)
+#define PLR2_E_UNSUPPORTED (-3)
+#define PLR2_E_WORKSPACE (-4)
+#define PLR2_E_ALIGN     (-5)
+
+/* KNN arithmetic modes.  EXACT reproduces the reference CUDA kernel's arithmetic bit for bit
+ * (sum over d of fma(a-b, a-b, acc), lib/knn/src/cuda/knn.cu:88-91, strict '<' so the lowest
+ * reference index wins ties, :158).  FAST ranks by |r|^2 - 2 q.r on centroid-centred coordinates
+ * (3 FMAs/pair); it returns the same index wherever best and second-best differ by >1e-6. */
+#define PLR2_KNN_EXACT 0
+#define PLR2_KNN_FAST  1
+
+int         plr2_abi_version(void);
+const char *plr2_last_error_string(void);   /* thread-local, never NULL */
+int         plr2_device_sm_count(void);     /* multiProcessorCount of the current device, or <0 */
+
+/* ---- (4) brute-force nearest neighbours ---------------------------------------------------
+ * ref   [batch][dim][n_ref]   f32, contiguous        (lib/knn/src/knn.h:33)
+ * query [batch][dim][n_query] f32, contiguous
+ * idx   [batch][k][n_query]   i64, 1-BASED           (knn.cu:128,147,171)
+ * dist  [batch][k][n_query]   f32 squared distances of the winners, or NULL
+ * dim==3,k==1 runs the tiled FP32x2 kernel; any other (dim,k<=64) runs the generic kernel. */
+size_t plr2_knn_workspace_bytes(int batch, int dim, int n_ref, int n_query, int k);
+int plr2_knn_f32(const float *ref, const float *query, int64_t *idx, float *dist,
+                 int batch, int dim, int n_ref, int n_query, int k, int mode,
+                 void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---- (3) fused quaternion->R, mesh transform, ADD / ADD-S, confidence-weighted loss -------
+ * One call handles `frames` independent frames (the reference only ever has frames==1).
+ *   pred_r [F][N][4] (w,x,y,z, un-normalised)   pred_t [F][N][3]   pred_c [F][N]
+ *   target [F][M][3]   model_points [F][M][3]   points [F][N][3]
+ *   obj    [F] i64 class ids;  sym_lut [num_obj] u8 (1 = symmetric class, lib/loss.py:40)
+ * ADD-S (nearest target point) is used iff sym_lut[obj[f]] && !refine  (lib/loss.py:39-40).
+ * Outputs:
+ *   dis    [F][N]   mean_j || R_n m_j + p_n + t_n - tgt_nj ||      (lib/loss.py:48)
+ *   loss   [F]      mean_n (dis_n c_n - w log c_n)                 (lib/loss.py:49)
+ *   jac_r  [F][N][4], jac_t [F][N][3]   d dis_n / d pred_r[n], d dis_n / d pred_t[n]
+ *                   (NN index held fixed, lib/loss.py:44 `.detach()`); may be NULL (inference)
+ */
+int plr2_pose_loss_fwd(const float *pred_r, const float *pred_t, const float *pred_c,
+                       const float *target, const float *model_points, const float *points,
+                       const int64_t *obj, const uint8_t *sym_lut, int num_obj,
+                       int frames, int n_points, int n_mesh, float w, int refine, int knn_mode,
+                       float *dis, float *loss, float *jac_r, float *jac_t, void *stream);
+
+/* Backward of the above given upstream grads of `loss` [F] and of the selected `dis_sel` [F]
+ * (either may be NULL = zero).  which_max [F] i32 comes from plr2_pose_select.
+ *   g_pred_r [F][N][4], g_pred_t [F][N][3], g_pred_c [F][N] */
+int plr2_pose_loss_bwd(const float *g_loss, const float *g_dis_sel, const int32_t *which_max,
+                       const float *pred_c, const float *dis, const float *jac_r, const float *jac_t,
+                       int frames, int n_points, float w,
+                       float *g_pred_r, float *g_pred_t, float *g_pred_c, void *stream);
+
+/* ---- (5) best-vote select + re-centre (lib/loss.py:52-69) ---------------------------------
+ *   which_max [F] i32 = argmax_n pred_c (lowest n on ties)
+ *   dis_sel   [F]     = dis[f][which_max]
+ *   new_points[F][N][3] = (points - t*) R*      new_target [F][M][3] = (target - t*) R*
+ *   pose_out  [F][12]   = R* row-major (9) then t* (3); may be NULL */
+int plr2_pose_select(const float *pred_r, const float *pred_t, const float *pred_c,
+                     const float *dis, const float *target, const float *points,
+                     int frames, int n_points, int n_mesh,
+                     int32_t *which_max, float *dis_sel, float *new_points, float *new_target,
+                     float *pose_out, void *stream);
+
+/* ---- refiner loss (lib/loss_refiner.py:12-62): one pose per frame -------------------------
+ *   pred_r [F][4], pred_t [F][3]; target/model_points [F][M][3]; points [F][N][3]
+ *   ADD-S iff sym_lut[obj[f]] (always, lib/loss_refiner.py:40)
+ *   dis [F]; new_points [F][N][3]; new_target [F][M][3]; jac_r [F][4], jac_t [F][3] (nullable)
+ *   pose_out [F][12] nullable.  Needs n_mesh <= 8192. */
+int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t,
+                         const float *target, const float *model_points, const float *points,
+                         const int64_t *obj, const uint8_t *sym_lut, int num_obj,
+                         int frames, int n_points, int n_mesh, int knn_mode,
+                         float *dis, float *new_points, float *new_target,
+                         float *jac_r, float *jac_t, float *pose_out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PLR2_B200_H */

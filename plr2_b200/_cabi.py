@@ -1,0 +1,66 @@
+"""ctypes binding of the C-ABI in include/plr2_b200.h.
+
+There is deliberately NO fallback: if libplr2_b200.so is missing or a call fails, we raise.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libplr2_b200.so")
+
+_vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+
+# name -> (restype, argtypes); must list every symbol include/plr2_b200.h declares
+SIGNATURES = {
+    "plr2_abi_version": (_i, []),
+    "plr2_last_error_string": (C.c_char_p, []),
+    "plr2_device_sm_count": (_i, []),
+    "plr2_knn_workspace_bytes": (_sz, [_i] * 5),
+    "plr2_knn_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "plr2_pose_loss_fwd": (_i, [_vp] * 8 + [_i] * 4 + [_f, _i, _i] + [_vp] * 5),
+    "plr2_pose_loss_bwd": (_i, [_vp] * 7 + [_i, _i, _f] + [_vp] * 4),
+    "plr2_pose_select": (_i, [_vp] * 6 + [_i] * 3 + [_vp] * 6),
+    "plr2_refine_loss_fwd": (_i, [_vp] * 7 + [_i] * 5 + [_vp] * 7),
+}
+
+_lib = None
+
+
+class Plr2Error(RuntimeError):
+    pass
+
+
+def lib():
+    """Load (once) and return the ctypes handle. Raises if the CUDA library was not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise Plr2Error(
+                f"{LIB_PATH} not found: build it with `python -m plr2_b200.build` "
+                "(there is no CPU / PyTorch fallback for this path)")
+        h = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(h, name)  # AttributeError if the symbol is missing
+            fn.restype = res
+            fn.argtypes = args
+        _lib = h
+    return _lib
+
+
+def check(status, what):
+    if status != 0:
+        msg = lib().plr2_last_error_string().decode(errors="replace")
+        raise Plr2Error(f"{what} failed with status {status}: {msg}")
+
+
+def ptr(t):
+    """Device/host pointer of a contiguous torch tensor (None -> NULL)."""
+    if t is None:
+        return None
+    assert t.is_contiguous(), "plr2_b200 C-ABI needs contiguous tensors"
+    return t.data_ptr()
+
+
+def stream_ptr(device=None):
+    import torch
+    return torch.cuda.current_stream(device).cuda_stream

@@ -1,0 +1,26 @@
+// C-ABI housekeeping: version, last-error text, device query.
+#include "common.cuh"
+#include <stdarg.h>
+
+namespace plr2 {
+static thread_local char g_err[512] = "";
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+}  // namespace plr2
+
+extern "C" int plr2_abi_version(void) { return PLR2_ABI_VERSION; }
+extern "C" const char *plr2_last_error_string(void) { return plr2::g_err; }
+extern "C" int plr2_device_sm_count(void) {
+  int dev = 0, n = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) {
+    plr2::set_error("plr2_device_sm_count: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  return n;
+}

@@ -1,0 +1,80 @@
+// Shared device/host helpers for the plr2_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/plr2_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "plr2_b200 kernels are written for sm_100a (B200) only"
+#endif
+
+namespace plr2 {
+
+// thread-local last-error text, set by the C-ABI wrappers
+void set_error(const char *fmt, ...);
+
+inline int check_launch(const char *what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+// ---- packed FP32x2 arithmetic (Blackwell FADD2 / FMUL2 / FFMA2) -----------------------------
+// Each op is IEEE round-to-nearest per half, i.e. bit-identical to the scalar add/mul/fma.
+typedef unsigned long long f32x2;
+
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+// 3-input min (FMNMX3): NaN operands are ignored like fminf
+__device__ __forceinline__ float min3(float a, float b, float c) {
+  float r;
+  asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// quaternion (w,x,y,z), already normalised -> rotation matrix, row-major, using exactly the
+// expression order of lib/loss.py:17-25
+__device__ __forceinline__ void quat_to_rot(float w, float x, float y, float z, float R[9]) {
+  R[0] = 1.0f - 2.0f * (y * y + z * z);
+  R[1] = 2.0f * x * y - 2.0f * w * z;
+  R[2] = 2.0f * w * y + 2.0f * x * z;
+  R[3] = 2.0f * x * y + 2.0f * z * w;
+  R[4] = 1.0f - 2.0f * (x * x + z * z);
+  R[5] = -2.0f * w * x + 2.0f * y * z;
+  R[6] = -2.0f * w * y + 2.0f * x * z;
+  R[7] = 2.0f * w * x + 2.0f * y * z;
+  R[8] = 1.0f - 2.0f * (x * x + y * y);
+}
+
+}  // namespace plr2

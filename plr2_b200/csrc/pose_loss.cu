@@ -1,0 +1,592 @@
+// Kernels (3) and (5): quaternion -> rotation, mesh-point transform, ADD / ADD-S distance,
+// confidence-weighted loss and its local Jacobians, best-vote selection and re-centring — fused so
+// that neither the (N, M, 3) prediction tensor nor the KNN index tensor is ever materialised.
+// Reference: lib/loss.py:12-69, lib/loss_refiner.py:12-62.
+#include "knn_core.cuh"
+
+namespace plr2 {
+
+// ---------------------------------------------------------------------------------------------
+// Per-hypothesis pose: normalised quaternion, rotation (row-major) and translation.
+struct Pose {
+  float q[4];   // normalised (w,x,y,z)
+  float inv_n;  // 1/||pred_r||
+  float R[9];
+  float s[3];   // translation added after rotation
+};
+
+__device__ __forceinline__ void make_pose(const float *__restrict__ r4, Pose &P) {
+  const float a = r4[0], b = r4[1], c = r4[2], d = r4[3];
+  const float n = sqrtf(a * a + b * b + c * c + d * d);  // torch.norm(pred_r, dim=2), lib/loss.py:15
+  P.inv_n = 1.0f / n;
+  P.q[0] = a / n; P.q[1] = b / n; P.q[2] = c / n; P.q[3] = d / n;
+  quat_to_rot(P.q[0], P.q[1], P.q[2], P.q[3], P.R);
+}
+
+// Accumulated per-hypothesis sums over mesh points: distance, d/ds and d/dR.
+struct Acc {
+  float dis;
+  float gs[3];
+  float G[9];
+};
+__device__ __forceinline__ void acc_zero(Acc &A) {
+  A.dis = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) A.gs[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) A.G[i] = 0.f;
+}
+
+// One (prediction, target) pair: adds ||p - t|| and, if JAC, the unit residual's outer products.
+template <bool JAC>
+__device__ __forceinline__ void acc_pair(Acc &A, float px, float py, float pz, float tx, float ty,
+                                         float tz, float mx, float my, float mz) {
+  const float dx = px - tx, dy = py - ty, dz = pz - tz;
+  const float d2 = dx * dx + dy * dy + dz * dz;
+  const float d = sqrtf(d2);
+  A.dis += d;
+  if (JAC) {
+    const float inv = d > 0.f ? 1.0f / d : 0.f;  // torch: d||x||/dx = 0 at x = 0
+    const float ux = dx * inv, uy = dy * inv, uz = dz * inv;
+    A.gs[0] += ux; A.gs[1] += uy; A.gs[2] += uz;
+    A.G[0] = fmaf(ux, mx, A.G[0]); A.G[1] = fmaf(ux, my, A.G[1]); A.G[2] = fmaf(ux, mz, A.G[2]);
+    A.G[3] = fmaf(uy, mx, A.G[3]); A.G[4] = fmaf(uy, my, A.G[4]); A.G[5] = fmaf(uy, mz, A.G[5]);
+    A.G[6] = fmaf(uz, mx, A.G[6]); A.G[7] = fmaf(uz, my, A.G[7]); A.G[8] = fmaf(uz, mz, A.G[8]);
+  }
+}
+
+// Chain d(dis)/dR (G, already divided by M) through R(q_hat) and q_hat = r/||r|| to d/d pred_r.
+// The partials are those of the exact expressions in quat_to_rot (lib/loss.py:17-25).
+__device__ __forceinline__ void jac_quat(const Pose &P, const float G[9], float out[4]) {
+  const float w = P.q[0], x = P.q[1], y = P.q[2], z = P.q[3];
+  float gw = 2.f * (-z * G[1] + y * G[2] + z * G[3] - x * G[5] - y * G[6] + x * G[7]);
+  float gx = 2.f * (y * G[1] + z * G[2] + y * G[3] - 2.f * x * G[4] - w * G[5] + z * G[6] + w * G[7] - 2.f * x * G[8]);
+  float gy = 2.f * (-2.f * y * G[0] + x * G[1] + w * G[2] + x * G[3] + z * G[5] - w * G[6] + z * G[7] - 2.f * y * G[8]);
+  float gz = 2.f * (-2.f * z * G[0] - w * G[1] + x * G[2] + w * G[3] - 2.f * z * G[4] + y * G[5] + x * G[6] + y * G[7]);
+  const float dot = w * gw + x * gx + y * gy + z * gz;
+  out[0] = (gw - w * dot) * P.inv_n;
+  out[1] = (gx - x * dot) * P.inv_n;
+  out[2] = (gy - y * dot) * P.inv_n;
+  out[3] = (gz - z * dot) * P.inv_n;
+}
+
+__device__ __forceinline__ bool frame_is_sym(const int64_t *obj, const uint8_t *sym_lut, int num_obj, int f) {
+  if (sym_lut == nullptr || obj == nullptr) return false;
+  const long long o = obj[f];
+  return o >= 0 && o < num_obj && sym_lut[o] != 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// ADD (index-matched) distance: block = 32 hypotheses x 8 mesh slices.  Mesh and target points are
+// staged as float4 so the 8 slices of a warp read one conflict-free 128 B row, broadcast over the
+// 4 hypotheses sharing a slice.
+constexpr int ADD_SLICES = 8;
+constexpr int ADD_NPB = 32;     // hypotheses per block
+constexpr int ADD_JT = 512;     // mesh points per smem tile
+
+template <bool JAC>
+__global__ void __launch_bounds__(ADD_SLICES * ADD_NPB)
+add_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
+                const float *__restrict__ target, const float *__restrict__ model,
+                const float *__restrict__ points, const int64_t *__restrict__ obj,
+                const uint8_t *__restrict__ sym_lut, int num_obj, int N, int M, int skip_sym,
+                float *__restrict__ dis, float *__restrict__ jac_r, float *__restrict__ jac_t) {
+  const int f = blockIdx.y;
+  if (skip_sym && frame_is_sym(obj, sym_lut, num_obj, f)) return;  // handled by adds_loss_kernel
+  __shared__ float4 sm[ADD_JT];
+  __shared__ float4 st[ADD_JT];
+  const int tid = threadIdx.x;
+  const int slice = tid & (ADD_SLICES - 1);
+  const int n = blockIdx.x * ADD_NPB + (tid >> 3);
+  const bool live = n < N;
+  const size_t fn = (size_t)f * N + (live ? n : 0);
+
+  Pose P;
+  make_pose(pred_r + fn * 4, P);
+  if (points != nullptr) {
+    P.s[0] = points[fn * 3 + 0] + pred_t[fn * 3 + 0];   // points + pred_t, lib/loss.py:37
+    P.s[1] = points[fn * 3 + 1] + pred_t[fn * 3 + 1];
+    P.s[2] = points[fn * 3 + 2] + pred_t[fn * 3 + 2];
+  } else {
+    P.s[0] = pred_t[fn * 3 + 0]; P.s[1] = pred_t[fn * 3 + 1]; P.s[2] = pred_t[fn * 3 + 2];
+  }
+  Acc A;
+  acc_zero(A);
+  const float *mb = model + (size_t)f * M * 3;
+  const float *tb = target + (size_t)f * M * 3;
+  for (int j0 = 0; j0 < M; j0 += ADD_JT) {
+    const int jt = min(ADD_JT, M - j0);
+    __syncthreads();
+    for (int j = tid; j < jt; j += blockDim.x) {
+      const float *m = mb + (size_t)(j0 + j) * 3;
+      const float *t = tb + (size_t)(j0 + j) * 3;
+      sm[j] = make_float4(__ldg(m), __ldg(m + 1), __ldg(m + 2), 0.f);
+      st[j] = make_float4(__ldg(t), __ldg(t + 1), __ldg(t + 2), 0.f);
+    }
+    __syncthreads();
+    for (int j = slice; j < jt; j += ADD_SLICES) {
+      const float4 m = sm[j], t = st[j];
+      const float px = fmaf(P.R[0], m.x, fmaf(P.R[1], m.y, fmaf(P.R[2], m.z, P.s[0])));
+      const float py = fmaf(P.R[3], m.x, fmaf(P.R[4], m.y, fmaf(P.R[5], m.z, P.s[1])));
+      const float pz = fmaf(P.R[6], m.x, fmaf(P.R[7], m.y, fmaf(P.R[8], m.z, P.s[2])));
+      acc_pair<JAC>(A, px, py, pz, t.x, t.y, t.z, m.x, m.y, m.z);
+    }
+  }
+  // reduce over the 8 slices (lanes differing in bits 0..2)
+#pragma unroll
+  for (int o = 1; o < ADD_SLICES; o <<= 1) {
+    A.dis += __shfl_xor_sync(0xffffffffu, A.dis, o);
+    if (JAC) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) A.gs[i] += __shfl_xor_sync(0xffffffffu, A.gs[i], o);
+#pragma unroll
+      for (int i = 0; i < 9; ++i) A.G[i] += __shfl_xor_sync(0xffffffffu, A.G[i], o);
+    }
+  }
+  if (live && slice == 0) {
+    const float invM = 1.0f / (float)M;
+    dis[fn] = A.dis * invM;
+    if (JAC) {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) A.G[i] *= invM;
+      float jq[4];
+      jac_quat(P, A.G, jq);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) jac_r[fn * 4 + i] = jq[i];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) jac_t[fn * 3 + i] = A.gs[i] * invM;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Block-wide sum of an Acc; result valid in thread 0.  `red` needs (blockDim/32)*13 floats.
+template <bool JAC>
+__device__ __forceinline__ void acc_block_reduce(Acc &A, float *red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  A.dis = warp_sum(A.dis);
+  if (JAC) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) A.gs[i] = warp_sum(A.gs[i]);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) A.G[i] = warp_sum(A.G[i]);
+  }
+  if (lane == 0) {
+    red[warp * 13] = A.dis;
+    if (JAC) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) red[warp * 13 + 1 + i] = A.gs[i];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) red[warp * 13 + 4 + i] = A.G[i];
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < nwarp; ++w) {
+      A.dis += red[w * 13];
+      if (JAC) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) A.gs[i] += red[w * 13 + 1 + i];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) A.G[i] += red[w * 13 + 4 + i];
+      }
+    }
+  }
+}
+
+// Stage the M target points of one frame as the SoA reference tile of the 1-NN scan.
+template <bool FAST>
+__device__ __forceinline__ void stage_targets(const float *__restrict__ tb, int M, int Mp, float *sx,
+                                              float *sy, float *sz, float *sw, float cx, float cy,
+                                              float cz) {
+  for (int j = threadIdx.x; j < Mp; j += blockDim.x) {
+    float x, y, z;
+    if (j < M) {
+      x = __ldg(tb + 3 * j); y = __ldg(tb + 3 * j + 1); z = __ldg(tb + 3 * j + 2);
+      if (FAST) {
+        x -= cx; y -= cy; z -= cz;
+        sw[j] = fmaf(z, z, fmaf(y, y, x * x));
+      }
+    } else {
+      x = y = z = FAST ? 0.f : CUDART_INF_F;
+      if (FAST) sw[j] = CUDART_INF_F;
+    }
+    sx[j] = x; sy[j] = y; sz[j] = z;
+  }
+}
+
+// Per-thread ADD-S accumulation over the mesh points j = j_first + i*blockDim (i < QPT) ... of one
+// pose: transform, 1-NN over the staged targets, residual to the nearest target.
+constexpr int ADDS_QPT = 4;
+template <bool FAST, bool JAC>
+__device__ __forceinline__ void adds_accumulate(const Pose &P, const float *__restrict__ mb,
+                                                const float *__restrict__ tb, int M, int Mp,
+                                                const float *sx, const float *sy, const float *sz,
+                                                const float *sw, float cx, float cy, float cz, Acc &A) {
+  const int lane = threadIdx.x & 31;
+  const int stride = blockDim.x;
+  for (int j0 = 0; j0 < M; j0 += stride * ADDS_QPT) {
+    float mx[ADDS_QPT], my[ADDS_QPT], mz[ADDS_QPT], px[ADDS_QPT], py[ADDS_QPT], pz[ADDS_QPT];
+    float nqx[ADDS_QPT], nqy[ADDS_QPT], nqz[ADDS_QPT], best[ADDS_QPT];
+    int bchunk[ADDS_QPT];
+#pragma unroll
+    for (int i = 0; i < ADDS_QPT; ++i) {
+      const int j = j0 + i * stride + threadIdx.x;
+      mx[i] = my[i] = mz[i] = 0.f;
+      if (j < M) { mx[i] = __ldg(mb + 3 * j); my[i] = __ldg(mb + 3 * j + 1); mz[i] = __ldg(mb + 3 * j + 2); }
+      px[i] = fmaf(P.R[0], mx[i], fmaf(P.R[1], my[i], fmaf(P.R[2], mz[i], P.s[0])));
+      py[i] = fmaf(P.R[3], mx[i], fmaf(P.R[4], my[i], fmaf(P.R[5], mz[i], P.s[1])));
+      pz[i] = fmaf(P.R[6], mx[i], fmaf(P.R[7], my[i], fmaf(P.R[8], mz[i], P.s[2])));
+      if (FAST) {
+        nqx[i] = -2.f * (px[i] - cx); nqy[i] = -2.f * (py[i] - cy); nqz[i] = -2.f * (pz[i] - cz);
+      } else {
+        nqx[i] = -px[i]; nqy[i] = -py[i]; nqz[i] = -pz[i];
+      }
+      best[i] = CUDART_INF_F;
+      bchunk[i] = 0;
+    }
+    nn_scan<FAST, ADDS_QPT>(sx, sy, sz, sw, Mp, 0, nqx, nqy, nqz, best, bchunk);
+#pragma unroll
+    for (int i = 0; i < ADDS_QPT; ++i) {
+      const int j = j0 + i * stride + threadIdx.x;
+      if (j < M) {
+        const int win = nn_resolve_smem<FAST>(sx, sy, sz, sw, M, bchunk[i], best[i], nqx[i], nqy[i], nqz[i], lane);
+        const float tx = __ldg(tb + 3 * win), ty = __ldg(tb + 3 * win + 1), tz = __ldg(tb + 3 * win + 2);
+        acc_pair<JAC>(A, px[i], py[i], pz[i], tx, ty, tz, mx[i], my[i], mz[i]);
+      }
+    }
+  }
+}
+
+// ADD-S for symmetric frames of Loss (lib/loss.py:39-46): one CTA per (hypothesis n, frame).
+constexpr int ADDS_THREADS = 128;
+template <bool FAST, bool JAC>
+__global__ void __launch_bounds__(ADDS_THREADS)
+adds_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
+                 const float *__restrict__ target, const float *__restrict__ model,
+                 const float *__restrict__ points, const int64_t *__restrict__ obj,
+                 const uint8_t *__restrict__ sym_lut, int num_obj, int N, int M,
+                 float *__restrict__ dis, float *__restrict__ jac_r, float *__restrict__ jac_t) {
+  const int f = blockIdx.y;
+  if (!frame_is_sym(obj, sym_lut, num_obj, f)) return;
+  extern __shared__ __align__(16) float dyn[];
+  __shared__ float red[(ADDS_THREADS / 32) * 13];
+  const int Mp = knn_pad(M);
+  float *sx = dyn, *sy = dyn + Mp, *sz = dyn + 2 * Mp, *sw = dyn + 3 * Mp;
+  const float *tb = target + (size_t)f * M * 3;
+  const float *mb = model + (size_t)f * M * 3;
+  float cx = 0.f, cy = 0.f, cz = 0.f;
+  if (FAST) { cx = __ldg(tb); cy = __ldg(tb + 1); cz = __ldg(tb + 2); }
+  stage_targets<FAST>(tb, M, Mp, sx, sy, sz, sw, cx, cy, cz);
+  const size_t fn = (size_t)f * N + blockIdx.x;
+  Pose P;
+  make_pose(pred_r + fn * 4, P);
+  P.s[0] = points[fn * 3 + 0] + pred_t[fn * 3 + 0];
+  P.s[1] = points[fn * 3 + 1] + pred_t[fn * 3 + 1];
+  P.s[2] = points[fn * 3 + 2] + pred_t[fn * 3 + 2];
+  __syncthreads();
+  Acc A;
+  acc_zero(A);
+  adds_accumulate<FAST, JAC>(P, mb, tb, M, Mp, sx, sy, sz, sw, cx, cy, cz, A);
+  acc_block_reduce<JAC>(A, red);
+  if (threadIdx.x == 0) {
+    const float invM = 1.0f / (float)M;
+    dis[fn] = A.dis * invM;
+    if (JAC) {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) A.G[i] *= invM;
+      float jq[4];
+      jac_quat(P, A.G, jq);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) jac_r[fn * 4 + i] = jq[i];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) jac_t[fn * 3 + i] = A.gs[i] * invM;
+    }
+  }
+}
+
+// loss[f] = mean_n (dis_n c_n - w log c_n)   (lib/loss.py:49); one CTA per frame, fixed order.
+__global__ void __launch_bounds__(256)
+loss_reduce_kernel(const float *__restrict__ dis, const float *__restrict__ pred_c, int N, float w,
+                   float *__restrict__ loss) {
+  __shared__ float red[8];
+  const int f = blockIdx.x;
+  float s = 0.f;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    const float c = pred_c[(size_t)f * N + n];
+    s += dis[(size_t)f * N + n] * c - w * logf(c);
+  }
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    loss[f] = t / (float)N;
+  }
+}
+
+// Backward combine: upstream grads of loss[f] and of the selected dis[f][which_max[f]].
+__global__ void __launch_bounds__(256)
+pose_loss_bwd_kernel(const float *__restrict__ g_loss, const float *__restrict__ g_dis_sel,
+                     const int32_t *__restrict__ which_max, const float *__restrict__ pred_c,
+                     const float *__restrict__ dis, const float *__restrict__ jac_r,
+                     const float *__restrict__ jac_t, int F, int N, float w,
+                     float *__restrict__ g_r, float *__restrict__ g_t, float *__restrict__ g_c) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)F * N) return;
+  const int f = (int)(i / N), n = (int)(i % N);
+  const float gl = g_loss ? g_loss[f] : 0.f;
+  const float c = pred_c[i];
+  float coef = gl * c / (float)N;
+  if (g_dis_sel != nullptr && which_max != nullptr && which_max[f] == n) coef += g_dis_sel[f];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) g_r[i * 4 + k] = coef * jac_r[i * 4 + k];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) g_t[i * 3 + k] = coef * jac_t[i * 3 + k];
+  if (g_c != nullptr) g_c[i] = gl * (dis[i] - w / c) / (float)N;
+}
+
+// ---------------------------------------------------------------------------------------------
+// (5) best-vote selection + re-centring, lib/loss.py:52-69.  One CTA per frame.
+__device__ __forceinline__ void recentre_rows(const float *__restrict__ src, float *__restrict__ dst,
+                                              int rows, const float *R, const float *t) {
+  for (int i = threadIdx.x; i < rows; i += blockDim.x) {
+    const float a = src[3 * i] - t[0], b = src[3 * i + 1] - t[1], c = src[3 * i + 2] - t[2];
+    // (x - t) . R  (row vector times ori_base, lib/loss.py:62,66)
+    dst[3 * i + 0] = a * R[0] + b * R[3] + c * R[6];
+    dst[3 * i + 1] = a * R[1] + b * R[4] + c * R[7];
+    dst[3 * i + 2] = a * R[2] + b * R[5] + c * R[8];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+pose_select_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
+                   const float *__restrict__ pred_c, const float *__restrict__ dis,
+                   const float *__restrict__ target, const float *__restrict__ points, int N, int M,
+                   int32_t *__restrict__ which_max, float *__restrict__ dis_sel,
+                   float *__restrict__ new_points, float *__restrict__ new_target,
+                   float *__restrict__ pose_out) {
+  __shared__ float sval[8];
+  __shared__ int sidx[8];
+  __shared__ float sR[9], sT[3];
+  const int f = blockIdx.x;
+  const float *c = pred_c + (size_t)f * N;
+  // argmax, lowest index on ties (torch.max over dim 1, lib/loss.py:53)
+  float bv = -CUDART_INF_F;
+  int bi = 0x7fffffff;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    const float v = c[n];
+    if (v > bv || bi == 0x7fffffff) { bv = v; bi = n; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (oi != 0x7fffffff && (bi == 0x7fffffff || ov > bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sval[threadIdx.x >> 5] = bv; sidx[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) {
+      const float ov = sval[w];
+      const int oi = sidx[w];
+      if (oi != 0x7fffffff && (bi == 0x7fffffff || ov > bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
+    }
+    if (bi == 0x7fffffff) bi = 0;
+    const size_t fn = (size_t)f * N + bi;
+    Pose P;
+    make_pose(pred_r + fn * 4, P);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) sR[i] = P.R[i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) sT[i] = pred_t[fn * 3 + i] + points[fn * 3 + i];  // lib/loss.py:57
+    if (which_max) which_max[f] = bi;
+    if (dis_sel && dis) dis_sel[f] = dis[fn];
+    if (pose_out) {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) pose_out[(size_t)f * 12 + i] = P.R[i];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) pose_out[(size_t)f * 12 + 9 + i] = sT[i];
+    }
+  }
+  __syncthreads();
+  if (new_points) recentre_rows(points + (size_t)f * N * 3, new_points + (size_t)f * N * 3, N, sR, sT);
+  if (new_target) recentre_rows(target + (size_t)f * M * 3, new_target + (size_t)f * M * 3, M, sR, sT);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Refiner loss, lib/loss_refiner.py:12-62: one pose per frame, one CTA per frame.
+constexpr int REFINE_THREADS = 256;
+template <bool FAST, bool JAC>
+__global__ void __launch_bounds__(REFINE_THREADS)
+refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
+                   const float *__restrict__ target, const float *__restrict__ model,
+                   const float *__restrict__ points, const int64_t *__restrict__ obj,
+                   const uint8_t *__restrict__ sym_lut, int num_obj, int N, int M,
+                   float *__restrict__ dis, float *__restrict__ new_points,
+                   float *__restrict__ new_target, float *__restrict__ jac_r,
+                   float *__restrict__ jac_t, float *__restrict__ pose_out) {
+  extern __shared__ __align__(16) float dyn[];
+  __shared__ float red[(REFINE_THREADS / 32) * 13];
+  __shared__ float sR[9], sT[3];
+  const int f = blockIdx.x;
+  const float *tb = target + (size_t)f * M * 3;
+  const float *mb = model + (size_t)f * M * 3;
+  Pose P;
+  make_pose(pred_r + (size_t)f * 4, P);
+  P.s[0] = pred_t[(size_t)f * 3]; P.s[1] = pred_t[(size_t)f * 3 + 1]; P.s[2] = pred_t[(size_t)f * 3 + 2];
+  Acc A;
+  acc_zero(A);
+  if (frame_is_sym(obj, sym_lut, num_obj, f)) {
+    const int Mp = knn_pad(M);
+    float *sx = dyn, *sy = dyn + Mp, *sz = dyn + 2 * Mp, *sw = dyn + 3 * Mp;
+    float cx = 0.f, cy = 0.f, cz = 0.f;
+    if (FAST) { cx = __ldg(tb); cy = __ldg(tb + 1); cz = __ldg(tb + 2); }
+    stage_targets<FAST>(tb, M, Mp, sx, sy, sz, sw, cx, cy, cz);
+    __syncthreads();
+    adds_accumulate<FAST, JAC>(P, mb, tb, M, Mp, sx, sy, sz, sw, cx, cy, cz, A);
+  } else {
+    for (int j = threadIdx.x; j < M; j += blockDim.x) {
+      const float mx = __ldg(mb + 3 * j), my = __ldg(mb + 3 * j + 1), mz = __ldg(mb + 3 * j + 2);
+      const float px = fmaf(P.R[0], mx, fmaf(P.R[1], my, fmaf(P.R[2], mz, P.s[0])));
+      const float py = fmaf(P.R[3], mx, fmaf(P.R[4], my, fmaf(P.R[5], mz, P.s[1])));
+      const float pz = fmaf(P.R[6], mx, fmaf(P.R[7], my, fmaf(P.R[8], mz, P.s[2])));
+      acc_pair<JAC>(A, px, py, pz, __ldg(tb + 3 * j), __ldg(tb + 3 * j + 1), __ldg(tb + 3 * j + 2), mx, my, mz);
+    }
+  }
+  acc_block_reduce<JAC>(A, red);
+  if (threadIdx.x == 0) {
+    const float invM = 1.0f / (float)M;
+    dis[f] = A.dis * invM;
+    if (JAC) {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) A.G[i] *= invM;
+      float jq[4];
+      jac_quat(P, A.G, jq);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) jac_r[(size_t)f * 4 + i] = jq[i];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) jac_t[(size_t)f * 3 + i] = A.gs[i] * invM;
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) sR[i] = P.R[i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) sT[i] = P.s[i];
+    if (pose_out) {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) pose_out[(size_t)f * 12 + i] = P.R[i];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) pose_out[(size_t)f * 12 + 9 + i] = P.s[i];
+    }
+  }
+  __syncthreads();
+  if (new_points) recentre_rows(points + (size_t)f * N * 3, new_points + (size_t)f * N * 3, N, sR, sT);
+  if (new_target) recentre_rows(tb, new_target + (size_t)f * M * 3, M, sR, sT);
+}
+
+static int set_dyn_smem(const void *fn, size_t bytes) {
+  if (bytes <= 48 * 1024) return 0;
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem=%zu): %s", bytes, cudaGetErrorString(e)); return (int)e; }
+  return 0;
+}
+
+}  // namespace plr2
+
+using namespace plr2;
+
+#define PLR2_LAUNCH_ADDS(KERNEL, FASTV, JACV, GRID, BLOCK, SMEM, ST, ...)                      \
+  do {                                                                                           \
+    auto kfn = KERNEL<FASTV, JACV>;                                                              \
+    int rc_ = set_dyn_smem((const void *)kfn, SMEM);                                             \
+    if (rc_) return rc_;                                                                         \
+    kfn<<<GRID, BLOCK, SMEM, ST>>>(__VA_ARGS__);                                                 \
+  } while (0)
+
+extern "C" int plr2_pose_loss_fwd(const float *pred_r, const float *pred_t, const float *pred_c,
+                                  const float *target, const float *model_points, const float *points,
+                                  const int64_t *obj, const uint8_t *sym_lut, int num_obj, int frames,
+                                  int n_points, int n_mesh, float w, int refine, int knn_mode,
+                                  float *dis, float *loss, float *jac_r, float *jac_t, void *stream) {
+  if (frames < 0 || n_points <= 0 || n_mesh <= 0 || frames > 65535) {
+    set_error("plr2_pose_loss_fwd: bad shape F=%d N=%d M=%d", frames, n_points, n_mesh);
+    return PLR2_E_SHAPE;
+  }
+  if (frames == 0) return 0;
+  if (!pred_r || !pred_t || !target || !model_points || !points || !dis || (loss && !pred_c) ||
+      ((jac_r == nullptr) != (jac_t == nullptr))) {
+    set_error("plr2_pose_loss_fwd: null pointer");
+    return PLR2_E_NULLPTR;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool jac = jac_r != nullptr;
+  const bool may_sym = !refine && sym_lut != nullptr && obj != nullptr;
+  dim3 g1((n_points + ADD_NPB - 1) / ADD_NPB, frames);
+  if (jac)
+    add_loss_kernel<true><<<g1, ADD_SLICES * ADD_NPB, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, may_sym ? 1 : 0, dis, jac_r, jac_t);
+  else
+    add_loss_kernel<false><<<g1, ADD_SLICES * ADD_NPB, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, may_sym ? 1 : 0, dis, jac_r, jac_t);
+  if (may_sym) {
+    if (n_mesh > 8192) { set_error("plr2_pose_loss_fwd: ADD-S needs n_mesh <= 8192 (got %d)", n_mesh); return PLR2_E_UNSUPPORTED; }
+    const bool fast = knn_mode == PLR2_KNN_FAST;
+    const size_t smem = (size_t)knn_pad(n_mesh) * sizeof(float) * (fast ? 4 : 3);
+    dim3 g2(n_points, frames);
+#define ARGS pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, dis, jac_r, jac_t
+    if (fast && jac) PLR2_LAUNCH_ADDS(adds_loss_kernel, true, true, g2, ADDS_THREADS, smem, st, ARGS);
+    else if (fast) PLR2_LAUNCH_ADDS(adds_loss_kernel, true, false, g2, ADDS_THREADS, smem, st, ARGS);
+    else if (jac) PLR2_LAUNCH_ADDS(adds_loss_kernel, false, true, g2, ADDS_THREADS, smem, st, ARGS);
+    else PLR2_LAUNCH_ADDS(adds_loss_kernel, false, false, g2, ADDS_THREADS, smem, st, ARGS);
+#undef ARGS
+  }
+  if (loss) loss_reduce_kernel<<<frames, 256, 0, st>>>(dis, pred_c, n_points, w, loss);
+  return check_launch("plr2_pose_loss_fwd");
+}
+
+extern "C" int plr2_pose_loss_bwd(const float *g_loss, const float *g_dis_sel, const int32_t *which_max,
+                                  const float *pred_c, const float *dis, const float *jac_r,
+                                  const float *jac_t, int frames, int n_points, float w,
+                                  float *g_pred_r, float *g_pred_t, float *g_pred_c, void *stream) {
+  if (frames < 0 || n_points <= 0) { set_error("plr2_pose_loss_bwd: bad shape"); return PLR2_E_SHAPE; }
+  if (frames == 0) return 0;
+  if (!pred_c || !dis || !jac_r || !jac_t || !g_pred_r || !g_pred_t) { set_error("plr2_pose_loss_bwd: null pointer"); return PLR2_E_NULLPTR; }
+  const size_t tot = (size_t)frames * n_points;
+  pose_loss_bwd_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      g_loss, g_dis_sel, which_max, pred_c, dis, jac_r, jac_t, frames, n_points, w, g_pred_r, g_pred_t, g_pred_c);
+  return check_launch("plr2_pose_loss_bwd");
+}
+
+extern "C" int plr2_pose_select(const float *pred_r, const float *pred_t, const float *pred_c,
+                                const float *dis, const float *target, const float *points, int frames,
+                                int n_points, int n_mesh, int32_t *which_max, float *dis_sel,
+                                float *new_points, float *new_target, float *pose_out, void *stream) {
+  if (frames < 0 || n_points <= 0 || n_mesh < 0) { set_error("plr2_pose_select: bad shape"); return PLR2_E_SHAPE; }
+  if (frames == 0) return 0;
+  if (!pred_r || !pred_t || !pred_c || !points || (new_target && !target)) { set_error("plr2_pose_select: null pointer"); return PLR2_E_NULLPTR; }
+  pose_select_kernel<<<frames, 256, 0, (cudaStream_t)stream>>>(pred_r, pred_t, pred_c, dis, target, points, n_points, n_mesh, which_max, dis_sel, new_points, new_target, pose_out);
+  return check_launch("plr2_pose_select");
+}
+
+extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, const float *target,
+                                    const float *model_points, const float *points, const int64_t *obj,
+                                    const uint8_t *sym_lut, int num_obj, int frames, int n_points,
+                                    int n_mesh, int knn_mode, float *dis, float *new_points,
+                                    float *new_target, float *jac_r, float *jac_t, float *pose_out,
+                                    void *stream) {
+  if (frames < 0 || n_points < 0 || n_mesh <= 0) { set_error("plr2_refine_loss_fwd: bad shape"); return PLR2_E_SHAPE; }
+  if (frames == 0) return 0;
+  if (!pred_r || !pred_t || !target || !model_points || !dis || (new_points && !points) ||
+      ((jac_r == nullptr) != (jac_t == nullptr))) { set_error("plr2_refine_loss_fwd: null pointer"); return PLR2_E_NULLPTR; }
+  if (n_mesh > 8192) { set_error("plr2_refine_loss_fwd: n_mesh <= 8192 required (got %d)", n_mesh); return PLR2_E_UNSUPPORTED; }
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool fast = knn_mode == PLR2_KNN_FAST, jac = jac_r != nullptr;
+  const bool may_sym = sym_lut != nullptr && obj != nullptr;
+  const size_t smem = may_sym ? (size_t)knn_pad(n_mesh) * sizeof(float) * (fast ? 4 : 3) : 0;
+#define ARGS pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, dis, new_points, new_target, jac_r, jac_t, pose_out
+  if (fast && jac) PLR2_LAUNCH_ADDS(refine_loss_kernel, true, true, frames, REFINE_THREADS, smem, st, ARGS);
+  else if (fast) PLR2_LAUNCH_ADDS(refine_loss_kernel, true, false, frames, REFINE_THREADS, smem, st, ARGS);
+  else if (jac) PLR2_LAUNCH_ADDS(refine_loss_kernel, false, true, frames, REFINE_THREADS, smem, st, ARGS);
+  else PLR2_LAUNCH_ADDS(refine_loss_kernel, false, false, frames, REFINE_THREADS, smem, st, ARGS);
+#undef ARGS
+  return check_launch("plr2_refine_loss_fwd");
+}
