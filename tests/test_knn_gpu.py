@@ -1,0 +1,127 @@
+"""GPU: kernel (4) against the oracle / the reference's golden indices, through the C-ABI."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import knn_oracle as KO
+from plr2_b200 import synth
+from plr2_b200.lib.knn import KNN_EXACT, KNN_FAST, KNearestNeighbor, knn_indices
+from tests.util import knn_gap_ok, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def run(ref, query, k=1, mode=KNN_EXACT, dist=False):
+    r = torch.from_numpy(ref).cuda()[None].contiguous()
+    q = torch.from_numpy(query).cuda()[None].contiguous()
+    out = knn_indices(r, q, k, mode, return_dist=dist)
+    torch.cuda.synchronize()
+    if dist:
+        return out[0][0].cpu().numpy(), out[1][0].cpu().numpy()
+    return out[0].cpu().numpy()
+
+
+@pytest.mark.parametrize("name", ["knn_d3_k1", "knn_d3_k4", "knn_d16_k2"])
+def test_golden_reference_indices(name):
+    g = load_golden(name)
+    k = int(g["k"])
+    idx = run(g["ref"], g["query"], k)
+    _, best, second = KO.knn_oracle(g["ref"], g["query"], 1, contract=False, want_second=True)
+    if k == 1:
+        bad, decided, diff = knn_gap_ok(idx, g["idx"], best, second)
+        assert bad == 0 and decided > 1000
+        # exact ties planted in the fixture (duplicated refs, queries on refs) -> lowest index
+        assert np.array_equal(idx[0, :8], g["idx"][0, :8])
+    else:
+        # generic kernel, fma arithmetic: compare with the fma oracle bit for bit
+        assert np.array_equal(idx, KO.knn_oracle(g["ref"], g["query"], k, contract=True)[0])
+
+
+@pytest.mark.parametrize("n_ref,n_query", [(1, 1), (1, 700), (15, 33), (16, 512), (17, 513), (500, 5000),
+                                           (2047, 100), (2048, 1031), (2049, 777), (5000, 300)])
+def test_exact_mode_bit_exact_vs_fma_oracle(n_ref, n_query):
+    rng = np.random.default_rng(n_ref * 7 + n_query)
+    ref = (rng.standard_normal((3, n_ref)) * 0.1 + 0.7).astype(np.float32)
+    query = (rng.standard_normal((3, n_query)) * 0.1 + 0.7).astype(np.float32)
+    idx, dist = run(ref, query, 1, KNN_EXACT, dist=True)
+    oidx, odist = KO.knn_oracle(ref, query, 1, contract=True)
+    assert np.array_equal(idx, oidx)
+    assert np.array_equal(dist, odist)      # squared distances bit-identical to knn.cu arithmetic
+
+
+def test_ties_on_lattice_lowest_index_wins():
+    rng = np.random.default_rng(3)
+    ref = rng.integers(-3, 4, (3, 777)).astype(np.float32)
+    query = rng.integers(-3, 4, (3, 4099)).astype(np.float32)
+    for mode in (KNN_EXACT, KNN_FAST):   # integers: both forms are exact -> identical indices
+        assert np.array_equal(run(ref, query, 1, mode), KO.knn_oracle(ref, query, 1)[0])
+
+
+def test_fast_mode_gap_rule_ycb_shape():
+    fr = synth.make_frame(synth.YCB, 11, obj=12, with_image=False)
+    pr, pt, _ = synth.make_predictions(fr, 12)
+    # queries = transformed model points of the first 40 hypotheses (20 000 queries, 500 refs)
+    qs = []
+    for n in range(40):
+        q = pr[n] / np.linalg.norm(pr[n])
+        rot = synth.quat_to_rot_np(q).astype(np.float32)
+        qs.append(fr["model_points"] @ rot.T + fr["points"][n] + pt[n])
+    query = np.ascontiguousarray(np.concatenate(qs, 0).T.astype(np.float32))
+    ref = np.ascontiguousarray(fr["target"].T)
+    oidx, best, second = KO.knn_oracle(ref, query, 1, contract=True, want_second=True)
+    for mode in (KNN_EXACT, KNN_FAST):
+        bad, decided, diff = knn_gap_ok(run(ref, query, 1, mode), oidx, best, second)
+        assert bad == 0 and decided > 0.9 * query.shape[1]
+        if mode == KNN_EXACT:
+            assert diff == 0
+
+
+def test_nan_and_inf_follow_reference_kernel():
+    ref = np.array([[0, 1, 2, 3], [0, 0, 0, 0], [0, 0, 0, 0]], np.float32)
+    query = np.array([[np.nan, 2.2, np.inf], [0, 0, 0], [0, 0, 0]], np.float32)
+    idx = run(ref, query)
+    assert idx[0, 0] == 1          # all distances NaN: index stays at its initial 1 (knn.cu:127-128)
+    assert idx[0, 1] == 3
+    assert idx[0, 2] == 1          # all distances +inf: nothing is '<' the first
+    ref2 = ref.copy(); ref2[0, 0] = np.nan          # dist[0] NaN -> every later '<' is false
+    assert run(ref2, query[:, 1:2])[0, 0] == 1
+
+
+def test_batched_and_dropin_signature():
+    rng = np.random.default_rng(0)
+    ref = rng.standard_normal((3, 3, 90)).astype(np.float32)
+    query = rng.standard_normal((3, 3, 1000)).astype(np.float32)
+    inds = KNearestNeighbor.apply(torch.from_numpy(ref), torch.from_numpy(query), 1)   # CPU in, like the reference
+    assert inds.is_cuda and inds.dtype == torch.int64 and tuple(inds.shape) == (3, 1, 1000)
+    inds_kw = KNearestNeighbor.apply(torch.from_numpy(ref).cuda(), torch.from_numpy(query).cuda(), k=1)
+    assert torch.equal(inds, inds_kw)
+    for b in range(3):
+        assert np.array_equal(inds[b].cpu().numpy(), KO.knn_oracle(ref[b], query[b], 1)[0])
+    # the reference's pybind entry, caller-allocated idx
+    from plr2_b200.lib.knn import knn_pytorch
+    out = torch.empty(3, 2, 1000, dtype=torch.int64, device="cuda")
+    assert knn_pytorch.knn(torch.from_numpy(ref).cuda(), torch.from_numpy(query).cuda(), out) == 1
+    assert np.array_equal(out[1].cpu().numpy(), KO.knn_oracle(ref[1], query[1], 2)[0])
+    with pytest.raises(RuntimeError):
+        knn_pytorch.knn(torch.from_numpy(ref).cuda().double(), torch.from_numpy(query).cuda(), out)
+
+
+def test_full_size_properties_c2():
+    """BASELINE config C2 size (500 refs x 500 000 queries): size-independent checks —
+    (i) queries that ARE reference points return themselves (lowest duplicate), (ii) the returned
+    distance is <= the distance to 64 random references, (iii) a 20 000-query slice equals the oracle."""
+    rng = np.random.default_rng(42)
+    n_ref, n_query = 500, 500_000
+    ref = (rng.standard_normal((3, n_ref)) * 0.05).astype(np.float32)
+    query = (rng.standard_normal((3, n_query)) * 0.05).astype(np.float32)
+    self_ids = rng.integers(0, n_ref, 1000)
+    query[:, :1000] = ref[:, self_ids]
+    idx, dist = run(ref, query, 1, KNN_EXACT, dist=True)
+    assert np.array_equal(idx[0, :1000], self_ids + 1) and np.all(dist[0, :1000] == 0)
+    probe = rng.integers(0, n_ref, 64)
+    d = ((query[:, :, None] - ref[:, None, probe]) ** 2).sum(0)
+    assert np.all(dist[0][:, None] <= d * (1 + 1e-6) + 1e-12)
+    sl = slice(300_000, 320_000)
+    assert np.array_equal(idx[:, sl], KO.knn_oracle(ref, query[:, sl], 1)[0])
+    fidx = run(ref, query, 1, KNN_FAST)
+    assert (fidx != idx).mean() < 1e-3

@@ -1,0 +1,142 @@
+"""GPU: kernels (3) and (5) — Loss / Loss_refine drop-ins against the reference's golden outputs and
+against the oracle on the same seeded inputs, through the C-ABI."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import densefusion_oracle as DO
+from plr2_b200 import ops, synth
+from plr2_b200.lib.loss import Loss
+from plr2_b200.lib.loss_refiner import Loss_refine
+from tests.util import assert_close, load_golden, shape_of, tt
+
+pytestmark = pytest.mark.gpu
+
+
+def cuda_loss(fr, preds, shp, w, refine, knn_mode=ops.KNN_EXACT, grad_mix=0.5):
+    pr, pt, pc = [tt(a, "cuda", grad=True) for a in preds]
+    crit = Loss(shp.num_mesh, list(shp.sym_list), knn_mode)
+    loss, dis, npts, ntgt = crit(pr[None], pt[None], pc[None], tt(fr["target"], "cuda")[None],
+                                 tt(fr["model_points"], "cuda")[None], tt(fr["idx"], "cuda").reshape(1, 1),
+                                 tt(fr["points"], "cuda")[None], w, refine)
+    assert loss.dim() == 0 and dis.dim() == 0 and tuple(npts.shape) == (1, shp.num_points, 3)
+    assert tuple(ntgt.shape) == (1, shp.num_mesh, 3) and not npts.requires_grad and not ntgt.requires_grad
+    (loss + grad_mix * dis).backward()
+    return [x.detach().cpu().numpy() for x in (loss, dis, npts[0], ntgt[0], pr.grad, pt.grad, pc.grad)]
+
+
+@pytest.mark.parametrize("name", ["loss_ycb_sym", "loss_ycb_nonsym", "loss_linemod_sym"])
+@pytest.mark.parametrize("mode", [ops.KNN_EXACT, ops.KNN_FAST])
+def test_loss_matches_reference_golden(name, mode):
+    g = load_golden(name)
+    shp = shape_of(g)
+    fr = synth.make_frame(shp, int(g["seed"]), obj=int(g["obj"]), with_image=False)
+    preds = synth.make_predictions(fr, int(g["seed"]) + 7)
+    loss, dis, npts, ntgt, gr, gt, gc = cuda_loss(fr, preds, shp, float(g["w"]), bool(g["refine"]), mode)
+    assert_close(loss, g["loss"], "loss", frac=1.0)
+    assert_close(dis, g["dis"], "dis", frac=1.0)
+    assert_close(npts, g["new_points"][0], "new_points")
+    assert_close(ntgt, g["new_target"][0], "new_target")
+    assert_close(gr, g["g_pred_r"][0], "g_pred_r")
+    assert_close(gt, g["g_pred_t"][0], "g_pred_t")
+    assert_close(gc, g["g_pred_c"][0], "g_pred_c")
+
+
+@pytest.mark.parametrize("shape,obj,refine", [(synth.LINEMOD, 3, False), (synth.LINEMOD, 7, False),
+                                              (synth.YCB, 12, False), (synth.YCB, 5, False),
+                                              (synth.YCB_REFINE, 12, True), (synth.YCB_REFINE, 3, True)])
+def test_loss_full_size_vs_oracle(shape, obj, refine):
+    """BASELINE configs C1/C2/C3 loss shapes (N=500/1000, M=500/2300) against the oracle."""
+    fr = synth.make_frame(shape, 77 + obj, obj=obj, with_image=False)
+    preds = synth.make_predictions(fr, 78)
+    w = 0.015
+    loss, dis, npts, ntgt, gr, gt, gc = cuda_loss(fr, preds, shape, w, refine)
+    pr, pt, pc = [tt(a, grad=True) for a in preds]
+    ol, od, onp, ont, ex = DO.pose_loss(pr, pt, pc, tt(fr["target"]), tt(fr["model_points"]), obj,
+                                        tt(fr["points"]), w, refine, shape.sym_list)
+    (ol + 0.5 * od).backward()
+    assert_close(loss, ol.item(), "loss", frac=1.0)
+    assert_close(dis, od.item(), "dis", frac=1.0)
+    assert_close(npts, onp.numpy(), "new_points")
+    assert_close(ntgt, ont.numpy(), "new_target")
+    assert_close(gr, pr.grad.numpy(), "g_pred_r")
+    assert_close(gt, pt.grad.numpy(), "g_pred_t")
+    assert_close(gc, pc.grad.numpy(), "g_pred_c")
+
+
+def test_adds_known_answer_on_gpu():
+    """src/estimation/main.py:121-131 known answer through the CUDA loss."""
+    pts = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0]], np.float32)
+    q = torch.tensor([[[np.cos(np.pi / 4), 0, 0, np.sin(np.pi / 4)]]], dtype=torch.float32, device="cuda")
+    z = torch.zeros(1, 1, 3, device="cuda")
+    c = torch.full((1, 1, 1), 0.5, device="cuda")
+    P = tt(pts, "cuda")[None]
+    crit = Loss(4, [1])
+    _, d_sym, _, _ = crit(q, z, c, P, P, torch.tensor([[1]], device="cuda"), z, 0.015, False)
+    _, d_non, _, _ = crit(q, z, c, P, P, torch.tensor([[0]], device="cuda"), z, 0.015, False)
+    assert float(d_sym) < 1e-6 and float(d_non) == pytest.approx(np.sqrt(2.0), rel=1e-5)
+
+
+def test_batched_frames_equal_per_frame_calls():
+    shp = synth.Shape(300, 21, 130, 20, 20, tuple(synth.YCB_SYM))
+    objs = [12, 3, 15, 0, 20]
+    frs = [synth.make_frame(shp, 900 + i, obj=o, with_image=False) for i, o in enumerate(objs)]
+    prs = [synth.make_predictions(f, 950 + i) for i, f in enumerate(frs)]
+    st = lambda key: tt(np.stack([f[key] for f in frs]), "cuda")
+    crit = Loss(shp.num_mesh, list(shp.sym_list))
+    B = [tt(np.stack([p[i] for p in prs]), "cuda") for i in range(3)]
+    loss, dis, npts, ntgt = crit(B[0], B[1], B[2], st("target"), st("model_points"),
+                                 tt(np.array(objs)[:, None], "cuda"), st("points"), 0.015, False)
+    assert tuple(loss.shape) == (5,) and tuple(dis.shape) == (5,)
+    for i, f in enumerate(frs):
+        l1, d1, p1, t1 = crit(B[0][i:i + 1], B[1][i:i + 1], B[2][i:i + 1], st("target")[i:i + 1],
+                              st("model_points")[i:i + 1], tt(np.array([[objs[i]]]), "cuda"),
+                              st("points")[i:i + 1], 0.015, False)
+        assert torch.equal(l1, loss[i]) and torch.equal(d1, dis[i])
+        assert torch.equal(p1[0], npts[i]) and torch.equal(t1[0], ntgt[i])
+
+
+@pytest.mark.parametrize("name", ["refiner_ycb_sym", "refiner_ycb_nonsym"])
+def test_refine_loss_matches_reference_golden(name):
+    g = load_golden(name)
+    shp = shape_of(g)
+    fr = synth.make_frame(shp, int(g["seed"]) + 1, obj=int(g["obj"]))
+    crit = Loss_refine(shp.num_mesh, list(shp.sym_list))
+    pts, tgt = tt(g["in_points"], "cuda")[None], tt(g["in_target"], "cuda")[None]
+    idx = tt(fr["idx"], "cuda").reshape(1, 1)
+    for ite in range(2):
+        pr = tt(g[f"it{ite}.pred_r"], "cuda", grad=True)
+        pt = tt(g[f"it{ite}.pred_t"], "cuda", grad=True)
+        dis, pts, tgt = crit(pr, pt, tgt, tt(fr["model_points"], "cuda")[None], idx, pts)
+        assert tuple(dis.shape) == (1,)
+        dis.backward()
+        assert_close(dis.detach().cpu().numpy(), g[f"it{ite}.dis"], "dis", frac=1.0)
+        assert_close(pts[0].cpu().numpy(), g[f"it{ite}.new_points"][0], "new_points")
+        assert_close(tgt[0].cpu().numpy(), g[f"it{ite}.new_target"][0], "new_target")
+        assert_close(pr.grad.cpu().numpy(), g[f"it{ite}.g_pred_r"], "g_pred_r", frac=1.0)
+        assert_close(pt.grad.cpu().numpy(), g[f"it{ite}.g_pred_t"], "g_pred_t", frac=1.0)
+        # hand the REFERENCE's tensors to the next iteration so errors do not compound in the test
+        pts, tgt = tt(g[f"it{ite}.new_points"], "cuda"), tt(g[f"it{ite}.new_target"], "cuda")
+
+
+@pytest.mark.parametrize("obj", [12, 3])
+def test_refine_loss_full_size_vs_oracle(obj):
+    shp = synth.YCB_REFINE       # M = 2300: 5.29e6 ADD-S pairs for symmetric classes
+    fr = synth.make_frame(shp, 1234, obj=obj, with_image=False)
+    rng = np.random.default_rng(9)
+    pr = (fr["gt_q"] + 0.05 * rng.standard_normal(4)).astype(np.float32)[None]
+    pt = (fr["gt_t"] + 0.005 * rng.standard_normal(3)).astype(np.float32)[None]
+    crit = Loss_refine(shp.num_mesh, list(shp.sym_list))
+    a, b = tt(pr, "cuda", grad=True), tt(pt, "cuda", grad=True)
+    dis, npts, ntgt = crit(a, b, tt(fr["target"], "cuda")[None], tt(fr["model_points"], "cuda")[None],
+                           tt(fr["idx"], "cuda").reshape(1, 1), tt(fr["points"], "cuda")[None])
+    dis.backward()
+    oa, ob = tt(pr, grad=True), tt(pt, grad=True)
+    od, onp, ont, _ = DO.refine_loss(oa, ob, tt(fr["target"]), tt(fr["model_points"]), obj, tt(fr["points"]),
+                                     shp.sym_list)
+    od.backward()
+    assert_close(dis.detach().cpu().numpy(), od.detach().numpy(), "dis", frac=1.0)
+    assert_close(npts[0].cpu().numpy(), onp.numpy(), "new_points")
+    assert_close(ntgt[0].cpu().numpy(), ont.numpy(), "new_target")
+    assert_close(a.grad.cpu().numpy(), oa.grad.numpy(), "g_pred_r", frac=1.0)
+    assert_close(b.grad.cpu().numpy(), ob.grad.numpy(), "g_pred_t", frac=1.0)
