@@ -107,6 +107,96 @@ int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t,
                          float *dis, float *new_points, float *new_target,
                          float *jac_r, float *jac_t, float *pose_out, void *stream);
 
+/* ---- (2) dense contractions --------------------------------------------------------------
+ * General FP32 GEMM with fused epilogue, C(m,n) (+)= f(sum_k A(m,k) B(k,n)):
+ *   A(m,k) = A[m*sam + k*sak],  B(k,n) = B[k*sbk + n*sbn],  C(m,n) = C[m*ldc + n]
+ *   f(x) = relu?( x + bias[n] + frame_bias[(m / rows_per_frame)*ldfb + n] ) * (relu_mask(m,n) > 0)
+ * Replaces the Conv1d(k=1)/Linear library calls of lib/network.py:54-63,107-121,152-163,193-200
+ * and their autograd (dX = dY W, dW = dY^T X).  split_k > 1 needs accumulate=1 (atomic adds). */
+typedef struct plr2_gemm_desc {
+  const float *A; long long sam, sak;
+  const float *B; long long sbk, sbn;
+  float *C; long long ldc;
+  int M, N, K;
+  const float *bias;                 /* [N] or NULL */
+  const float *frame_bias;           /* [frames][ldfb] or NULL */
+  int rows_per_frame; long long ldfb;
+  const float *relu_mask; long long ldmask;   /* or NULL */
+  int relu, accumulate, split_k;
+} plr2_gemm_desc;
+int plr2_gemm_f32(const plr2_gemm_desc *desc, void *stream);
+
+/* Tensor-core contraction (tcgen05, sm_100a): C[M,N] (f32, ldc) = relu?(X W^T + bias) with both
+ * operands in SPLIT-BF16: two bf16 planes hi = bf16(v), lo = bf16(v - hi), plane p at
+ * base + p*plane_stride (elements), rows K-contiguous with pitch lda / ldw.  The product is evaluated
+ * as X_hi W_hi + X_hi W_lo + X_lo W_hi with FP32 accumulation in TMEM.  K must be a multiple of 64. */
+int plr2_split_bf16x2(const float *src, long long ld, long long rows, int cols, void *dst_planes,
+                      long long ldd, long long plane_stride, void *stream);
+int plr2_gemm_bf16x2(const void *A_planes, long long lda, long long a_plane, const void *W_planes,
+                     long long ldw, long long w_plane, int M, int N, int K, const float *bias, int relu,
+                     float *C, long long ldc, void *stream);
+
+/* ---- (1)+(2) PoseNet / PoseRefineNet hot path ---------------------------------------------
+ * Parameter tables: device pointers to the tensors of the reference's state dict, in this order
+ * (weight then bias of each layer; Conv1d weights (out,in,1) and Linear weights (out,in) are both
+ * row-major [out][in]):
+ *   PoseNet       (lib/network.py:39-52,70-93): feat.conv1, feat.e_conv1, feat.conv2, feat.e_conv2,
+ *                 feat.conv5, feat.conv6, conv1_r, conv1_t, conv1_c, conv2_r, conv2_t, conv2_c,
+ *                 conv3_r, conv3_t, conv3_c, conv4_r, conv4_t, conv4_c              (18 layers)
+ *   PoseRefineNet (lib/network.py:136-186): feat.conv1, feat.e_conv1, feat.conv2, feat.e_conv2,
+ *                 feat.conv5, feat.conv6, conv1_r, conv1_t, conv2_r, conv2_t, conv3_r, conv3_t (12)
+ * The same struct is used for gradients (float* written instead of read). */
+#define PLR2_POSENET_LAYERS 18
+#define PLR2_REFINER_LAYERS 12
+typedef struct plr2_param_table {
+  float *w[PLR2_POSENET_LAYERS];
+  float *b[PLR2_POSENET_LAYERS];
+} plr2_param_table;
+
+#define PLR2_NET_POSENET 0
+#define PLR2_NET_REFINER 1
+/* precision of the large contractions */
+#define PLR2_PREC_FP32 0      /* FP32 SIMT everywhere (bit-for-bit reproducible) */
+#define PLR2_PREC_BF16X2 1    /* tcgen05 kind::f16 on split-bf16 operands (hi+lo, 3 MMAs), FP32 accumulate in TMEM */
+
+/* Packed weight buffer (floats) and workspace (bytes) sizes. */
+size_t plr2_net_packed_floats(int net, int num_obj);
+size_t plr2_net_workspace_bytes(int net, int frames, int n_points, int num_obj, int training);
+/* Gather the state-dict tensors into the packed layout: packed[0, T) holds the FP32 copy and, when
+ * split_bf16 != 0, packed[T, 2T) (T = plr2_net_packed_floats/2) the split-bf16 planes of the same layout. */
+int plr2_net_pack(int net, const plr2_param_table *params, int num_obj, float *packed, int split_bf16,
+                  void *stream);
+/* Scatter a packed gradient buffer back into per-parameter tensors (overwrites them). */
+int plr2_net_unpack_grads(int net, const float *packed_grad, const plr2_param_table *grads, int num_obj,
+                          void *stream);
+
+/* PoseNet.forward without the backbone (lib/network.py:98-132) for `frames` frames:
+ *   out_img [F][32][hw] f32 backbone output; choose [F][N] i64; x [F][N][3]; obj [F] i64
+ *   -> pred_r [F][N][4], pred_t [F][N][3], pred_c [F][N][1], emb [F][32][N]
+ * training != 0 keeps every activation in the workspace for plr2_posenet_backward. */
+int plr2_posenet_forward(const float *packed, const float *out_img, const int64_t *choose, const float *x,
+                         const int64_t *obj, int frames, int n_points, int hw, int num_obj,
+                         void *workspace, size_t workspace_bytes, float *pred_r, float *pred_t,
+                         float *pred_c, float *emb, int training, int precision, void *stream);
+/* Backward: upstream grads of pred_r/t/c -> packed parameter grads (overwritten) and, if
+ * g_out_img != NULL, the gradient w.r.t. the backbone output (must be zero-filled by the caller;
+ * duplicates in `choose` accumulate).  Uses the workspace left by the training forward. */
+int plr2_posenet_backward(const float *packed, const int64_t *choose, const float *x, const int64_t *obj,
+                          int frames, int n_points, int hw, int num_obj, void *workspace,
+                          size_t workspace_bytes, const float *g_pred_r, const float *g_pred_t,
+                          const float *g_pred_c, float *packed_grad, float *g_out_img, int precision,
+                          void *stream);
+
+/* PoseRefineNet.forward (lib/network.py:187-206): x [F][N][3], emb [F][32][N], obj [F]
+ *   -> pred_r [F][4], pred_t [F][3] */
+int plr2_refiner_forward(const float *packed, const float *x, const float *emb, const int64_t *obj,
+                         int frames, int n_points, int num_obj, void *workspace, size_t workspace_bytes,
+                         float *pred_r, float *pred_t, int training, int precision, void *stream);
+int plr2_refiner_backward(const float *packed, const float *x, const float *emb, const int64_t *obj,
+                          int frames, int n_points, int num_obj, void *workspace, size_t workspace_bytes,
+                          const float *g_pred_r, const float *g_pred_t, float *packed_grad, int precision,
+                          void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -23,6 +23,41 @@ SIGNATURES = {
     "plr2_refine_loss_fwd": (_i, [_vp] * 7 + [_i] * 5 + [_vp] * 7),
 }
 
+
+
+class GemmDesc(C.Structure):
+    _fields_ = [("A", _vp), ("sam", C.c_longlong), ("sak", C.c_longlong),
+                ("B", _vp), ("sbk", C.c_longlong), ("sbn", C.c_longlong),
+                ("C", _vp), ("ldc", C.c_longlong),
+                ("M", _i), ("N", _i), ("K", _i),
+                ("bias", _vp), ("frame_bias", _vp), ("rows_per_frame", _i), ("ldfb", C.c_longlong),
+                ("relu_mask", _vp), ("ldmask", C.c_longlong),
+                ("relu", _i), ("accumulate", _i), ("split_k", _i)]
+
+
+POSENET_LAYERS = 18
+REFINER_LAYERS = 12
+
+
+class ParamTable(C.Structure):
+    _fields_ = [("w", _vp * POSENET_LAYERS), ("b", _vp * POSENET_LAYERS)]
+
+
+_pp = C.POINTER(ParamTable)
+SIGNATURES.update({
+    "plr2_gemm_f32": (_i, [C.POINTER(GemmDesc), _vp]),
+    "plr2_split_bf16x2": (_i, [_vp, C.c_longlong, C.c_longlong, _i, _vp, C.c_longlong, C.c_longlong, _vp]),
+    "plr2_gemm_bf16x2": (_i, [_vp, C.c_longlong, C.c_longlong, _vp, C.c_longlong, C.c_longlong, _i, _i, _i, _vp, _i, _vp, C.c_longlong, _vp]),
+    "plr2_net_packed_floats": (_sz, [_i, _i]),
+    "plr2_net_workspace_bytes": (_sz, [_i] * 5),
+    "plr2_net_pack": (_i, [_i, _pp, _i, _vp, _i, _vp]),
+    "plr2_net_unpack_grads": (_i, [_i, _vp, _pp, _i, _vp]),
+    "plr2_posenet_forward": (_i, [_vp] * 5 + [_i] * 4 + [_vp, _sz] + [_vp] * 4 + [_i, _i, _vp]),
+    "plr2_posenet_backward": (_i, [_vp] * 4 + [_i] * 4 + [_vp, _sz] + [_vp] * 5 + [_i, _vp]),
+    "plr2_refiner_forward": (_i, [_vp] * 4 + [_i] * 3 + [_vp, _sz] + [_vp] * 2 + [_i, _i, _vp]),
+    "plr2_refiner_backward": (_i, [_vp] * 4 + [_i] * 3 + [_vp, _sz] + [_vp] * 3 + [_i, _vp]),
+})
+
 _lib = None
 
 

@@ -1,0 +1,427 @@
+// Kernel (2): the dense contractions of the PointNet / head MLPs on the 5th-gen tensor cores.
+//
+//   Y[M,N] = epi( X[M,K] W[N,K]^T )   with X, W given as SPLIT-BF16:  v = hi + lo, hi = bf16(v),
+//   lo = bf16(v - hi)  (16 mantissa bits), and the product evaluated as
+//        X_hi W_hi + X_hi W_lo + X_lo W_hi          (3 tcgen05.mma kind::f16, FP32 accumulate in TMEM)
+// which keeps ~2^-16 relative operand error — enough for the north-star rtol 1e-3 on poses, losses and
+// gradients, which plain TF32 / bf16 operands do not reach on this network.
+//
+// Structure (one CTA per SM, persistent over output tiles of 128 x BN):
+//   warp 0    : TMA producer — per K-block of 64: X_hi, X_lo (128x64 bf16 each), W_hi, W_lo (BNx64)
+//               into a STAGES-deep shared-memory ring (128B-swizzled, K-major), mbarrier expect_tx
+//   warp 1    : MMA issuer — 3 products x 4 (UMMA_K = 16) tcgen05.mma per K-block into one of two
+//               TMEM accumulator stages; tcgen05.commit frees the smem slot / publishes the tile
+//   warp 2    : TMEM allocator
+//   warps 4-7 : epilogue — tcgen05.ld 32 lanes x 32 columns, + bias (+ per-frame bias), ReLU, then
+//               FP32 store | split-bf16 store (operand of the next layer) | per-frame pooling partials
+//               (AvgPool1d fused: conv6's output is never written)
+#include "gemm_tc.cuh"
+#include "tc_ptx.cuh"
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+namespace plr2 {
+
+using namespace tc;
+
+constexpr int TC_BM = 128, TC_BK = 64;
+constexpr int TC_THREADS = 256;
+constexpr int TC_EPI_PITCH = 36;                       // floats per staged row (32 + 4 pad: conflict-free float4)
+constexpr int TC_EPI_FLOATS = 32 * TC_EPI_PITCH;        // per epilogue warp
+
+template <int BN> struct TcCfg {
+  static constexpr int STAGES = BN == 256 ? 2 : 3;
+  static constexpr int A_BYTES = TC_BM * TC_BK * 2;            // one plane
+  static constexpr int B_BYTES = BN * TC_BK * 2;
+  static constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
+  static constexpr int TMEM_COLS = 2 * BN;                      // two accumulator stages
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 4 * 32 * 36 * 4 /*epilogue slabs*/;
+};
+
+struct TcKernelArgs {
+  int M, N, K, batch;
+  int m_tiles, n_tiles;
+  int a_col_z, b_row_z;          // per-batch offsets: A K-coordinate (elements), W row
+  long long c_col_z, bias_z;
+  const float *bias, *frame_bias;
+  int rows_per_frame; long long ldfb;
+  int relu, out_mode;
+  float *Cf; long long ldc;
+  __nv_bfloat16 *Cb; long long ldcb, c_plane;
+  float *pool;                   // [ceil(M/32)][2][N]
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
+                   const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
+                   const TcKernelArgs g) {
+  using Cfg = TcCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t *full_bar = bars;                       // [STAGES]  TMA -> MMA
+  uint64_t *empty_bar = bars + Cfg::STAGES;        // [STAGES]  MMA -> TMA
+  uint64_t *tfull_bar = bars + 2 * Cfg::STAGES;    // [2]       MMA -> epilogue
+  uint64_t *tempty_bar = tfull_bar + 2;            // [2]       epilogue -> MMA
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_kb = g.K / TC_BK;
+  const int tiles_per_z = g.m_tiles * g.n_tiles;
+  const int num_tiles = tiles_per_z * g.batch;
+
+  if (threadIdx.x == 0) {
+    prefetch_tensormap(&tmA_hi); prefetch_tensormap(&tmA_lo);
+    prefetch_tensormap(&tmB_hi); prefetch_tensormap(&tmB_lo);
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar + s, 1); mbar_init(tempty_bar + s, 128); }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int z = t / tiles_per_z, r = t % tiles_per_z;
+        const int m0 = (r / g.n_tiles) * TC_BM, n0 = (r % g.n_tiles) * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar + stage, phase ^ 1);
+          uint8_t *sA = smem + stage * Cfg::STAGE_BYTES;
+          uint8_t *sB = sA + 2 * Cfg::A_BYTES;
+          mbar_arrive_expect_tx(full_bar + stage, Cfg::STAGE_BYTES);
+          const int ka = z * g.a_col_z + kb * TC_BK, kw = kb * TC_BK, rw = z * g.b_row_z + n0;
+          tma_load_2d(sA, &tmA_hi, full_bar + stage, ka, m0);
+          tma_load_2d(sA + Cfg::A_BYTES, &tmA_lo, full_bar + stage, ka, m0);
+          tma_load_2d(sB, &tmB_hi, full_bar + stage, kw, rw);
+          tma_load_2d(sB + Cfg::B_BYTES, &tmB_lo, full_bar + stage, kw, rw);
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(TC_BM, BN);
+      int stage = 0; uint32_t phase = 0;
+      int as = 0; uint32_t aphase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        mbar_wait(tempty_bar + as, aphase ^ 1);          // epilogue has drained this accumulator
+        fence_after_sync();
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar + stage, phase);
+          fence_after_sync();
+          const uint32_t sA = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+          const uint32_t sB = sA + 2 * Cfg::A_BYTES;
+          const uint64_t a_hi = make_desc_k128(sA), a_lo = make_desc_k128(sA + Cfg::A_BYTES);
+          const uint64_t b_hi = make_desc_k128(sB), b_lo = make_desc_k128(sB + Cfg::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < TC_BK / 16; ++k) {          // small cross terms first, then hi*hi
+            const uint64_t adv = static_cast<uint64_t>(k * 2);   // 32 bytes >> 4 inside the swizzle atom
+            mma_f16(tmem_d, a_lo + adv, b_hi + adv, idesc, (kb | k) != 0);
+            mma_f16(tmem_d, a_hi + adv, b_lo + adv, idesc, 1);
+            mma_f16(tmem_d, a_hi + adv, b_hi + adv, idesc, 1);
+          }
+          mma_commit(empty_bar + stage);                  // smem slot reusable once these MMAs retire
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit(tfull_bar + as);                       // accumulator complete
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int wq = warp - 4;                              // TMEM lane quarter == warp % 4
+    int as = 0; uint32_t aphase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      const int z = t / tiles_per_z, r = t % tiles_per_z;
+      const int m0 = (r / g.n_tiles) * TC_BM, n0 = (r % g.n_tiles) * BN;
+      const float *bias = g.bias ? g.bias + z * g.bias_z : nullptr;
+      mbar_wait(tfull_bar + as, aphase);
+      fence_after_sync();
+      float *sT = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256) + wq * TC_EPI_FLOATS;
+      const int rbase = m0 + wq * 32;                     // first row of this warp's 32-row slab
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        if (n0 + c0 >= g.N) break;                        // warp-uniform
+        const int nc = n0 + c0;
+        // TMEM -> registers (thread = row) -> smem slab [32][36] -> registers (lanes along columns),
+        // so that every global store covers full 128-byte row segments.
+        uint32_t raw[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + as * BN + c0, raw);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<uint4 *>(sT + lane * TC_EPI_PITCH + 4 * q) = make_uint4(raw[4 * q], raw[4 * q + 1], raw[4 * q + 2], raw[4 * q + 3]);
+        __syncwarp();
+        if (g.out_mode != TC_OUT_BF16X2) {
+          const int cq = lane & 7, rq = lane >> 3;        // 8 column quads x 4 rows per pass
+          const int n = nc + 4 * cq;
+          const bool vec = n + 3 < g.N;
+          float bv[4] = {0.f, 0.f, 0.f, 0.f};
+          if (bias) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) if (n + j < g.N) bv[j] = __ldg(bias + n + j);
+          }
+          float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
+          const int fa = rbase / g.rows_per_frame;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = 4 * i + rq, row = rbase + r;
+            const float4 a4 = *reinterpret_cast<const float4 *>(sT + r * TC_EPI_PITCH + 4 * cq);
+            float a[4] = {a4.x + bv[0], a4.y + bv[1], a4.z + bv[2], a4.w + bv[3]};
+            if (row < g.M) {
+              const int fr = row / g.rows_per_frame;
+              if (g.frame_bias) {
+                const float *fb = g.frame_bias + (long long)fr * g.ldfb + n;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) if (n + j < g.N) a[j] += __ldg(fb + j);
+              }
+              if (g.relu) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) a[j] = fmaxf(a[j], 0.f);
+              }
+              if (g.out_mode == TC_OUT_F32) {
+                float *dst = g.Cf + (long long)row * g.ldc + z * g.c_col_z + n;
+                if (vec && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                  *reinterpret_cast<float4 *>(dst) = make_float4(a[0], a[1], a[2], a[3]);
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) if (n + j < g.N) dst[j] = a[j];
+                }
+              } else {                                    // TC_OUT_POOL: <= 2 frames per 32 rows
+                if (fr == fa) { sa[0] += a[0]; sa[1] += a[1]; sa[2] += a[2]; sa[3] += a[3]; }
+                else          { sb[0] += a[0]; sb[1] += a[1]; sb[2] += a[2]; sb[3] += a[3]; }
+              }
+            }
+          }
+          if (g.out_mode == TC_OUT_POOL && rbase < g.M) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              sa[j] += __shfl_xor_sync(0xffffffffu, sa[j], 8);  sa[j] += __shfl_xor_sync(0xffffffffu, sa[j], 16);
+              sb[j] += __shfl_xor_sync(0xffffffffu, sb[j], 8);  sb[j] += __shfl_xor_sync(0xffffffffu, sb[j], 16);
+            }
+            if (rq == 0) {
+              float *dst = g.pool + ((long long)(rbase >> 5) * 2) * g.N + n;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) if (n + j < g.N) { dst[j] = sa[j]; dst[g.N + j] = sb[j]; }
+            }
+          }
+        } else {
+          const int cq = lane & 3, rq = lane >> 2;        // 4 column octets x 8 rows per pass
+          const int n = nc + 8 * cq;
+          float bv[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bv[j] = (bias && n + j < g.N) ? __ldg(bias + n + j) : 0.f;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int r = 8 * i + rq, row = rbase + r;
+            const float4 a0 = *reinterpret_cast<const float4 *>(sT + r * TC_EPI_PITCH + 8 * cq);
+            const float4 a1 = *reinterpret_cast<const float4 *>(sT + r * TC_EPI_PITCH + 8 * cq + 4);
+            float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            if (row < g.M) {
+              const float *fb = g.frame_bias ? g.frame_bias + (long long)(row / g.rows_per_frame) * g.ldfb + n : nullptr;
+              uint32_t hi[4], lo[4];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                a[j] += bv[j];
+                if (fb && n + j < g.N) a[j] += __ldg(fb + j);
+                if (g.relu) a[j] = fmaxf(a[j], 0.f);
+              }
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const __nv_bfloat16 h0 = __float2bfloat16_rn(a[2 * q]), h1 = __float2bfloat16_rn(a[2 * q + 1]);
+                const __nv_bfloat16 l0 = __float2bfloat16_rn(a[2 * q] - __bfloat162float(h0));
+                const __nv_bfloat16 l1 = __float2bfloat16_rn(a[2 * q + 1] - __bfloat162float(h1));
+                hi[q] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+                lo[q] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+              }
+              __nv_bfloat16 *dh = g.Cb + (long long)row * g.ldcb + z * g.c_col_z + n;
+              __nv_bfloat16 *dl = dh + g.c_plane;
+              if (n + 7 < g.N) {
+                *reinterpret_cast<uint4 *>(dh) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4 *>(dl) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (n + j < g.N) {
+                    dh[j] = __ushort_as_bfloat16((unsigned short)(hi[j >> 1] >> ((j & 1) * 16)));
+                    dl[j] = __ushort_as_bfloat16((unsigned short)(lo[j >> 1] >> ((j & 1) * 16)));
+                  }
+              }
+            }
+          }
+        }
+        __syncwarp();
+      }
+      fence_before_sync();
+      mbar_arrive(tempty_bar + as);                       // 128 arrivals release the accumulator
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 2) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, int ncols, float *__restrict__ ap) {
+  const int f = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncols) return;
+  const long long r_beg = (long long)f * rows_per_frame;
+  long long r_end = r_beg + rows_per_frame;
+  if (r_end > M) r_end = M;
+  float s = 0.f;
+  for (long long g = r_beg >> 5; g <= (r_end - 1) >> 5; ++g) {
+    const int fa = (int)((g << 5) / rows_per_frame);        // frame of the group's first row
+    s += pool[(g * 2 + (fa == f ? 0 : 1)) * ncols + c];
+  }
+  ap[(long long)f * ncols + c] = s / (float)rows_per_frame;
+}
+
+int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap, cudaStream_t st) {
+  dim3 grid((ncols + 255) / 256, frames);
+  pool_finish_kernel<<<grid, 256, 0, st>>>(pool, rows_per_frame, M, ncols, ap);
+  return check_launch("pool_finish");
+}
+
+__global__ void __launch_bounds__(256)
+split_bf16x2_kernel(const float *__restrict__ src, long long ld, long long rows, int cols,
+                    __nv_bfloat16 *__restrict__ dst, long long ldd, long long plane) {
+  const long long total = rows * cols;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols; const int c = (int)(i % cols);
+    const float v = src[r * ld + c];
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    dst[r * ldd + c] = h;
+    dst[plane + r * ldd + c] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+int split_bf16x2(const float *src, long long ld, long long rows, int cols, __nv_bfloat16 *dst, long long ldd,
+                 long long plane, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  long long blocks = (rows * cols + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  split_bf16x2_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, ld, rows, cols, dst, ldd, plane);
+  return check_launch("split_bf16x2");
+}
+
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// K-major bf16 matrix [rows][cols] with row pitch ld (elements); box = 64 columns x box_rows rows.
+static int make_map(CUtensorMap *m, const __nv_bfloat16 *base, long long cols, long long rows, long long ld,
+                    int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled unavailable"); return PLR2_E_UNSUPPORTED; }
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld * 2) % 16) { set_error("tensor map: base/pitch not 16-byte aligned"); return PLR2_E_ALIGN; }
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16 *>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d): cols=%lld rows=%lld ld=%lld", (int)r, cols, rows, ld); return PLR2_E_UNSUPPORTED; }
+  return 0;
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <int BN>
+static int launch_tc(const TcGemm &g, cudaStream_t st) {
+  using Cfg = TcCfg<BN>;
+  CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
+  const long long a_cols = (long long)g.a_col_z * (g.batch - 1) + g.K;
+  const long long w_rows = (long long)g.b_row_z * (g.batch - 1) + g.N;
+  int rc;
+  if ((rc = make_map(&ma_hi, g.A, a_cols, g.M, g.lda, TC_BM))) return rc;
+  if ((rc = make_map(&ma_lo, g.A + g.a_plane, a_cols, g.M, g.lda, TC_BM))) return rc;
+  if ((rc = make_map(&mb_hi, g.W, g.K, w_rows, g.ldw, BN))) return rc;
+  if ((rc = make_map(&mb_lo, g.W + g.w_plane, g.K, w_rows, g.ldw, BN))) return rc;
+  TcKernelArgs k{};
+  k.M = g.M; k.N = g.N; k.K = g.K; k.batch = g.batch;
+  k.m_tiles = (g.M + TC_BM - 1) / TC_BM; k.n_tiles = (g.N + BN - 1) / BN;
+  k.a_col_z = g.a_col_z; k.b_row_z = g.b_row_z; k.c_col_z = g.c_col_z; k.bias_z = g.bias_z;
+  k.bias = g.bias; k.frame_bias = g.frame_bias; k.rows_per_frame = g.rows_per_frame > 0 ? g.rows_per_frame : 1; k.ldfb = g.ldfb;
+  k.relu = g.relu; k.out_mode = g.out_mode;
+  k.Cf = g.Cf; k.ldc = g.ldc; k.Cb = g.Cb; k.ldcb = g.ldcb; k.c_plane = g.c_plane; k.pool = g.pool;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16x2_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) { set_error("gemm_bf16x2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
+    attr_set = true;
+  }
+  const long long tiles = (long long)k.m_tiles * k.n_tiles * k.batch;
+  const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  gemm_bf16x2_kernel<BN><<<grid, TC_THREADS, Cfg::SMEM_BYTES, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, k);
+  return check_launch("gemm_bf16x2");
+}
+
+int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
+  if (g.M <= 0 || g.N <= 0) return 0;
+  if (g.K <= 0 || g.K % TC_BK) { set_error("gemm_bf16x2: K=%d must be a positive multiple of %d", g.K, TC_BK); return PLR2_E_SHAPE; }
+  if (!g.A || !g.W) { set_error("gemm_bf16x2: null operand"); return PLR2_E_NULLPTR; }
+  if (g.out_mode == TC_OUT_F32 && !g.Cf) { set_error("gemm_bf16x2: null Cf"); return PLR2_E_NULLPTR; }
+  if (g.out_mode == TC_OUT_BF16X2 && (!g.Cb || (g.ldcb % 8) || (g.c_col_z % 8))) { set_error("gemm_bf16x2: bf16 output needs 16-byte aligned rows"); return PLR2_E_ALIGN; }
+  if (g.out_mode == TC_OUT_POOL && (!g.pool || g.rows_per_frame < 32 || g.batch != 1)) { set_error("gemm_bf16x2: pooled output needs rows_per_frame >= 32"); return PLR2_E_UNSUPPORTED; }
+  if (g.N >= 256) return launch_tc<256>(g, st);
+  return launch_tc<128>(g, st);
+}
+
+}  // namespace plr2
+
+// C-ABI test/primitive entries ------------------------------------------------------------------
+extern "C" int plr2_split_bf16x2(const float *src, long long ld, long long rows, int cols, void *dst_planes,
+                                 long long ldd, long long plane_stride, void *stream) {
+  if (!src || !dst_planes) { plr2::set_error("plr2_split_bf16x2: null pointer"); return PLR2_E_NULLPTR; }
+  return plr2::split_bf16x2(src, ld, rows, cols, (__nv_bfloat16 *)dst_planes, ldd, plane_stride, (cudaStream_t)stream);
+}
+
+extern "C" int plr2_gemm_bf16x2(const void *A_planes, long long lda, long long a_plane, const void *W_planes,
+                                long long ldw, long long w_plane, int M, int N, int K, const float *bias, int relu,
+                                float *C, long long ldc, void *stream) {
+  plr2::TcGemm g;
+  g.A = (const __nv_bfloat16 *)A_planes; g.lda = lda; g.a_plane = a_plane;
+  g.W = (const __nv_bfloat16 *)W_planes; g.ldw = ldw; g.w_plane = w_plane;
+  g.M = M; g.N = N; g.K = K; g.bias = bias; g.relu = relu; g.out_mode = plr2::TC_OUT_F32; g.Cf = C; g.ldc = ldc;
+  return plr2::gemm_bf16x2(g, (cudaStream_t)stream);
+}

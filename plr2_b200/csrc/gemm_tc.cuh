@@ -1,0 +1,32 @@
+// Internal interface of the tcgen05 split-bf16 GEMM (gemm_bf16x2.cu).
+#pragma once
+#include "common.cuh"
+#include <cuda_bf16.h>
+
+namespace plr2 {
+
+enum { TC_OUT_F32 = 0, TC_OUT_BF16X2 = 1, TC_OUT_POOL = 2 };
+
+// Y = epi(X W^T).  X: bf16 planes [2][rows][lda] (plane stride a_plane elements), W likewise.
+// batch > 1: problem z reads X columns [z*a_col_z, +K), W rows [z*b_row_z, +N), writes C columns
+// [z*c_col_z, +N) and uses bias + z*bias_z.
+struct TcGemm {
+  const __nv_bfloat16 *A = nullptr; long long lda = 0, a_plane = 0;
+  const __nv_bfloat16 *W = nullptr; long long ldw = 0, w_plane = 0;
+  int M = 0, N = 0, K = 0, batch = 1;
+  int a_col_z = 0, b_row_z = 0; long long c_col_z = 0, bias_z = 0;
+  const float *bias = nullptr, *frame_bias = nullptr; int rows_per_frame = 1; long long ldfb = 0;
+  int relu = 0, out_mode = TC_OUT_F32;
+  float *Cf = nullptr; long long ldc = 0;
+  __nv_bfloat16 *Cb = nullptr; long long ldcb = 0, c_plane = 0;
+  float *pool = nullptr;      // TC_OUT_POOL: [ceil(M/32)][2][N] partial column sums
+};
+
+int gemm_bf16x2(const TcGemm &g, cudaStream_t st);
+// ap[f][c] = (1/rows_per_frame) * sum of the pooling partials belonging to frame f
+int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap, cudaStream_t st);
+// dst planes <- split(src): hi = bf16(v), lo = bf16(v - hi)
+int split_bf16x2(const float *src, long long ld, long long rows, int cols, __nv_bfloat16 *dst, long long ldd,
+                 long long plane, cudaStream_t st);
+
+}  // namespace plr2

@@ -1,0 +1,89 @@
+// Packed parameter layout and workspace carving for PoseNet / PoseRefineNet (host side).
+#pragma once
+#include "common.cuh"
+
+namespace plr2 {
+
+inline size_t al32(size_t n) { return (n + 31) / 32 * 32; }   // 128-byte granularity
+inline int al4(int n) { return (n + 3) / 4 * 4; }
+
+// Packed weights (floats).  Heads are concatenated so one launch covers r/t/c:
+//   PoseNet : h1pf [1920,384] = conv1_{r,t,c}.weight[:, 0:384]   (per-point part of the 1408 inputs)
+//             h1ap [1920,1024] = conv1_{r,t,c}.weight[:, 384:1408] (per-frame part: global feature)
+//             h2w [3][256,640], h3w [3][128,256], h4w [8*O,128] (r rows, t rows, c rows)
+//   Refiner : h1ap [1024,1024] = conv1_{r,t}.weight, h2w [2][128,512], h4w [7*O,128]; no h1pf/h3w
+struct NetLayout {
+  int net, O, heads;          // heads = 3 (posenet) / 2 (refiner)
+  int c5k;                    // conv5 input channels: 256 / 384
+  int h1n, h2n, h2k, h3n, h3k, h4k;
+  int oc[3], on[3], ldo;      // column offset / width of each head in the raw output buffer
+  size_t c1w, e1w, c2w, e2w, c5w, c6w, h1pf, h1ap, h2w, h3w, h4w;
+  size_t c1b, e1b, c2b, e2b, c5b, c6b, h1b, h2b, h3b, h4b;
+  size_t total;
+};
+
+inline NetLayout make_layout(int net, int O) {
+  NetLayout L{};
+  L.net = net; L.O = O;
+  const bool pn = net == PLR2_NET_POSENET;
+  L.heads = pn ? 3 : 2;
+  L.c5k = pn ? 256 : 384;
+  L.h1n = pn ? 640 : 512;          // per head
+  L.h2n = pn ? 256 : 128; L.h2k = L.h1n;
+  L.h3n = pn ? 128 : 0;   L.h3k = L.h2n;
+  L.h4k = 128;
+  const int widths[3] = {4, 3, 1};
+  int c = 0;
+  for (int h = 0; h < 3; ++h) {
+    L.oc[h] = c; L.on[h] = h < L.heads ? widths[h] * O : 0;
+    c += al4(L.on[h]);
+  }
+  L.ldo = c;
+  size_t o = 0;
+  auto take = [&](size_t n) { size_t r = o; o += al32(n); return r; };
+  L.c1w = take(64 * 4); L.e1w = take(64 * 32); L.c2w = take(128 * 64); L.e2w = take(128 * 64);
+  L.c5w = take((size_t)512 * L.c5k); L.c6w = take(1024 * 512);
+  L.h1pf = take(pn ? (size_t)3 * 640 * 384 : 0);
+  L.h1ap = take((size_t)L.heads * L.h1n * 1024);
+  L.h2w = take((size_t)L.heads * L.h2n * L.h2k);
+  L.h3w = take((size_t)L.heads * L.h3n * L.h3k);
+  L.h4w = take((size_t)(L.on[0] + L.on[1] + L.on[2]) * 128);
+  L.c1b = take(64); L.e1b = take(64); L.c2b = take(128); L.e2b = take(128); L.c5b = take(512); L.c6b = take(1024);
+  L.h1b = take((size_t)L.heads * L.h1n); L.h2b = take((size_t)L.heads * L.h2n); L.h3b = take((size_t)L.heads * L.h3n);
+  L.h4b = take((size_t)L.on[0] + L.on[1] + L.on[2]);
+  L.total = o;
+  return L;
+}
+
+// Workspace (floats) for R = frames*n_points rows.
+struct NetWorkspace {
+  float *pf, *x5, *x6, *ap, *hb, *h1, *h2, *h3, *out, *embT, *dpf, *dap, *dhb;
+  size_t floats;
+};
+
+inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, int n_points, int training) {
+  NetWorkspace W{};
+  const size_t R = (size_t)frames * n_points, F = frames;
+  const bool pn = L.net == PLR2_NET_POSENET;
+  float *p = reinterpret_cast<float *>(base);
+  size_t o = 0;
+  auto take = [&](size_t n) { float *r = p ? p + o : nullptr; o += al32(n); return r; };
+  W.pf = take(R * 384); W.x5 = take(R * 512); W.x6 = take(R * 1024);
+  W.ap = take(F * 1024);
+  const size_t h1all = (size_t)L.heads * L.h1n, h2all = (size_t)L.heads * L.h2n, h3all = (size_t)L.heads * L.h3n;
+  if (pn) {
+    W.hb = take(F * h1all); W.h1 = take(R * h1all); W.h2 = take(R * h2all); W.h3 = take(R * h3all);
+    W.out = take(R * L.ldo);
+  } else {
+    W.hb = nullptr; W.h1 = take(F * h1all); W.h2 = take(F * h2all); W.h3 = nullptr;
+    W.out = take(F * L.ldo);
+  }
+  W.embT = take(R * 32);
+  if (training) {
+    W.dpf = take(R * 384); W.dap = take(F * 1024); W.dhb = take(pn ? F * h1all : 0);
+  }
+  W.floats = o;
+  return W;
+}
+
+}  // namespace plr2

@@ -1,0 +1,23 @@
+// Internal declarations of the non-GEMM PointNet kernels (pointnet.cu).
+#pragma once
+#include "net_layout.cuh"
+
+namespace plr2 {
+
+int first_layer(const float *packed, const NetLayout &L, const float *out_img, const int64_t *choose,
+                const float *emb_in, const float *x, int frames, int N, int hw, float *pf, float *emb_out,
+                float *embT, cudaStream_t st);
+int scatter_emb_grad(const float *demb, const int64_t *choose, int frames, int N, int hw, float *g_out_img,
+                     cudaStream_t st);
+int segment_colsum(const float *X, long long ld, int nseg, int rows_per_seg, int ncols, float scale, float *out,
+                   long long ldo, cudaStream_t st);
+int segment_bcast_mask(const float *dseg, const float *X, size_t rows, int rows_per_seg, int ncols, float scale,
+                       float *dX, cudaStream_t st);
+int select_outputs(const float *raw, const NetLayout &L, const int64_t *obj, int rows_per_frame, size_t rows,
+                   float *pred_r, float *pred_t, float *pred_c, cudaStream_t st);
+int select_outputs_bwd(float *raw, const NetLayout &L, const int64_t *obj, int rows_per_frame, size_t rows,
+                       const float *g_r, const float *g_t, const float *g_c, cudaStream_t st);
+int net_copy_params(const NetLayout &L, const plr2_param_table *P, float *packed, bool to_packed, int round,
+                    cudaStream_t st);
+
+}  // namespace plr2

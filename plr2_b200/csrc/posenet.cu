@@ -1,0 +1,317 @@
+// Orchestration of kernels (1)+(2): PoseNet / PoseRefineNet forward and backward as a fixed sequence
+// of launches on one stream (no host synchronisation, CUDA-graph capturable).
+// Reference: lib/network.py:53-68,95-132 (PoseNet), :151-168,187-206 (PoseRefineNet).
+//
+// Activations are POINT-MAJOR: one row per point (row = frame*N + n), channels contiguous, so every
+// Conv1d(k=1) is Y = X W^T with both operands K-contiguous.  Feature buffer pf [R,384]:
+//   [0,64) relu(conv1 x) | [64,128) relu(e_conv1 emb) | [128,256) relu(conv2 .) | [256,384) relu(e_conv2 .)
+// i.e. pointfeat_1 | pointfeat_2 of the reference, already concatenated.
+// Algebraic hoist: the 1024 global-feature inputs of conv1_{r,t,c} are constant per
+// frame, so they enter as a per-frame bias hb = W1[:,384:] ap + b1 instead of 1024 extra K per point.
+#include "gemm.cuh"
+#include "pointnet.cuh"
+
+namespace plr2 {
+
+static int gemm_any(const GemmArgs &g, int precision, cudaStream_t st) {
+  (void)precision;
+  return gemm_f32(g, 1, st);
+}
+
+#define RC(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
+
+static int check_ws(const NetLayout &L, void *ws, size_t bytes, int frames, int n, int training, NetWorkspace &W) {
+  if (!ws) { set_error("network: workspace is NULL"); return PLR2_E_NULLPTR; }
+  if (reinterpret_cast<uintptr_t>(ws) & 127) { set_error("network: workspace must be 128-byte aligned"); return PLR2_E_ALIGN; }
+  W = carve_workspace(L, ws, frames, n, training);
+  if (W.floats * sizeof(float) > bytes) {
+    set_error("network: workspace too small (%zu < %zu bytes)", bytes, W.floats * sizeof(float));
+    return PLR2_E_WORKSPACE;
+  }
+  return 0;
+}
+
+// Shared PointNet feature trunk: first layer, conv2/e_conv2, conv5, conv6, per-frame mean.
+static int feat_forward(const float *pk, const NetLayout &L, const NetWorkspace &W, const float *out_img,
+                        const int64_t *choose, const float *emb_in, const float *x, int F, int N, int hw,
+                        float *emb_out, int training, int precision, cudaStream_t st) {
+  const int R = F * N;
+  RC(first_layer(pk, L, out_img, choose, emb_in, x, F, N, hw, W.pf, emb_out, training ? W.embT : nullptr, st));
+  GemmArgs g = gemm_nt(W.pf, 384, pk + L.c2w, 64, W.pf + 128, 384, R, 128, 64);   // conv2
+  g.bias = pk + L.c2b; g.relu = 1;
+  RC(gemm_any(g, precision, st));
+  g = gemm_nt(W.pf + 64, 384, pk + L.e2w, 64, W.pf + 256, 384, R, 128, 64);       // e_conv2
+  g.bias = pk + L.e2b; g.relu = 1;
+  RC(gemm_any(g, precision, st));
+  const float *a5 = L.c5k == 256 ? W.pf + 128 : W.pf;                              // pointfeat_2 | pointfeat_3
+  g = gemm_nt(a5, 384, pk + L.c5w, L.c5k, W.x5, 512, R, 512, L.c5k);              // conv5
+  g.bias = pk + L.c5b; g.relu = 1;
+  RC(gemm_any(g, precision, st));
+  g = gemm_nt(W.x5, 512, pk + L.c6w, 512, W.x6, 1024, R, 1024, 512);              // conv6
+  g.bias = pk + L.c6b; g.relu = 1;
+  RC(gemm_any(g, precision, st));
+  RC(segment_colsum(W.x6, 1024, F, N, 1024, 1.0f / (float)N, W.ap, 1024, st));    // AvgPool1d(num_points)
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Backward helpers.  Every dX is written IN PLACE over the activation whose ReLU it passes through
+// (the mask is read and the gradient written by the same thread), after the weight gradient that
+// still needs that activation has been issued.
+static int auto_split(int M, int N, int batch, int K) {
+  const long long tiles = (long long)((M + 127) / 128) * ((N + 127) / 128) * batch;
+  long long s = (2 * 148 + tiles - 1) / tiles;
+  const long long smax = K / 256 > 0 ? K / 256 : 1;
+  if (s > smax) s = smax;
+  return (int)(s < 1 ? 1 : s);
+}
+static int wgrad(GemmArgs g, cudaStream_t st) { return gemm_f32(g, auto_split(g.M, g.N, g.batch, g.K), st); }
+static int bgrad(const float *dY, long long ld, int rows, int ncols, float *db, cudaStream_t st) {
+  return segment_colsum(dY, ld, 1, rows, ncols, 1.0f, db, ncols, st);
+}
+
+// From W.dap (d loss / d pooled feature) and W.dpf (head contributions to d pf, or undefined when
+// !dpf_has_heads) down to the first layer.  Leaves d e1 in W.dpf[:,64:128] and d emb in W.embT.
+static int feat_backward(const float *pk, float *gp, const NetLayout &L, const NetWorkspace &W, const float *x,
+                         int F, int N, bool dpf_has_heads, cudaStream_t st) {
+  const int R = F * N;
+  // AvgPool1d backward through conv6's ReLU: dx6 = (x6 > 0) * dap[frame] / N     (in place)
+  RC(segment_bcast_mask(W.dap, W.x6, (size_t)R, N, 1024, 1.0f / (float)N, W.x6, st));
+  RC(wgrad(gemm_tn(W.x6, 1024, W.x5, 512, gp + L.c6w, 512, 1024, 512, R), st));
+  RC(bgrad(W.x6, 1024, R, 1024, gp + L.c6b, st));
+  GemmArgs g = gemm_nn(W.x6, 1024, pk + L.c6w, 512, W.x5, 512, R, 512, 1024);     // dx5 (in place)
+  g.relu_mask = W.x5; g.ldmask = 512;
+  RC(gemm_f32(g, 1, st));
+  const float *a5 = L.c5k == 256 ? W.pf + 128 : W.pf;
+  RC(wgrad(gemm_tn(W.x5, 512, a5, 384, gp + L.c5w, L.c5k, 512, L.c5k, R), st));
+  RC(bgrad(W.x5, 512, R, 512, gp + L.c5b, st));
+  const int off2 = L.c5k == 256 ? 0 : 128;    // column of pointfeat_2 inside conv5's input
+  if (L.c5k == 384) {                         // refiner: conv5 also reads pointfeat_1
+    g = gemm_nn(W.x5, 512, pk + L.c5w, 384, W.dpf, 384, R, 128, 512);
+    g.accumulate = dpf_has_heads ? 1 : 0;
+    RC(gemm_f32(g, 1, st));
+  }
+  g = gemm_nn(W.x5, 512, pk + L.c5w + off2, L.c5k, W.dpf + 128, 384, R, 256, 512);  // d pointfeat_2
+  g.accumulate = dpf_has_heads ? 1 : 0;
+  g.relu_mask = W.pf + 128; g.ldmask = 384;
+  RC(gemm_f32(g, 1, st));
+  // conv2 / e_conv2
+  for (int e = 0; e < 2; ++e) {
+    const int cin = e * 64, cout = 128 + e * 128;
+    const size_t wo = e ? L.e2w : L.c2w, bo = e ? L.e2b : L.c2b;
+    RC(wgrad(gemm_tn(W.dpf + cout, 384, W.pf + cin, 384, gp + wo, 64, 128, 64, R), st));
+    RC(bgrad(W.dpf + cout, 384, R, 128, gp + bo, st));
+    g = gemm_nn(W.dpf + cout, 384, pk + wo, 64, W.dpf + cin, 384, R, 64, 128);
+    g.accumulate = 1; g.relu_mask = W.pf + cin; g.ldmask = 384;
+    RC(gemm_f32(g, 1, st));
+  }
+  // conv1 (3 -> 64) and e_conv1 (32 -> 64)
+  RC(wgrad(gemm_tn(W.dpf, 384, x, 3, gp + L.c1w, 4, 64, 3, R), st));
+  RC(bgrad(W.dpf, 384, R, 64, gp + L.c1b, st));
+  RC(wgrad(gemm_tn(W.dpf + 64, 384, W.embT, 32, gp + L.e1w, 32, 64, 32, R), st));
+  RC(bgrad(W.dpf + 64, 384, R, 64, gp + L.e1b, st));
+  return 0;
+}
+
+}  // namespace plr2
+
+using namespace plr2;
+
+extern "C" size_t plr2_net_packed_floats(int net, int num_obj) { return 2 * make_layout(net, num_obj).total; }
+
+extern "C" size_t plr2_net_workspace_bytes(int net, int frames, int n_points, int num_obj, int training) {
+  const NetLayout L = make_layout(net, num_obj);
+  return carve_workspace(L, nullptr, frames, n_points, training).floats * sizeof(float);
+}
+
+extern "C" int plr2_net_pack(int net, const plr2_param_table *params, int num_obj, float *packed, int split_bf16,
+                             void *stream) {
+  if (!params || !packed) { set_error("plr2_net_pack: null pointer"); return PLR2_E_NULLPTR; }
+  if (num_obj <= 0 || (net != PLR2_NET_POSENET && net != PLR2_NET_REFINER)) { set_error("plr2_net_pack: bad net/num_obj"); return PLR2_E_SHAPE; }
+  return net_copy_params(make_layout(net, num_obj), params, packed, true, split_bf16, (cudaStream_t)stream);
+}
+
+extern "C" int plr2_net_unpack_grads(int net, const float *packed_grad, const plr2_param_table *grads, int num_obj,
+                                     void *stream) {
+  if (!grads || !packed_grad) { set_error("plr2_net_unpack_grads: null pointer"); return PLR2_E_NULLPTR; }
+  if (num_obj <= 0 || (net != PLR2_NET_POSENET && net != PLR2_NET_REFINER)) { set_error("plr2_net_unpack_grads: bad net/num_obj"); return PLR2_E_SHAPE; }
+  return net_copy_params(make_layout(net, num_obj), grads, const_cast<float *>(packed_grad), false, 0,
+                         (cudaStream_t)stream);
+}
+
+extern "C" int plr2_posenet_forward(const float *packed, const float *out_img, const int64_t *choose,
+                                    const float *x, const int64_t *obj, int frames, int n_points, int hw,
+                                    int num_obj, void *workspace, size_t workspace_bytes, float *pred_r,
+                                    float *pred_t, float *pred_c, float *emb, int training, int precision,
+                                    void *stream) {
+  if (frames < 0 || n_points <= 0 || hw <= 0 || num_obj <= 0) { set_error("plr2_posenet_forward: bad shape"); return PLR2_E_SHAPE; }
+  if (frames == 0) return 0;
+  if (!packed || !out_img || !choose || !x || !obj || !pred_r || !pred_t || !pred_c) { set_error("plr2_posenet_forward: null pointer"); return PLR2_E_NULLPTR; }
+  if ((long long)frames * n_points > 0x7fffffffLL / 2048) { set_error("plr2_posenet_forward: too many rows per call"); return PLR2_E_SHAPE; }
+  const NetLayout L = make_layout(PLR2_NET_POSENET, num_obj);
+  NetWorkspace W;
+  RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int F = frames, N = n_points, R = F * N;
+  const float *pk = packed;
+  RC(feat_forward(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, training, precision, st));
+  // per-frame bias of the three conv1 heads: hb[F,1920] = ap W1[:,384:]^T + b1   (FP32 always)
+  GemmArgs g = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.hb, 1920, F, 1920, 1024);
+  g.bias = pk + L.h1b;
+  RC(gemm_f32(g, 1, st));
+  // conv1_{r,t,c} on the per-point 384 channels, all three heads in one launch
+  g = gemm_nt(W.pf, 384, pk + L.h1pf, 384, W.h1, 1920, R, 1920, 384);
+  g.frame_bias = W.hb; g.rows_per_frame = N; g.ldfb = 1920; g.relu = 1;
+  RC(gemm_any(g, precision, st));
+  // conv2_* : block diagonal, batch = head
+  g = gemm_nt(W.h1, 1920, pk + L.h2w, 640, W.h2, 768, R, 256, 640);
+  g.bias = pk + L.h2b; g.relu = 1; g.batch = 3; g.zA = 640; g.zB = 256 * 640; g.zC = 256; g.zbias = 256;
+  RC(gemm_any(g, precision, st));
+  // conv3_*
+  g = gemm_nt(W.h2, 768, pk + L.h3w, 256, W.h3, 384, R, 128, 256);
+  g.bias = pk + L.h3b; g.relu = 1; g.batch = 3; g.zA = 256; g.zB = 128 * 256; g.zC = 128; g.zbias = 128;
+  RC(gemm_any(g, precision, st));
+  // conv4_* for every class (the class of each frame is selected afterwards)
+  size_t row = 0;
+  for (int h = 0; h < 3; ++h) {
+    g = gemm_nt(W.h3 + h * 128, 384, pk + L.h4w + row * 128, 128, W.out + L.oc[h], L.ldo, R, L.on[h], 128);
+    g.bias = pk + L.h4b + row;
+    RC(gemm_f32(g, 1, st));
+    row += L.on[h];
+  }
+  RC(select_outputs(W.out, L, obj, N, (size_t)R, pred_r, pred_t, pred_c, st));
+  return 0;
+}
+
+extern "C" int plr2_refiner_forward(const float *packed, const float *x, const float *emb, const int64_t *obj,
+                                    int frames, int n_points, int num_obj, void *workspace,
+                                    size_t workspace_bytes, float *pred_r, float *pred_t, int training,
+                                    int precision, void *stream) {
+  if (frames < 0 || n_points <= 0 || num_obj <= 0) { set_error("plr2_refiner_forward: bad shape"); return PLR2_E_SHAPE; }
+  if (frames == 0) return 0;
+  if (!packed || !x || !emb || !obj || !pred_r || !pred_t) { set_error("plr2_refiner_forward: null pointer"); return PLR2_E_NULLPTR; }
+  if ((long long)frames * n_points > 0x7fffffffLL / 2048) { set_error("plr2_refiner_forward: too many rows per call"); return PLR2_E_SHAPE; }
+  const NetLayout L = make_layout(PLR2_NET_REFINER, num_obj);
+  NetWorkspace W;
+  RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int F = frames, N = n_points;
+  const float *pk = packed;
+  RC(feat_forward(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, training, precision, st));
+  // Linear 1024 -> 512 (x2 heads), 512 -> 128, 128 -> num_obj*{4,3}: M = frames, FP32
+  GemmArgs g = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.h1, 1024, F, 1024, 1024);
+  g.bias = pk + L.h1b; g.relu = 1;
+  RC(gemm_f32(g, 1, st));
+  g = gemm_nt(W.h1, 1024, pk + L.h2w, 512, W.h2, 256, F, 128, 512);
+  g.bias = pk + L.h2b; g.relu = 1; g.batch = 2; g.zA = 512; g.zB = 128 * 512; g.zC = 128; g.zbias = 128;
+  RC(gemm_f32(g, 1, st));
+  size_t row = 0;
+  for (int h = 0; h < 2; ++h) {
+    g = gemm_nt(W.h2 + h * 128, 256, pk + L.h4w + row * 128, 128, W.out + L.oc[h], L.ldo, F, L.on[h], 128);
+    g.bias = pk + L.h4b + row;
+    RC(gemm_f32(g, 1, st));
+    row += L.on[h];
+  }
+  RC(select_outputs(W.out, L, obj, 1, (size_t)F, pred_r, pred_t, nullptr, st));
+  return 0;
+}
+
+extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose, const float *x,
+                                     const int64_t *obj, int frames, int n_points, int hw, int num_obj,
+                                     void *workspace, size_t workspace_bytes, const float *g_pred_r,
+                                     const float *g_pred_t, const float *g_pred_c, float *packed_grad,
+                                     float *g_out_img, int precision, void *stream) {
+  (void)precision;   // backward contractions run in FP32 in this version
+  if (frames <= 0 || n_points <= 0 || num_obj <= 0) { set_error("plr2_posenet_backward: bad shape"); return PLR2_E_SHAPE; }
+  if (!packed || !x || !obj || !g_pred_r || !g_pred_t || !g_pred_c || !packed_grad || (g_out_img && !choose)) {
+    set_error("plr2_posenet_backward: null pointer"); return PLR2_E_NULLPTR;
+  }
+  const NetLayout L = make_layout(PLR2_NET_POSENET, num_obj);
+  NetWorkspace W;
+  RC(check_ws(L, workspace, workspace_bytes, frames, n_points, 1, W));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int F = frames, N = n_points, R = F * N;
+  const float *pk = packed;
+  float *gp = packed_grad;
+  cudaError_t e = cudaMemsetAsync(gp, 0, L.total * sizeof(float), st);
+  if (e != cudaSuccess) { set_error("plr2_posenet_backward: memset: %s", cudaGetErrorString(e)); return (int)e; }
+  RC(select_outputs_bwd(W.out, L, obj, N, (size_t)R, g_pred_r, g_pred_t, g_pred_c, st));
+  size_t row = 0;
+  for (int h = 0; h < 3; ++h) {               // conv4_*
+    RC(wgrad(gemm_tn(W.out + L.oc[h], L.ldo, W.h3 + h * 128, 384, gp + L.h4w + row * 128, 128, L.on[h], 128, R), st));
+    RC(bgrad(W.out + L.oc[h], L.ldo, R, L.on[h], gp + L.h4b + row, st));
+    GemmArgs g = gemm_nn(W.out + L.oc[h], L.ldo, pk + L.h4w + row * 128, 128, W.h3 + h * 128, 384, R, 128, L.on[h]);
+    g.relu_mask = W.h3 + h * 128; g.ldmask = 384;
+    RC(gemm_f32(g, 1, st));
+    row += L.on[h];
+  }
+  // conv3_*
+  GemmArgs g = gemm_tn(W.h3, 384, W.h2, 768, gp + L.h3w, 256, 128, 256, R);
+  g.batch = 3; g.zA = 128; g.zB = 256; g.zC = 128 * 256;
+  RC(wgrad(g, st));
+  RC(bgrad(W.h3, 384, R, 384, gp + L.h3b, st));
+  g = gemm_nn(W.h3, 384, pk + L.h3w, 256, W.h2, 768, R, 256, 128);
+  g.batch = 3; g.zA = 128; g.zB = 128 * 256; g.zC = 256; g.relu_mask = W.h2; g.ldmask = 768; g.zmask = 256;
+  RC(gemm_f32(g, 1, st));
+  // conv2_*
+  g = gemm_tn(W.h2, 768, W.h1, 1920, gp + L.h2w, 640, 256, 640, R);
+  g.batch = 3; g.zA = 256; g.zB = 640; g.zC = 256 * 640;
+  RC(wgrad(g, st));
+  RC(bgrad(W.h2, 768, R, 768, gp + L.h2b, st));
+  g = gemm_nn(W.h2, 768, pk + L.h2w, 640, W.h1, 1920, R, 640, 256);
+  g.batch = 3; g.zA = 256; g.zB = 256 * 640; g.zC = 640; g.relu_mask = W.h1; g.ldmask = 1920; g.zmask = 640;
+  RC(gemm_f32(g, 1, st));
+  // conv1_*: per-point part, per-frame (pooled) part, bias
+  RC(wgrad(gemm_tn(W.h1, 1920, W.pf, 384, gp + L.h1pf, 384, 1920, 384, R), st));
+  RC(segment_colsum(W.h1, 1920, F, N, 1920, 1.0f, W.dhb, 1920, st));
+  RC(bgrad(W.dhb, 1920, F, 1920, gp + L.h1b, st));
+  RC(gemm_f32(gemm_tn(W.dhb, 1920, W.ap, 1024, gp + L.h1ap, 1024, 1920, 1024, F), 1, st));
+  RC(gemm_f32(gemm_nn(W.dhb, 1920, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1920), 1, st));
+  RC(gemm_f32(gemm_nn(W.h1, 1920, pk + L.h1pf, 384, W.dpf, 384, R, 384, 1920), 1, st));
+  RC(feat_backward(pk, gp, L, W, x, F, N, true, st));
+  if (g_out_img != nullptr) {                 // d emb = d e1 . We1, scattered back to the pixels
+    RC(gemm_f32(gemm_nn(W.dpf + 64, 384, pk + L.e1w, 32, W.embT, 32, R, 32, 64), 1, st));
+    RC(scatter_emb_grad(W.embT, choose, F, N, hw, g_out_img, st));
+  }
+  return 0;
+}
+
+extern "C" int plr2_refiner_backward(const float *packed, const float *x, const float *emb, const int64_t *obj,
+                                     int frames, int n_points, int num_obj, void *workspace,
+                                     size_t workspace_bytes, const float *g_pred_r, const float *g_pred_t,
+                                     float *packed_grad, int precision, void *stream) {
+  (void)precision; (void)emb;
+  if (frames <= 0 || n_points <= 0 || num_obj <= 0) { set_error("plr2_refiner_backward: bad shape"); return PLR2_E_SHAPE; }
+  if (!packed || !x || !obj || !g_pred_r || !g_pred_t || !packed_grad) { set_error("plr2_refiner_backward: null pointer"); return PLR2_E_NULLPTR; }
+  const NetLayout L = make_layout(PLR2_NET_REFINER, num_obj);
+  NetWorkspace W;
+  RC(check_ws(L, workspace, workspace_bytes, frames, n_points, 1, W));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int F = frames, N = n_points;
+  const float *pk = packed;
+  float *gp = packed_grad;
+  cudaError_t e = cudaMemsetAsync(gp, 0, L.total * sizeof(float), st);
+  if (e != cudaSuccess) { set_error("plr2_refiner_backward: memset: %s", cudaGetErrorString(e)); return (int)e; }
+  RC(select_outputs_bwd(W.out, L, obj, 1, (size_t)F, g_pred_r, g_pred_t, nullptr, st));
+  size_t row = 0;
+  for (int h = 0; h < 2; ++h) {               // conv3_{r,t}
+    RC(gemm_f32(gemm_tn(W.out + L.oc[h], L.ldo, W.h2 + h * 128, 256, gp + L.h4w + row * 128, 128, L.on[h], 128, F), 1, st));
+    RC(bgrad(W.out + L.oc[h], L.ldo, F, L.on[h], gp + L.h4b + row, st));
+    GemmArgs g = gemm_nn(W.out + L.oc[h], L.ldo, pk + L.h4w + row * 128, 128, W.h2 + h * 128, 256, F, 128, L.on[h]);
+    g.relu_mask = W.h2 + h * 128; g.ldmask = 256;
+    RC(gemm_f32(g, 1, st));
+    row += L.on[h];
+  }
+  GemmArgs g = gemm_tn(W.h2, 256, W.h1, 1024, gp + L.h2w, 512, 128, 512, F);      // conv2_{r,t}
+  g.batch = 2; g.zA = 128; g.zB = 512; g.zC = 128 * 512;
+  RC(gemm_f32(g, 1, st));
+  RC(bgrad(W.h2, 256, F, 256, gp + L.h2b, st));
+  g = gemm_nn(W.h2, 256, pk + L.h2w, 512, W.h1, 1024, F, 512, 128);
+  g.batch = 2; g.zA = 128; g.zB = 128 * 512; g.zC = 512; g.relu_mask = W.h1; g.ldmask = 1024; g.zmask = 512;
+  RC(gemm_f32(g, 1, st));
+  RC(gemm_f32(gemm_tn(W.h1, 1024, W.ap, 1024, gp + L.h1ap, 1024, 1024, 1024, F), 1, st));   // conv1_{r,t}
+  RC(bgrad(W.h1, 1024, F, 1024, gp + L.h1b, st));
+  RC(gemm_f32(gemm_nn(W.h1, 1024, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1024), 1, st));
+  RC(feat_backward(pk, gp, L, W, x, F, N, false, st));
+  return 0;
+}

@@ -132,3 +132,181 @@ class RefineLossFn(torch.autograd.Function):
         jac_r, jac_t = ctx.saved_tensors
         g = g_dis.reshape(-1, 1).to(torch.float32)
         return ((g * jac_r).reshape(ctx.shapes[0]), (g * jac_t).reshape(ctx.shapes[1]), None, None, None, None, None, None)
+
+
+# ------------------------------------------------------------------------------------------------
+# PoseNet / PoseRefineNet hot path
+NET_POSENET, NET_REFINER = 0, 1
+PREC_FP32, PREC_BF16X2 = 0, 1
+
+POSENET_LAYER_NAMES = (["feat.conv1", "feat.e_conv1", "feat.conv2", "feat.e_conv2", "feat.conv5", "feat.conv6"]
+                       + [f"conv{i}_{h}" for i in (1, 2, 3, 4) for h in "rtc"])
+REFINER_LAYER_NAMES = (["feat.conv1", "feat.e_conv1", "feat.conv2", "feat.e_conv2", "feat.conv5", "feat.conv6"]
+                       + [f"conv{i}_{h}" for i in (1, 2, 3) for h in "rt"])
+
+
+def _param_table(tensors):
+    """tensors: list of (weight, bias) CUDA tensors in the C-ABI layer order."""
+    t = _cabi.ParamTable()
+    for i, (w, b) in enumerate(tensors):
+        assert w.is_contiguous() and b.is_contiguous() and w.dtype == torch.float32
+        t.w[i] = w.data_ptr()
+        t.b[i] = b.data_ptr()
+    return t
+
+
+class NetState:
+    """Per-module device state: packed (and optionally TF32-rounded) weights, re-packed whenever a
+    parameter's version counter or storage changes; a reusable inference workspace."""
+
+    def __init__(self, net, num_obj):
+        self.net, self.num_obj = net, num_obj
+        self.packed = None
+        self.key = None
+        self.ws = None
+
+    def packed_for(self, params, precision):
+        dev = params[0].device
+        key = (str(dev), precision) + tuple((p.data_ptr(), p._version) for p in params)
+        if key != self.key:
+            L = _cabi.lib()
+            n = L.plr2_net_packed_floats(self.net, self.num_obj)
+            if self.packed is None or self.packed.device != dev or self.packed.numel() != n:
+                self.packed = torch.empty(n, dtype=torch.float32, device=dev)
+            pairs = [(params[2 * i].detach(), params[2 * i + 1].detach()) for i in range(len(params) // 2)]
+            pairs = [(w.contiguous(), b.contiguous()) for w, b in pairs]
+            with torch.cuda.device(dev):
+                rc = L.plr2_net_pack(self.net, _param_table(pairs), self.num_obj, _cabi.ptr(self.packed),
+                                     1 if precision == PREC_BF16X2 else 0, _cabi.stream_ptr(dev))
+            _cabi.check(rc, "plr2_net_pack")
+            self.key = key
+        return self.packed
+
+    def workspace(self, frames, n_points, training, dev):
+        nbytes = _cabi.lib().plr2_net_workspace_bytes(self.net, frames, n_points, self.num_obj, int(training))
+        if training:      # activations must survive until backward: one buffer per forward
+            return torch.empty(nbytes, dtype=torch.uint8, device=dev), nbytes
+        if self.ws is None or self.ws.device != dev or self.ws.numel() < nbytes:
+            self.ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        return self.ws, nbytes
+
+
+def _unpack_grads(net, num_obj, gpacked, params, dev):
+    sizes = [p.numel() for p in params]
+    flat = torch.empty(sum(sizes), dtype=torch.float32, device=dev)
+    views, o = [], 0
+    for p, n in zip(params, sizes):
+        views.append(flat[o:o + n].view(p.shape))
+        o += n
+    pairs = [(views[2 * i], views[2 * i + 1]) for i in range(len(views) // 2)]
+    with torch.cuda.device(dev):
+        rc = _cabi.lib().plr2_net_unpack_grads(net, _cabi.ptr(gpacked), _param_table(pairs), num_obj,
+                                               _cabi.stream_ptr(dev))
+    _cabi.check(rc, "plr2_net_unpack_grads")
+    return views
+
+
+class PoseNetFn(torch.autograd.Function):
+    """PoseNet.forward minus the backbone (lib/network.py:98-132) for F frames.
+    out_img (F,32,H,W), x (F,N,3), choose (F,1,N)|(F,N) i64, obj (F,1)|(F,) i64, then the 36 parameters
+    -> pred_r (F,N,4), pred_t (F,N,3), pred_c (F,N,1), emb (F,32,N)."""
+
+    @staticmethod
+    def forward(ctx, state, precision, out_img, x, choose, obj, *params):
+        _need_cuda(out_img, "PoseNetFn")
+        dev = out_img.device
+        F, C, H, Wd = out_img.shape
+        N = x.shape[1]
+        assert C == 32, "the PSPNet backbone emits 32 channels (lib/pspnet.py:53-56)"
+        oi, xs = _f32c(out_img), _f32c(x)
+        ch = choose.detach().reshape(F, N).to(torch.int64).contiguous()
+        ob = obj.detach().reshape(F).to(torch.int64).contiguous()
+        training = any(ctx.needs_input_grad)
+        packed = state.packed_for(params, precision)
+        ws, nbytes = state.workspace(F, N, training, dev)
+        pred_r = torch.empty((F, N, 4), dtype=torch.float32, device=dev)
+        pred_t = torch.empty((F, N, 3), dtype=torch.float32, device=dev)
+        pred_c = torch.empty((F, N, 1), dtype=torch.float32, device=dev)
+        emb = torch.empty((F, 32, N), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = _cabi.lib().plr2_posenet_forward(
+                _cabi.ptr(packed), _cabi.ptr(oi), _cabi.ptr(ch), _cabi.ptr(xs), _cabi.ptr(ob), F, N, H * Wd,
+                state.num_obj, _cabi.ptr(ws), nbytes, _cabi.ptr(pred_r), _cabi.ptr(pred_t), _cabi.ptr(pred_c),
+                _cabi.ptr(emb), int(training), precision, _cabi.stream_ptr(dev))
+        _cabi.check(rc, "plr2_posenet_forward")
+        if training:
+            ctx.state, ctx.precision = state, precision
+            ctx.saved = (packed.clone() if False else packed, ws, nbytes, ch, xs, ob, (F, N, H, Wd))
+            ctx.params = params
+            ctx.packed_key = state.key
+        ctx.mark_non_differentiable(emb)
+        return pred_r, pred_t, pred_c, emb
+
+    @staticmethod
+    def backward(ctx, g_r, g_t, g_c, _g_emb):
+        packed, ws, nbytes, ch, xs, ob, (F, N, H, Wd) = ctx.saved
+        state = ctx.state
+        if state.key != ctx.packed_key:     # parameters changed between forward and backward
+            packed = state.packed_for(ctx.params, ctx.precision)
+        dev = xs.device
+        gp = torch.empty(packed.numel() // 2, dtype=torch.float32, device=dev)
+        g_img = torch.zeros((F, 32, H, Wd), dtype=torch.float32, device=dev) if ctx.needs_input_grad[2] else None
+        z = lambda g, shp: _f32c(g) if g is not None else torch.zeros(shp, dtype=torch.float32, device=dev)
+        g_r, g_t, g_c = z(g_r, (F, N, 4)), z(g_t, (F, N, 3)), z(g_c, (F, N, 1))
+        with torch.cuda.device(dev):
+            rc = _cabi.lib().plr2_posenet_backward(
+                _cabi.ptr(packed), _cabi.ptr(ch), _cabi.ptr(xs), _cabi.ptr(ob), F, N, H * Wd, state.num_obj,
+                _cabi.ptr(ws), nbytes, _cabi.ptr(g_r), _cabi.ptr(g_t), _cabi.ptr(g_c), _cabi.ptr(gp),
+                _cabi.ptr(g_img), ctx.precision, _cabi.stream_ptr(dev))
+        _cabi.check(rc, "plr2_posenet_backward")
+        grads = _unpack_grads(NET_POSENET, state.num_obj, gp, ctx.params, dev)
+        ctx.saved = None
+        return (None, None, g_img, None, None, None) + tuple(grads)
+
+
+class RefinerFn(torch.autograd.Function):
+    """PoseRefineNet.forward (lib/network.py:187-206) for F frames: x (F,N,3), emb (F,32,N), obj
+    -> pred_r (F,4), pred_t (F,3)."""
+
+    @staticmethod
+    def forward(ctx, state, precision, x, emb, obj, *params):
+        _need_cuda(x, "RefinerFn")
+        dev = x.device
+        F, N = x.shape[0], x.shape[1]
+        xs, em = _f32c(x), _f32c(emb)
+        ob = obj.detach().reshape(F).to(torch.int64).contiguous()
+        training = any(ctx.needs_input_grad)
+        packed = state.packed_for(params, precision)
+        ws, nbytes = state.workspace(F, N, training, dev)
+        pred_r = torch.empty((F, 4), dtype=torch.float32, device=dev)
+        pred_t = torch.empty((F, 3), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = _cabi.lib().plr2_refiner_forward(
+                _cabi.ptr(packed), _cabi.ptr(xs), _cabi.ptr(em), _cabi.ptr(ob), F, N, state.num_obj,
+                _cabi.ptr(ws), nbytes, _cabi.ptr(pred_r), _cabi.ptr(pred_t), int(training), precision,
+                _cabi.stream_ptr(dev))
+        _cabi.check(rc, "plr2_refiner_forward")
+        if training:
+            ctx.state, ctx.precision, ctx.params, ctx.packed_key = state, precision, params, state.key
+            ctx.saved = (packed, ws, nbytes, xs, em, ob, (F, N))
+        return pred_r, pred_t
+
+    @staticmethod
+    def backward(ctx, g_r, g_t):
+        packed, ws, nbytes, xs, em, ob, (F, N) = ctx.saved
+        state = ctx.state
+        if state.key != ctx.packed_key:
+            packed = state.packed_for(ctx.params, ctx.precision)
+        dev = xs.device
+        gp = torch.empty(packed.numel() // 2, dtype=torch.float32, device=dev)
+        g_r = _f32c(g_r) if g_r is not None else torch.zeros((F, 4), dtype=torch.float32, device=dev)
+        g_t = _f32c(g_t) if g_t is not None else torch.zeros((F, 3), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = _cabi.lib().plr2_refiner_backward(
+                _cabi.ptr(packed), _cabi.ptr(xs), _cabi.ptr(em), _cabi.ptr(ob), F, N, state.num_obj,
+                _cabi.ptr(ws), nbytes, _cabi.ptr(g_r), _cabi.ptr(g_t), _cabi.ptr(gp), ctx.precision,
+                _cabi.stream_ptr(dev))
+        _cabi.check(rc, "plr2_refiner_backward")
+        grads = _unpack_grads(NET_REFINER, state.num_obj, gp, ctx.params, dev)
+        ctx.saved = None
+        return (None, None, None, None, None) + tuple(grads)

@@ -1,0 +1,191 @@
+"""GPU: kernels (1)+(2) — PoseNet / PoseRefineNet drop-ins (forward and backward) against the
+reference's golden outputs and the oracle, plus the GEMM entry point against numpy."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import densefusion_oracle as DO
+from plr2_b200 import _cabi, ops, synth
+from plr2_b200.lib.loss import Loss
+from plr2_b200.lib.loss_refiner import Loss_refine
+from plr2_b200.lib.network import PoseNet, PoseRefineNet
+from tests.util import assert_close, load_golden, shape_of, tt
+
+pytestmark = pytest.mark.gpu
+
+
+def build_posenet(shp, seed, precision):
+    net = PoseNet(shp.num_points, shp.num_obj, precision=precision)
+    net.cnn = torch.nn.Identity()        # the `img` argument then carries the backbone output
+    net.load_state_dict({k: tt(v) for k, v in synth.make_params("posenet", shp.num_obj, seed).items()}, strict=False)
+    return net.cuda()
+
+
+def build_refiner(shp, seed, precision):
+    net = PoseRefineNet(shp.num_points, shp.num_obj, precision=precision)
+    net.load_state_dict({k: tt(v) for k, v in synth.make_params("refiner", shp.num_obj, seed).items()})
+    return net.cuda()
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K,layout", [(1, 1, 1, "nt"), (130, 70, 33, "nt"), (257, 129, 64, "nt"),
+                                          (1000, 640, 384, "nt"), (300, 96, 200, "nn"), (77, 130, 1000, "tn"),
+                                          (128, 256, 4096, "tn_split"), (5, 1920, 1024, "nt")])
+def test_gemm_f32_layouts_and_epilogues(M, N, K, layout):
+    rng = np.random.default_rng(M * 3 + N * 5 + K)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    B = rng.standard_normal((K, N)).astype(np.float32)
+    bias = rng.standard_normal(N).astype(np.float32)
+    d = _cabi.GemmDesc()
+    keep = []
+
+    def dev(a):
+        t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        keep.append(t)
+        return t
+
+    if layout == "nt":       # A [M,K] k-contig, W [N,K] k-contig
+        a, b = dev(A), dev(B.T)
+        d.A, d.sam, d.sak, d.B, d.sbk, d.sbn = a.data_ptr(), K, 1, b.data_ptr(), 1, K
+    elif layout == "nn":     # A [M,K], B [K,N] n-contig
+        a, b = dev(A), dev(B)
+        d.A, d.sam, d.sak, d.B, d.sbk, d.sbn = a.data_ptr(), K, 1, b.data_ptr(), N, 1
+    else:                    # A stored [K,M] m-contig, B [K,N]
+        a, b = dev(A.T), dev(B)
+        d.A, d.sam, d.sak, d.B, d.sbk, d.sbn = a.data_ptr(), 1, M, b.data_ptr(), N, 1
+    C0 = rng.standard_normal((M, N)).astype(np.float32)
+    c = dev(C0)
+    d.C, d.ldc, d.M, d.N, d.K = c.data_ptr(), N, M, N, K
+    want = A.astype(np.float64) @ B.astype(np.float64)
+    if layout == "tn_split":
+        d.accumulate, d.split_k = 1, 7
+        want = want + C0
+    elif layout == "tn":
+        d.accumulate = 1
+        want = want + C0
+    else:
+        d.bias, d.relu = dev(bias).data_ptr(), 1
+        want = np.maximum(want + bias, 0)
+    rc = _cabi.lib().plr2_gemm_f32(ctypes.byref(d), torch.cuda.current_stream().cuda_stream)
+    _cabi.check(rc, "plr2_gemm_f32")
+    torch.cuda.synchronize()
+    assert_close(c.cpu().numpy(), want, "gemm", rtol=1e-4, atol=1e-4 * np.sqrt(K), frac=1.0)
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["posenet_linemod_nonsym", "posenet_ycb_sym", "posenet_ycb_refine"])
+@pytest.mark.parametrize("precision", [ops.PREC_FP32, ops.PREC_BF16X2])
+def test_posenet_forward_backward_matches_reference_golden(name, precision):
+    g = load_golden(name)
+    shp = shape_of(g)
+    net = build_posenet(shp, int(g["seed"]), precision)
+    fr = synth.make_frame(shp, int(g["seed"]) + 1, obj=int(g["obj"]))
+    img = tt(fr["out_img"], "cuda")[None]
+    points = tt(fr["points"], "cuda")[None]
+    choose = tt(fr["choose"], "cuda")[None, None]
+    idx = tt(fr["idx"], "cuda").reshape(1, 1)
+    pr, pt, pc, emb = net(img, points, choose, idx)
+    assert tuple(pr.shape) == (1, shp.num_points, 4) and tuple(pt.shape) == (1, shp.num_points, 3)
+    assert tuple(pc.shape) == (1, shp.num_points, 1) and tuple(emb.shape) == (1, 32, shp.num_points)
+    assert not emb.requires_grad
+    pr.retain_grad(); pt.retain_grad(); pc.retain_grad()
+    crit = Loss(shp.num_mesh, list(shp.sym_list))
+    loss, dis, npts, ntgt = crit(pr, pt, pc, tt(fr["target"], "cuda")[None], tt(fr["model_points"], "cuda")[None],
+                                 idx, points, float(g["w"]), bool(g["refine"]))
+    loss.backward()
+    c = lambda t: t.detach().cpu().numpy()
+    assert np.array_equal(c(emb), g["emb"])
+    assert_close(c(pr), g["pred_r"], "pred_r")
+    assert_close(c(pt), g["pred_t"], "pred_t")
+    assert_close(c(pc), g["pred_c"], "pred_c")
+    assert_close(c(loss), g["loss"], "loss", frac=1.0)
+    assert_close(c(dis), g["dis"], "dis", frac=1.0)
+    assert_close(c(npts), g["new_points"], "new_points")
+    assert_close(c(ntgt), g["new_target"], "new_target")
+    for k, p in net.named_parameters():
+        assert p.grad is not None, k
+        assert_close(p.grad.norm().item(), g["gnorm." + k], "gnorm." + k, rtol=2e-3, frac=1.0)
+        assert_close(c(p.grad).reshape(-1)[::97], g["gsub." + k], "gsub." + k)
+
+
+@pytest.mark.parametrize("name", ["refiner_ycb_sym", "refiner_ycb_nonsym"])
+@pytest.mark.parametrize("precision", [ops.PREC_FP32, ops.PREC_BF16X2])
+def test_refiner_chain_matches_reference_golden(name, precision):
+    g = load_golden(name)
+    shp = shape_of(g)
+    net = build_refiner(shp, int(g["seed"]), precision)
+    fr = synth.make_frame(shp, int(g["seed"]) + 1, obj=int(g["obj"]))
+    emb = tt(fr["out_img"].reshape(32, -1)[:, fr["choose"]], "cuda")[None]
+    crit = Loss_refine(shp.num_mesh, list(shp.sym_list))
+    idx = tt(fr["idx"], "cuda").reshape(1, 1)
+    pts, tgt = tt(g["in_points"], "cuda")[None], tt(g["in_target"], "cuda")[None]
+    c = lambda t: t.detach().cpu().numpy()
+    for ite in range(2):       # tools/train.py:141-145
+        pr, pt = net(pts, emb, idx)
+        assert tuple(pr.shape) == (1, 4) and tuple(pt.shape) == (1, 3)
+        dis, pts, tgt = crit(pr, pt, tgt, tt(fr["model_points"], "cuda")[None], idx, pts)
+        dis.backward()
+        assert_close(c(pr), g[f"it{ite}.pred_r"], "pred_r", frac=1.0)
+        assert_close(c(pt), g[f"it{ite}.pred_t"], "pred_t", frac=1.0)
+        assert_close(c(dis), g[f"it{ite}.dis"], "dis", frac=1.0, rtol=2e-3)
+        assert_close(c(pts), g[f"it{ite}.new_points"], "new_points", rtol=2e-3)
+        assert_close(c(tgt), g[f"it{ite}.new_target"], "new_target", rtol=2e-3)
+    for k, p in net.named_parameters():      # accumulated over both iterations
+        assert_close(p.grad.norm().item(), g["gnorm." + k], "gnorm." + k, rtol=5e-3, frac=1.0)
+
+
+@pytest.mark.parametrize("shape,obj", [(synth.LINEMOD, 3), (synth.YCB, 12)])
+def test_posenet_full_size_vs_oracle(shape, obj):
+    """BASELINE configs C1 / C2 at full size (N = 500 / 1000): forward + loss + all gradients."""
+    net = build_posenet(shape, 31, ops.PREC_FP32)
+    fr = synth.make_frame(shape, 32, obj=obj)
+    img = tt(fr["out_img"], "cuda", grad=True)
+    points, choose = tt(fr["points"], "cuda")[None], tt(fr["choose"], "cuda")[None, None]
+    idx = tt(fr["idx"], "cuda").reshape(1, 1)
+    pr, pt, pc, emb = net(img[None], points, choose, idx)
+    crit = Loss(shape.num_mesh, list(shape.sym_list))
+    loss, dis, _, _ = crit(pr, pt, pc, tt(fr["target"], "cuda")[None], tt(fr["model_points"], "cuda")[None], idx,
+                           points, 0.015, False)
+    loss.backward()
+    p = {k: tt(v, grad=True) for k, v in synth.make_params("posenet", shape.num_obj, 31).items()}
+    oimg = tt(fr["out_img"], grad=True)
+    opr, opt_, opc, oemb = DO.posenet_forward(p, oimg, tt(fr["points"]), tt(fr["choose"]), obj, shape.num_obj)
+    ol, od, _, _, _ = DO.pose_loss(opr, opt_, opc, tt(fr["target"]), tt(fr["model_points"]), obj, tt(fr["points"]),
+                                   0.015, False, shape.sym_list)
+    ol.backward()
+    c = lambda t: t.detach().cpu().numpy()
+    assert_close(c(pr)[0], c(opr), "pred_r")
+    assert_close(c(pt)[0], c(opt_), "pred_t")
+    assert_close(c(pc)[0], c(opc), "pred_c")
+    assert_close(c(loss), ol.item(), "loss", frac=1.0)
+    assert_close(c(img.grad), c(oimg.grad), "g_out_img", frac=0.99)
+    for k, v in net.named_parameters():
+        assert_close(c(v.grad), c(p[k].grad), "grad " + k)
+
+
+def test_batched_frames_equal_single_frame_calls():
+    shp = synth.Shape(200, 21, 100, 24, 24, tuple(synth.YCB_SYM))
+    net = build_posenet(shp, 5, ops.PREC_FP32)
+    frs = [synth.make_frame(shp, 60 + i) for i in range(4)]
+    st = lambda key: tt(np.stack([f[key] for f in frs]), "cuda")
+    with torch.no_grad():
+        pr, pt, pc, emb = net(st("out_img"), st("points"), st("choose")[:, None], st("idx")[:, None])
+        for i in range(4):
+            a = net(st("out_img")[i:i + 1], st("points")[i:i + 1], st("choose")[i:i + 1, None], st("idx")[i:i + 1, None])
+            for x, y in zip(a, (pr, pt, pc, emb)):
+                assert torch.equal(x[0], y[i])
+
+
+def test_weight_update_is_picked_up():
+    shp = synth.Shape(64, 13, 50, 16, 16, tuple(synth.LINEMOD_SYM))
+    net = build_posenet(shp, 7, ops.PREC_FP32)
+    fr = synth.make_frame(shp, 8)
+    args = (tt(fr["out_img"], "cuda")[None], tt(fr["points"], "cuda")[None], tt(fr["choose"], "cuda")[None, None],
+            tt(fr["idx"], "cuda").reshape(1, 1))
+    with torch.no_grad():
+        a = net(*args)[0].clone()
+        net.conv4_r.bias.add_(1.0)
+        b = net(*args)[0]
+    assert torch.allclose(b, a + 1.0, atol=1e-5)
