@@ -86,4 +86,41 @@ inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, 
   return W;
 }
 
+
+// Workspace of the tensor-core (split-bf16) inference path.  Activations consumed by tcgen05 layers
+// are stored as two bf16 planes [2][R][width]; *_plane is the plane stride in elements.
+struct TcWorkspace {
+  void *pf, *x5, *h1, *h2;                 // bf16 planes
+  long long pf_plane, x5_plane, h1_plane, h2_plane;
+  float *pool, *ap, *hb, *h3, *out;        // fp32; refiner: hb = l1 out, h3 = l2 out
+  size_t bytes;
+};
+
+inline TcWorkspace carve_tc_workspace(const NetLayout &L, void *base, int frames, int n_points) {
+  TcWorkspace W{};
+  const size_t R = (size_t)frames * n_points, F = frames;
+  const bool pn = L.net == PLR2_NET_POSENET;
+  uint8_t *p = reinterpret_cast<uint8_t *>(base);
+  size_t o = 0;
+  auto take = [&](size_t nbytes) { void *r = p ? p + o : nullptr; o += (nbytes + 127) / 128 * 128; return r; };
+  const size_t h1all = (size_t)L.heads * L.h1n, h2all = (size_t)L.heads * L.h2n, h3all = (size_t)L.heads * L.h3n;
+  W.pf = take(2 * R * 384 * 2); W.pf_plane = (long long)R * 384;
+  W.x5 = take(2 * R * 512 * 2); W.x5_plane = (long long)R * 512;
+  W.pool = (float *)take(((R + 31) / 32) * 2 * 1024 * sizeof(float));
+  W.ap = (float *)take(F * 1024 * sizeof(float));
+  if (pn) {
+    W.hb = (float *)take(F * h1all * sizeof(float));
+    W.h1 = take(2 * R * h1all * 2); W.h1_plane = (long long)R * h1all;
+    W.h2 = take(2 * R * h2all * 2); W.h2_plane = (long long)R * h2all;
+    W.h3 = (float *)take(R * h3all * sizeof(float));
+    W.out = (float *)take(R * L.ldo * sizeof(float));
+  } else {
+    W.hb = (float *)take(F * h1all * sizeof(float));
+    W.h3 = (float *)take(F * h2all * sizeof(float));
+    W.out = (float *)take(F * L.ldo * sizeof(float));
+  }
+  W.bytes = o;
+  return W;
+}
+
 }  // namespace plr2

@@ -16,12 +16,14 @@ namespace plr2 {
 // point-major feature buffer pf (ld 384).
 constexpr int FL_THREADS = 128;
 
+template <bool OUT_BF16>
 __global__ void __launch_bounds__(FL_THREADS)
 first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
                    const float *__restrict__ e1w, const float *__restrict__ e1b,
                    const float *__restrict__ out_img, const int64_t *__restrict__ choose,
                    const float *__restrict__ emb_in, const float *__restrict__ x, int N, int hw,
-                   float *__restrict__ pf, float *__restrict__ emb_out, float *__restrict__ embT) {
+                   float *__restrict__ pf, __nv_bfloat16 *__restrict__ pfb, long long pf_plane,
+                   float *__restrict__ emb_out, float *__restrict__ embT) {
   __shared__ __align__(16) float sw1[64 * 4];
   __shared__ __align__(16) float swe[64 * 32];
   __shared__ float sb1[64], sbe[64];
@@ -56,34 +58,49 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
     for (int q = 0; q < 8; ++q) dst[q] = make_float4(e[4 * q], e[4 * q + 1], e[4 * q + 2], e[4 * q + 3]);
   }
   const float px = x[row * 3], py = x[row * 3 + 1], pz = x[row * 3 + 2];
-  float4 *prow = reinterpret_cast<float4 *>(pf + row * 384);
-#pragma unroll 2
-  for (int o4 = 0; o4 < 16; ++o4) {
-    float v[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int o = o4 * 4 + j;
-      const float4 w = *reinterpret_cast<const float4 *>(sw1 + o * 4);
-      v[j] = fmaxf(fmaf(w.z, pz, fmaf(w.y, py, fmaf(w.x, px, sb1[o]))), 0.f);
-    }
-    prow[o4] = make_float4(v[0], v[1], v[2], v[3]);
-  }
+  // 8 outputs at a time: conv1 (o < 64) then e_conv1 (o >= 64)
 #pragma unroll 1
-  for (int o4 = 0; o4 < 16; ++o4) {
-    float v[4];
+  for (int o8 = 0; o8 < 16; ++o8) {
+    float v[8];
+    if (o8 < 8) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int o = o4 * 4 + j;
-      float acc = sbe[o];
-#pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const float4 w = *reinterpret_cast<const float4 *>(swe + o * 32 + q * 4);
-        acc = fmaf(w.x, e[4 * q], acc); acc = fmaf(w.y, e[4 * q + 1], acc);
-        acc = fmaf(w.z, e[4 * q + 2], acc); acc = fmaf(w.w, e[4 * q + 3], acc);
+      for (int j = 0; j < 8; ++j) {
+        const int o = o8 * 8 + j;
+        const float4 w = *reinterpret_cast<const float4 *>(sw1 + o * 4);
+        v[j] = fmaxf(fmaf(w.z, pz, fmaf(w.y, py, fmaf(w.x, px, sb1[o]))), 0.f);
       }
-      v[j] = fmaxf(acc, 0.f);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int o = (o8 - 8) * 8 + j;
+        float acc = sbe[o];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 w = *reinterpret_cast<const float4 *>(swe + o * 32 + q * 4);
+          acc = fmaf(w.x, e[4 * q], acc); acc = fmaf(w.y, e[4 * q + 1], acc);
+          acc = fmaf(w.z, e[4 * q + 2], acc); acc = fmaf(w.w, e[4 * q + 3], acc);
+        }
+        v[j] = fmaxf(acc, 0.f);
+      }
     }
-    prow[16 + o4] = make_float4(v[0], v[1], v[2], v[3]);
+    if (OUT_BF16) {
+      uint32_t hi[4], lo[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * q]), h1 = __float2bfloat16_rn(v[2 * q + 1]);
+        const __nv_bfloat16 l0 = __float2bfloat16_rn(v[2 * q] - __bfloat162float(h0));
+        const __nv_bfloat16 l1 = __float2bfloat16_rn(v[2 * q + 1] - __bfloat162float(h1));
+        hi[q] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+        lo[q] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+      }
+      __nv_bfloat16 *d = pfb + row * 384 + o8 * 8;
+      *reinterpret_cast<uint4 *>(d) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      *reinterpret_cast<uint4 *>(d + pf_plane) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    } else {
+      float4 *d = reinterpret_cast<float4 *>(pf + row * 384 + o8 * 8);
+      d[0] = make_float4(v[0], v[1], v[2], v[3]);
+      d[1] = make_float4(v[4], v[5], v[6], v[7]);
+    }
   }
 }
 
@@ -91,9 +108,20 @@ int first_layer(const float *packed, const NetLayout &L, const float *out_img, c
                 const float *emb_in, const float *x, int frames, int N, int hw, float *pf, float *emb_out,
                 float *embT, cudaStream_t st) {
   dim3 grid((N + FL_THREADS - 1) / FL_THREADS, frames);
-  first_layer_kernel<<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
-                                                  out_img, choose, emb_in, x, N, hw, pf, emb_out, embT);
+  first_layer_kernel<false><<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
+                                                         out_img, choose, emb_in, x, N, hw, pf, nullptr, 0, emb_out, embT);
   return check_launch("first_layer");
+}
+
+// same, writing the split-bf16 planes consumed by the tensor-core layers
+int first_layer_bf16(const float *packed, const NetLayout &L, const float *out_img, const int64_t *choose,
+                     const float *emb_in, const float *x, int frames, int N, int hw, __nv_bfloat16 *pfb,
+                     long long pf_plane, float *emb_out, cudaStream_t st) {
+  dim3 grid((N + FL_THREADS - 1) / FL_THREADS, frames);
+  first_layer_kernel<true><<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
+                                                        out_img, choose, emb_in, x, N, hw, nullptr, pfb, pf_plane, emb_out,
+                                                        nullptr);
+  return check_launch("first_layer_bf16");
 }
 
 // d out_img[f][c][choose[f][n]] += demb[row][c]  (duplicates in choose accumulate)

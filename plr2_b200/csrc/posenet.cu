@@ -9,6 +9,7 @@
 // Algebraic hoist: the 1024 global-feature inputs of conv1_{r,t,c} are constant per
 // frame, so they enter as a per-frame bias hb = W1[:,384:] ap + b1 instead of 1024 extra K per point.
 #include "gemm.cuh"
+#include "gemm_tc.cuh"
 #include "pointnet.cuh"
 
 namespace plr2 {
@@ -51,6 +52,111 @@ static int feat_forward(const float *pk, const NetLayout &L, const NetWorkspace 
   g.bias = pk + L.c6b; g.relu = 1;
   RC(gemm_any(g, precision, st));
   RC(segment_colsum(W.x6, 1024, F, N, 1024, 1.0f / (float)N, W.ap, 1024, st));    // AvgPool1d(num_points)
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tensor-core inference path (PLR2_PREC_BF16X2, no activations kept for backward).
+static bool use_tc(int precision, int training, int n_points) {
+  return precision == PLR2_PREC_BF16X2 && !training && n_points >= 32;
+}
+
+static int check_tc_ws(const NetLayout &L, void *ws, size_t bytes, int frames, int n, TcWorkspace &W) {
+  if (!ws) { set_error("network: workspace is NULL"); return PLR2_E_NULLPTR; }
+  if (reinterpret_cast<uintptr_t>(ws) & 127) { set_error("network: workspace must be 128-byte aligned"); return PLR2_E_ALIGN; }
+  W = carve_tc_workspace(L, ws, frames, n);
+  if (W.bytes > bytes) { set_error("network: workspace too small (%zu < %zu bytes)", bytes, W.bytes); return PLR2_E_WORKSPACE; }
+  return 0;
+}
+
+// first layer, conv2/e_conv2, conv5, conv6 + fused per-frame average pooling -> W.ap [F,1024]
+static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspace &W, const float *out_img,
+                           const int64_t *choose, const float *emb_in, const float *x, int F, int N, int hw,
+                           float *emb_out, cudaStream_t st) {
+  const int R = F * N;
+  const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);   // split-bf16 weights
+  const long long wplane = (long long)L.total;
+  __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *x5 = (__nv_bfloat16 *)W.x5;
+  RC(first_layer_bf16(pk, L, out_img, choose, emb_in, x, F, N, hw, pf, W.pf_plane, emb_out, st));
+  TcGemm g;
+  g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.c2w; g.ldw = 64; g.w_plane = wplane;
+  g.M = R; g.N = 128; g.K = 64; g.bias = pk + L.c2b; g.relu = 1;
+  g.out_mode = TC_OUT_BF16X2; g.Cb = pf + 128; g.ldcb = 384; g.c_plane = W.pf_plane;
+  RC(gemm_bf16x2(g, st));                                                            // conv2
+  g.A = pf + 64; g.W = wb + L.e2w; g.bias = pk + L.e2b; g.Cb = pf + 256;
+  RC(gemm_bf16x2(g, st));                                                            // e_conv2
+  g = TcGemm();
+  g.A = L.c5k == 256 ? pf + 128 : pf; g.lda = 384; g.a_plane = W.pf_plane;
+  g.W = wb + L.c5w; g.ldw = L.c5k; g.w_plane = wplane;
+  g.M = R; g.N = 512; g.K = L.c5k; g.bias = pk + L.c5b; g.relu = 1;
+  g.out_mode = TC_OUT_BF16X2; g.Cb = x5; g.ldcb = 512; g.c_plane = W.x5_plane;
+  RC(gemm_bf16x2(g, st));                                                            // conv5
+  g = TcGemm();
+  g.A = x5; g.lda = 512; g.a_plane = W.x5_plane; g.W = wb + L.c6w; g.ldw = 512; g.w_plane = wplane;
+  g.M = R; g.N = 1024; g.K = 512; g.bias = pk + L.c6b; g.relu = 1;
+  g.out_mode = TC_OUT_POOL; g.pool = W.pool; g.rows_per_frame = N;
+  RC(gemm_bf16x2(g, st));                                                            // conv6 + AvgPool partials
+  RC(pool_finish(W.pool, F, N, R, 1024, W.ap, st));
+  return 0;
+}
+
+static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorkspace &W, const float *out_img,
+                              const int64_t *choose, const float *x, const int64_t *obj, int F, int N, int hw,
+                              float *pred_r, float *pred_t, float *pred_c, float *emb, cudaStream_t st) {
+  const int R = F * N;
+  const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);
+  const long long wplane = (long long)L.total;
+  __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *h1 = (__nv_bfloat16 *)W.h1, *h2 = (__nv_bfloat16 *)W.h2;
+  RC(feat_forward_tc(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, st));
+  GemmArgs s = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.hb, 1920, F, 1920, 1024);     // per-frame bias (FP32)
+  s.bias = pk + L.h1b;
+  RC(gemm_f32(s, 1, st));
+  TcGemm g;
+  g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.h1pf; g.ldw = 384; g.w_plane = wplane;
+  g.M = R; g.N = 1920; g.K = 384; g.frame_bias = W.hb; g.rows_per_frame = N; g.ldfb = 1920; g.relu = 1;
+  g.out_mode = TC_OUT_BF16X2; g.Cb = h1; g.ldcb = 1920; g.c_plane = W.h1_plane;
+  RC(gemm_bf16x2(g, st));                                                            // conv1_{r,t,c}
+  g = TcGemm();
+  g.A = h1; g.lda = 1920; g.a_plane = W.h1_plane; g.W = wb + L.h2w; g.ldw = 640; g.w_plane = wplane;
+  g.M = R; g.N = 256; g.K = 640; g.batch = 3; g.a_col_z = 640; g.b_row_z = 256; g.c_col_z = 256; g.bias_z = 256;
+  g.bias = pk + L.h2b; g.relu = 1;
+  g.out_mode = TC_OUT_BF16X2; g.Cb = h2; g.ldcb = 768; g.c_plane = W.h2_plane;
+  RC(gemm_bf16x2(g, st));                                                            // conv2_*
+  g = TcGemm();
+  g.A = h2; g.lda = 768; g.a_plane = W.h2_plane; g.W = wb + L.h3w; g.ldw = 256; g.w_plane = wplane;
+  g.M = R; g.N = 128; g.K = 256; g.batch = 3; g.a_col_z = 256; g.b_row_z = 128; g.c_col_z = 128; g.bias_z = 128;
+  g.bias = pk + L.h3b; g.relu = 1;
+  g.out_mode = TC_OUT_F32; g.Cf = W.h3; g.ldc = 384;
+  RC(gemm_bf16x2(g, st));                                                            // conv3_* (FP32 out)
+  size_t row = 0;
+  for (int h = 0; h < 3; ++h) {                                                      // conv4_* (FP32 SIMT)
+    GemmArgs c = gemm_nt(W.h3 + h * 128, 384, pk + L.h4w + row * 128, 128, W.out + L.oc[h], L.ldo, R, L.on[h], 128);
+    c.bias = pk + L.h4b + row;
+    RC(gemm_f32(c, 1, st));
+    row += L.on[h];
+  }
+  RC(select_outputs(W.out, L, obj, N, (size_t)R, pred_r, pred_t, pred_c, st));
+  return 0;
+}
+
+static int refiner_forward_tc(const float *pk, const NetLayout &L, const TcWorkspace &W, const float *x,
+                              const float *emb, const int64_t *obj, int F, int N, float *pred_r, float *pred_t,
+                              cudaStream_t st) {
+  RC(feat_forward_tc(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, st));
+  GemmArgs g = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.hb, 1024, F, 1024, 1024);
+  g.bias = pk + L.h1b; g.relu = 1;
+  RC(gemm_f32(g, 1, st));
+  g = gemm_nt(W.hb, 1024, pk + L.h2w, 512, W.h3, 256, F, 128, 512);
+  g.bias = pk + L.h2b; g.relu = 1; g.batch = 2; g.zA = 512; g.zB = 128 * 512; g.zC = 128; g.zbias = 128;
+  RC(gemm_f32(g, 1, st));
+  size_t row = 0;
+  for (int h = 0; h < 2; ++h) {
+    g = gemm_nt(W.h3 + h * 128, 256, pk + L.h4w + row * 128, 128, W.out + L.oc[h], L.ldo, F, L.on[h], 128);
+    g.bias = pk + L.h4b + row;
+    RC(gemm_f32(g, 1, st));
+    row += L.on[h];
+  }
+  RC(select_outputs(W.out, L, obj, 1, (size_t)F, pred_r, pred_t, nullptr, st));
   return 0;
 }
 
@@ -121,7 +227,9 @@ extern "C" size_t plr2_net_packed_floats(int net, int num_obj) { return 2 * make
 
 extern "C" size_t plr2_net_workspace_bytes(int net, int frames, int n_points, int num_obj, int training) {
   const NetLayout L = make_layout(net, num_obj);
-  return carve_workspace(L, nullptr, frames, n_points, training).floats * sizeof(float);
+  const size_t a = carve_workspace(L, nullptr, frames, n_points, training).floats * sizeof(float);
+  const size_t b = carve_tc_workspace(L, nullptr, frames, n_points).bytes;
+  return a > b ? a : b;
 }
 
 extern "C" int plr2_net_pack(int net, const plr2_param_table *params, int num_obj, float *packed, int split_bf16,
@@ -149,9 +257,14 @@ extern "C" int plr2_posenet_forward(const float *packed, const float *out_img, c
   if (!packed || !out_img || !choose || !x || !obj || !pred_r || !pred_t || !pred_c) { set_error("plr2_posenet_forward: null pointer"); return PLR2_E_NULLPTR; }
   if ((long long)frames * n_points > 0x7fffffffLL / 2048) { set_error("plr2_posenet_forward: too many rows per call"); return PLR2_E_SHAPE; }
   const NetLayout L = make_layout(PLR2_NET_POSENET, num_obj);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (use_tc(precision, training, n_points)) {
+    TcWorkspace T;
+    RC(check_tc_ws(L, workspace, workspace_bytes, frames, n_points, T));
+    return posenet_forward_tc(packed, L, T, out_img, choose, x, obj, frames, n_points, hw, pred_r, pred_t, pred_c, emb, st);
+  }
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));
-  cudaStream_t st = (cudaStream_t)stream;
   const int F = frames, N = n_points, R = F * N;
   const float *pk = packed;
   RC(feat_forward(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, training, precision, st));
@@ -192,9 +305,14 @@ extern "C" int plr2_refiner_forward(const float *packed, const float *x, const f
   if (!packed || !x || !emb || !obj || !pred_r || !pred_t) { set_error("plr2_refiner_forward: null pointer"); return PLR2_E_NULLPTR; }
   if ((long long)frames * n_points > 0x7fffffffLL / 2048) { set_error("plr2_refiner_forward: too many rows per call"); return PLR2_E_SHAPE; }
   const NetLayout L = make_layout(PLR2_NET_REFINER, num_obj);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (use_tc(precision, training, n_points)) {
+    TcWorkspace T;
+    RC(check_tc_ws(L, workspace, workspace_bytes, frames, n_points, T));
+    return refiner_forward_tc(packed, L, T, x, emb, obj, frames, n_points, pred_r, pred_t, st);
+  }
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));
-  cudaStream_t st = (cudaStream_t)stream;
   const int F = frames, N = n_points;
   const float *pk = packed;
   RC(feat_forward(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, training, precision, st));

@@ -189,3 +189,68 @@ def test_weight_update_is_picked_up():
         net.conv4_r.bias.add_(1.0)
         b = net(*args)[0]
     assert torch.allclose(b, a + 1.0, atol=1e-5)
+
+
+# ---------------------------------------------------------------------------------------------
+# tensor-core (tcgen05 split-bf16) inference path
+@pytest.mark.parametrize("name", ["posenet_linemod_nonsym", "posenet_ycb_sym", "posenet_ycb_refine"])
+def test_posenet_inference_tensor_core_matches_reference_golden(name):
+    g = load_golden(name)
+    shp = shape_of(g)
+    net = build_posenet(shp, int(g["seed"]), ops.PREC_BF16X2)
+    fr = synth.make_frame(shp, int(g["seed"]) + 1, obj=int(g["obj"]))
+    points = tt(fr["points"], "cuda")[None]
+    idx = tt(fr["idx"], "cuda").reshape(1, 1)
+    with torch.no_grad():
+        pr, pt, pc, emb = net(tt(fr["out_img"], "cuda")[None], points, tt(fr["choose"], "cuda")[None, None], idx)
+        crit = Loss(shp.num_mesh, list(shp.sym_list))
+        loss, dis, npts, ntgt = crit(pr, pt, pc, tt(fr["target"], "cuda")[None], tt(fr["model_points"], "cuda")[None],
+                                     idx, points, float(g["w"]), bool(g["refine"]))
+    c = lambda t: t.detach().cpu().numpy()
+    assert np.array_equal(c(emb), g["emb"])
+    assert_close(c(pr), g["pred_r"], "pred_r")
+    assert_close(c(pt), g["pred_t"], "pred_t")
+    assert_close(c(pc), g["pred_c"], "pred_c")
+    assert_close(c(loss), g["loss"], "loss", frac=1.0)
+    assert_close(c(dis), g["dis"], "dis", frac=1.0)
+    assert_close(c(npts), g["new_points"], "new_points")
+    assert_close(c(ntgt), g["new_target"], "new_target")
+
+
+@pytest.mark.parametrize("name", ["refiner_ycb_sym", "refiner_ycb_nonsym"])
+def test_refiner_inference_tensor_core_matches_reference_golden(name):
+    g = load_golden(name)
+    shp = shape_of(g)
+    net = build_refiner(shp, int(g["seed"]), ops.PREC_BF16X2)
+    fr = synth.make_frame(shp, int(g["seed"]) + 1, obj=int(g["obj"]))
+    emb = tt(fr["out_img"].reshape(32, -1)[:, fr["choose"]], "cuda")[None]
+    idx = tt(fr["idx"], "cuda").reshape(1, 1)
+    with torch.no_grad():
+        pr, pt = net(tt(g["in_points"], "cuda")[None], emb, idx)
+    assert_close(pr.cpu().numpy(), g["it0.pred_r"], "pred_r", frac=1.0)
+    assert_close(pt.cpu().numpy(), g["it0.pred_t"], "pred_t", frac=1.0)
+
+
+@pytest.mark.parametrize("frames", [1, 5])
+def test_tensor_core_full_size_vs_oracle_and_fp32_path(frames):
+    """YCB shape (N = 1000, 21 classes): tensor-core inference vs the oracle, per element, and
+    identical per frame whether batched or not."""
+    shp = synth.YCB
+    net = build_posenet(shp, 41, ops.PREC_BF16X2)
+    frs = [synth.make_frame(shp, 70 + i) for i in range(frames)]
+    st = lambda key: tt(np.stack([f[key] for f in frs]), "cuda")
+    with torch.no_grad():
+        pr, pt, pc, emb = net(st("out_img"), st("points"), st("choose")[:, None], st("idx")[:, None])
+    p = {k: tt(v) for k, v in synth.make_params("posenet", shp.num_obj, 41).items()}
+    for i, fr in enumerate(frs):
+        with torch.no_grad():
+            opr, opt_, opc, oemb = DO.posenet_forward(p, tt(fr["out_img"]), tt(fr["points"]), tt(fr["choose"]),
+                                                      int(fr["idx"]), shp.num_obj)
+        assert_close(pr[i].cpu().numpy(), opr.numpy(), "pred_r")
+        assert_close(pt[i].cpu().numpy(), opt_.numpy(), "pred_t")
+        assert_close(pc[i].cpu().numpy(), opc.numpy(), "pred_c")
+        assert np.array_equal(emb[i].cpu().numpy(), oemb.numpy())
+    if frames > 1:
+        with torch.no_grad():
+            a = net(st("out_img")[2:3], st("points")[2:3], st("choose")[2:3, None], st("idx")[2:3, None])
+        assert torch.equal(a[0][0], pr[2]) and torch.equal(a[1][0], pt[2]) and torch.equal(a[2][0], pc[2])
