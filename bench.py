@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""Benchmark of the DenseFusion dense-fusion + loss hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W              # this repo (CUDA, sm_100a)
+    python bench.py --impl reference --gpus N --steps K ...    # CPU restatement of the reference's path
+
+Workload (config C4 of BASELINE.json / SURVEY.md §8d): per GPU and per step, FRAMES synthetic
+YCB-shaped frames (N=1000 points, 21 classes, 5 of them symmetric, 120x120 crop, M=2300 mesh points)
+go through PoseNet (backbone output given) -> Loss(refine) -> 2 x (PoseRefineNet -> Loss_refine with
+ADD-S for symmetric classes).  One pose per frame => metric poses/sec.  Frames are independent, so
+ranks simply own different frames ("weak" scaling: FRAMES per GPU is fixed); no data-path collective.
+One JSON line is printed by rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+from plr2_b200 import synth  # noqa: E402
+
+METRIC = "poses/sec (PoseNet+2 refine+ADD-S)"
+SHAPE = synth.YCB_REFINE           # N=1000, O=21, M=2300, 120x120
+DISTINCT = 32                      # distinct synthetic frames generated; tiled up to FRAMES
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                "sm_max_mhz": d.get("sm_max_mhz", 1965.0), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "sm_max_mhz": 1965.0,
+            "source": "fallback"}
+
+
+def make_workload(frames, seed0):
+    """dict of CPU tensors (frames, ...) in the reference's per-frame layout."""
+    base = [synth.make_frame(SHAPE, seed0 + i) for i in range(min(DISTINCT, frames))]
+    pick = [base[i % len(base)] for i in range(frames)]
+    st = lambda k: torch.from_numpy(np.stack([f[k] for f in pick]))
+    return {"out_img": st("out_img"), "points": st("points"), "choose": st("choose")[:, None, :],
+            "obj": st("idx")[:, None], "target": st("target"), "model_points": st("model_points")}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            if not (t0 - 0.05 <= ts <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU restatement of the reference's path (oracle port) — the reference arm and the cpu_baseline leg
+def cpu_reference_step(work, params_pn, params_rf, frames):
+    from oracle import densefusion_oracle as DO      # the ONLY place bench.py touches oracle/
+    out = []
+    with torch.no_grad():
+        for f in range(frames):
+            obj = int(work["obj"][f, 0])
+            pr, pt, pc, emb = DO.posenet_forward(params_pn, work["out_img"][f], work["points"][f],
+                                                 work["choose"][f, 0], obj, SHAPE.num_obj)
+            _, dis, npts, ntgt, _ = DO.pose_loss(pr, pt, pc, work["target"][f], work["model_points"][f], obj,
+                                                 work["points"][f], 0.015, True, SHAPE.sym_list)
+            for _ in range(2):
+                rr, rt = DO.refiner_forward(params_rf, npts, emb, obj, SHAPE.num_obj)
+                dis, npts, ntgt, _ = DO.refine_loss(rr, rt, ntgt, work["model_points"][f], obj, npts, SHAPE.sym_list)
+            out.append(float(dis))
+    return out
+
+
+def time_cpu_reference(work, params_pn, params_rf, frames, steps, warmup):
+    for _ in range(warmup):
+        cpu_reference_step(work, params_pn, params_rf, min(frames, 2))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_reference_step(work, params_pn, params_rf, frames)
+    dt = time.perf_counter() - t0
+    return frames * steps / dt, dt
+
+
+def knn_roofline(pk):
+    """ADD-S 1-NN kernel at config C2 size (500 refs x 500 000 queries per frame, 8 frames)."""
+    from plr2_b200.lib.knn import knn_indices
+    g = torch.Generator(device="cuda").manual_seed(0)
+    ref = torch.randn(8, 3, 500, device="cuda", generator=g) * 0.05
+    qry = torch.randn(8, 3, 500_000, device="cuda", generator=g) * 0.05
+    peak_tflops = 148 * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12
+    out = {}
+    for name, mode in (("exact", 0), ("fast", 1)):
+        for _ in range(3):
+            knn_indices(ref, qry, 1, mode)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            knn_indices(ref, qry, 1, mode)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        pairs = 8 * 500 * 500_000
+        out[name] = {"Gpairs_s": pairs / ms / 1e6, "achieved": 8 * pairs / ms / 1e9, "peak": peak_tflops,
+                     "unit": "TFLOP/s", "frac": 8 * pairs / ms / 1e9 / peak_tflops, "bound": "fp32",
+                     "ms_per_launch": ms, "pairs_per_launch": pairs}
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+def dist_setup(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        backend = "gloo" if args.impl == "reference" else "nccl"
+        if args.impl != "reference":
+            torch.cuda.set_device(local)
+        dist.init_process_group(backend=backend)
+    return world, rank, local
+
+
+def run_reference(args, world, rank):
+    """Reference arm: the reference's CPU implementation of the path (oracle port; the reference's own
+    Python modules cannot travel to the GPU box) on the box's host cores, rank 0 only."""
+    if rank != 0:
+        return
+    torch.set_num_threads(os.cpu_count() or 1)
+    frames = args.ref_frames
+    work = make_workload(frames, 1000)
+    pn = {k: torch.from_numpy(v) for k, v in synth.make_params("posenet", SHAPE.num_obj, 1).items()}
+    rf = {k: torch.from_numpy(v) for k, v in synth.make_params("refiner", SHAPE.num_obj, 2).items()}
+    rate, dt = time_cpu_reference(work, pn, rf, frames, args.steps, min(args.warmup, 3))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": "poses/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C4: YCB-shaped frames, PoseNet(out_img given)+Loss(refine)+2x(PoseRefineNet+Loss_refine ADD-S)",
+                   "frames_per_step": frames, "num_points": SHAPE.num_points, "num_mesh": SHAPE.num_mesh,
+                   "num_obj": SHAPE.num_obj},
+        "cpu_baseline": {"value": rate, "unit": "poses/s", "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": f"{frames} frames/step x {args.steps} steps (oracle: torch CPU fp32 + C/OpenMP 1-NN)"},
+        "e2e": {"value": rate, "unit": "poses/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, world, rank, local):
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (this path has no CPU fallback; use --impl reference)")
+    from plr2_b200 import _cabi, ops
+    from plr2_b200.pipeline import DenseFusionPipeline, INPUT_KEYS
+    import ctypes as C
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    L = _cabi.lib()
+    pk = peaks()
+    frames = args.frames
+    knn_mode = ops.KNN_FAST if args.knn == "fast" else ops.KNN_EXACT
+    pipe = DenseFusionPipeline(SHAPE.num_points, SHAPE.num_obj, SHAPE.num_mesh, SHAPE.sym_list, device=dev,
+                               precision=ops.PREC_BF16X2, knn_mode=knn_mode, chunk_frames=args.chunk)
+    pn = synth.make_params("posenet", SHAPE.num_obj, 1)
+    rf = synth.make_params("refiner", SHAPE.num_obj, 2)
+    pipe.load_params(pn, rf)
+    work = make_workload(frames, 1000 + 7919 * rank)
+    host = {k: v.pin_memory() for k, v in work.items()}
+    devw = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    # ---- device-resident (value) ---------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        pipe.infer(*(devw[k] for k in INPUT_KEYS))
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    launches0 = L.plr2_launch_count()
+    L.plr2_profile_begin()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        res = pipe.infer(*(devw[k] for k in INPUT_KEYS))
+    e1.record()
+    barrier()
+    t1 = time.time()
+    ms_dev = max_over_ranks(e0.elapsed_time(e1))
+    tc_ms, tc_n, tc_fl = C.c_double(), C.c_longlong(), C.c_double()
+    L.plr2_profile_end(C.byref(tc_ms), C.byref(tc_n), C.byref(tc_fl))
+    launches = L.plr2_launch_count() - launches0
+    clocks = sampler.stop(t0, t1) if sampler else None
+    value = world * frames * args.steps / (ms_dev / 1e3)
+
+    # ---- end to end from pinned host buffers (e2e) ---------------------------------------------
+    for _ in range(3):
+        pipe.infer_host(host)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        res_host = pipe.infer_host(host)
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    e2e = world * frames * args.steps / (ms_e2e / 1e3)
+    h2d = DenseFusionPipeline.bytes_per_frame(host) * frames
+    d2h = frames * 4
+    finite = bool(torch.isfinite(res_host).all()) and bool(torch.isfinite(res).all())
+    if rank != 0:
+        return
+
+    # ---- rooflines, CPU baseline (rank 0, N == 1 only for the CPU leg) --------------------------
+    achieved = tc_fl.value / (tc_ms.value / 1e3) / 1e12 if tc_ms.value > 0 else 0.0
+    peak = pk["bf16_tflops_sustained"]
+    roofline = {"bound": "tensor", "kernel": "gemm_bf16x2_kernel (tcgen05 kind::f16, split-bf16: 3 MMAs per algorithmic MAC)",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                "executed_tflops": 3 * achieved, "frac_executed": 3 * achieved / peak,
+                "launches": int(tc_n.value), "avg_launch_ms": tc_ms.value / max(1, tc_n.value),
+                "share_of_step": tc_ms.value / (e0.elapsed_time(e1) * 0 + ms_dev) if ms_dev else None,
+                "peak_source": pk["source"] + " bf16_tflops_sustained"}
+    knn = knn_roofline(pk)
+    cpu = None
+    if world == 1 and args.cpu_frames > 0:
+        torch.set_num_threads(os.cpu_count() or 1)
+        pnt = {k: torch.from_numpy(v) for k, v in pn.items()}
+        rft = {k: torch.from_numpy(v) for k, v in rf.items()}
+        rate, dt = time_cpu_reference(work, pnt, rft, args.cpu_frames, 2, 1)
+        cpu = {"value": rate, "unit": "poses/s", "cores": torch.get_num_threads(), "kind": "port",
+               "sample": f"{args.cpu_frames} frames x 2 passes of the same workload ({dt:.1f} s; oracle: torch CPU fp32 + C/OpenMP 1-NN)"}
+        # cross-check the first frames against the oracle (the oracle is the checker, never the product)
+        ref = cpu_reference_step(work, pnt, rft, 2)
+        got = [float(x) for x in res_host[:2]]
+        cpu["check_first2_rel_err"] = [abs(a - b) / max(abs(b), 1e-12) for a, b in zip(got, ref)]
+    line = {
+        "metric": METRIC, "value": value, "unit": "poses/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16x2-split operands, f32 accumulate (f32 SIMT for small layers/losses)",
+        "data": "synthetic",
+        "config": {"workload": "C4: YCB-shaped frames, PoseNet(out_img given)+Loss(refine)+2x(PoseRefineNet+Loss_refine ADD-S)",
+                   "frames_per_gpu_per_step": frames, "chunk_frames": args.chunk, "num_points": SHAPE.num_points,
+                   "num_mesh": SHAPE.num_mesh, "num_obj": SHAPE.num_obj, "crop": [SHAPE.height, SHAPE.width],
+                   "knn_mode": args.knn, "l2": "inputs (%.0f MB per step) larger than L2" % (h2d / 1e6),
+                   "results_finite": finite},
+        "e2e": {"value": e2e, "unit": "poses/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roofline,
+        "roofline_knn": knn,
+        "knn_gpairs_per_s": {k: v["Gpairs_s"] for k, v in knn.items()},
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=512, help="frames per GPU per step (config C4)")
+    ap.add_argument("--chunk", type=int, default=64, help="frames per launch chunk")
+    ap.add_argument("--knn", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--cpu-frames", type=int, default=8, help="frames of the CPU baseline sample (0 = skip)")
+    ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the reference arm")
+    args = ap.parse_args()
+    world, rank, local = dist_setup(args)
+    if args.impl == "reference":
+        run_reference(args, world, rank)
+    else:
+        run_ours(args, world, rank, local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

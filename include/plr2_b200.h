@@ -14,8 +14,7 @@
  *   plr2_pose_loss_bwd      <- autograd of the above            (torch autograd in the reference)
  *   plr2_pose_select        <- best-vote select + re-centre     lib/loss.py:52-69
  *   plr2_refine_loss_fwd/bwd<- loss_calculation (refiner)       lib/loss_refiner.py:12-62
- *   plr2_gather_emb         <- torch.gather at `choose`         lib/network.py:98-102
- *   plr2_linear_*           <- Conv1d(k=1)/Linear + ReLU chain  lib/network.py:53-68,107-121,151-168,193-200
+ *   plr2_gemm_f32 / plr2_gemm_bf16x2 <- Conv1d(k=1)/Linear library calls  lib/network.py:54-63,107-121,152-163,193-200
  *   plr2_posenet_* / plr2_refiner_*  <- PoseNet.forward / PoseRefineNet.forward  lib/network.py:95-132,187-206
  */
 #ifndef PLR2_B200_H
@@ -46,6 +45,11 @@ extern "C" {
 int         plr2_abi_version(void);
 const char *plr2_last_error_string(void);   /* thread-local, never NULL */
 int         plr2_device_sm_count(void);     /* multiProcessorCount of the current device, or <0 */
+long long   plr2_launch_count(void);        /* kernels launched by this library so far (this process) */
+/* Bracket every tensor-core GEMM launch with CUDA events; end() synchronises the device and returns
+ * the summed kernel time (ms), launch count and algorithmic FLOPs (2 M N K) of those launches. */
+int         plr2_profile_begin(void);
+int         plr2_profile_end(double *ms, long long *launches, double *flops);
 
 /* ---- (4) brute-force nearest neighbours ---------------------------------------------------
  * ref   [batch][dim][n_ref]   f32, contiguous        (lib/knn/src/knn.h:33)

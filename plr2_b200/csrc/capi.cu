@@ -4,6 +4,7 @@
 
 namespace plr2 {
 static thread_local char g_err[512] = "";
+long long g_launch_count = 0;
 void set_error(const char *fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -24,3 +25,4 @@ extern "C" int plr2_device_sm_count(void) {
   }
   return n;
 }
+extern "C" long long plr2_launch_count(void) { return plr2::g_launch_count; }

@@ -14,7 +14,11 @@ namespace plr2 {
 // thread-local last-error text, set by the C-ABI wrappers
 void set_error(const char *fmt, ...);
 
-inline int check_launch(const char *what) {
+// number of kernels this library has launched (plr2_launch_count)
+extern long long g_launch_count;
+
+inline int check_launch(const char *what, int launches = 1) {
+  g_launch_count += launches;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));

@@ -19,6 +19,7 @@
 #include "tc_ptx.cuh"
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <vector>
 
 namespace plr2 {
 
@@ -366,6 +367,25 @@ static int sm_count() {
   return n;
 }
 
+// Optional CUDA-event timing of every tensor-core launch (plr2_profile_begin / plr2_profile_end).
+struct TcProfile {
+  bool on = false;
+  std::vector<cudaEvent_t> ev;      // pairs
+  size_t used = 0;
+  double flops = 0.0;
+  long long launches = 0;
+};
+static TcProfile g_prof;
+
+static cudaEvent_t prof_event() {
+  if (g_prof.used == g_prof.ev.size()) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    g_prof.ev.push_back(e);
+  }
+  return g_prof.ev[g_prof.used++];
+}
+
 template <int BN>
 static int launch_tc(const TcGemm &g, cudaStream_t st) {
   using Cfg = TcCfg<BN>;
@@ -392,7 +412,13 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   }
   const long long tiles = (long long)k.m_tiles * k.n_tiles * k.batch;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  if (g_prof.on) cudaEventRecord(prof_event(), st);
   gemm_bf16x2_kernel<BN><<<grid, TC_THREADS, Cfg::SMEM_BYTES, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, k);
+  if (g_prof.on) {
+    cudaEventRecord(prof_event(), st);
+    g_prof.flops += 2.0 * g.M * g.N * g.K * g.batch;
+    g_prof.launches += 1;
+  }
   return check_launch("gemm_bf16x2");
 }
 
@@ -424,4 +450,28 @@ extern "C" int plr2_gemm_bf16x2(const void *A_planes, long long lda, long long a
   g.W = (const __nv_bfloat16 *)W_planes; g.ldw = ldw; g.w_plane = w_plane;
   g.M = M; g.N = N; g.K = K; g.bias = bias; g.relu = relu; g.out_mode = plr2::TC_OUT_F32; g.Cf = C; g.ldc = ldc;
   return plr2::gemm_bf16x2(g, (cudaStream_t)stream);
+}
+
+// Profiling of the tensor-core launches: between begin and end every gemm_bf16x2 launch is bracketed
+// by CUDA events on its stream.  end() synchronises the device and returns the summed kernel time,
+// the number of launches and their algorithmic FLOPs (2 M N K per problem; the kernel executes 3x
+// that many bf16 tensor-core FLOPs).
+extern "C" int plr2_profile_begin(void) {
+  plr2::g_prof.on = true; plr2::g_prof.used = 0; plr2::g_prof.flops = 0.0; plr2::g_prof.launches = 0;
+  return 0;
+}
+extern "C" int plr2_profile_end(double *ms, long long *launches, double *flops) {
+  using namespace plr2;
+  g_prof.on = false;
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { set_error("plr2_profile_end: %s", cudaGetErrorString(e)); return (int)e; }
+  double total = 0.0;
+  for (size_t i = 0; i + 1 < g_prof.used; i += 2) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, g_prof.ev[i], g_prof.ev[i + 1]) == cudaSuccess) total += t;
+  }
+  if (ms) *ms = total;
+  if (launches) *launches = g_prof.launches;
+  if (flops) *flops = g_prof.flops;
+  return 0;
 }

@@ -540,7 +540,7 @@ extern "C" int plr2_pose_loss_fwd(const float *pred_r, const float *pred_t, cons
 #undef ARGS
   }
   if (loss) loss_reduce_kernel<<<frames, 256, 0, st>>>(dis, pred_c, n_points, w, loss);
-  return check_launch("plr2_pose_loss_fwd");
+  return check_launch("plr2_pose_loss_fwd", 1 + (may_sym ? 1 : 0) + (loss ? 1 : 0));
 }
 
 extern "C" int plr2_pose_loss_bwd(const float *g_loss, const float *g_dis_sel, const int32_t *which_max,

@@ -97,7 +97,7 @@ class PoseNet(nn.Module):
         if x.shape[1] != self.num_points:
             raise ValueError(f"PoseNet built for {self.num_points} points got {x.shape[1]} "
                              "(AvgPool1d(num_points), lib/network.py:51,65)")
-        return ops.PoseNetFn.apply(self._state, self.precision, out_img, x, choose, obj,
+        return ops.PoseNetFn.apply(self._state, self.precision, torch.is_grad_enabled(), out_img, x, choose, obj,
                                    *self.hot_path_parameters())
 
     def forward(self, img, x, choose, obj):
@@ -126,4 +126,5 @@ class PoseRefineNet(nn.Module):
     def forward(self, x, emb, obj):
         if x.shape[1] != self.num_points:
             raise ValueError(f"PoseRefineNet built for {self.num_points} points got {x.shape[1]}")
-        return ops.RefinerFn.apply(self._state, self.precision, x, emb, obj, *self.hot_path_parameters())
+        return ops.RefinerFn.apply(self._state, self.precision, torch.is_grad_enabled(), x, emb, obj,
+                                   *self.hot_path_parameters())

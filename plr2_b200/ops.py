@@ -212,7 +212,7 @@ class PoseNetFn(torch.autograd.Function):
     -> pred_r (F,N,4), pred_t (F,N,3), pred_c (F,N,1), emb (F,32,N)."""
 
     @staticmethod
-    def forward(ctx, state, precision, out_img, x, choose, obj, *params):
+    def forward(ctx, state, precision, grad_mode, out_img, x, choose, obj, *params):
         _need_cuda(out_img, "PoseNetFn")
         dev = out_img.device
         F, C, H, Wd = out_img.shape
@@ -221,7 +221,7 @@ class PoseNetFn(torch.autograd.Function):
         oi, xs = _f32c(out_img), _f32c(x)
         ch = choose.detach().reshape(F, N).to(torch.int64).contiguous()
         ob = obj.detach().reshape(F).to(torch.int64).contiguous()
-        training = any(ctx.needs_input_grad)
+        training = bool(grad_mode) and any(ctx.needs_input_grad)
         packed = state.packed_for(params, precision)
         ws, nbytes = state.workspace(F, N, training, dev)
         pred_r = torch.empty((F, N, 4), dtype=torch.float32, device=dev)
@@ -250,7 +250,7 @@ class PoseNetFn(torch.autograd.Function):
             packed = state.packed_for(ctx.params, ctx.precision)
         dev = xs.device
         gp = torch.empty(packed.numel() // 2, dtype=torch.float32, device=dev)
-        g_img = torch.zeros((F, 32, H, Wd), dtype=torch.float32, device=dev) if ctx.needs_input_grad[2] else None
+        g_img = torch.zeros((F, 32, H, Wd), dtype=torch.float32, device=dev) if ctx.needs_input_grad[3] else None
         z = lambda g, shp: _f32c(g) if g is not None else torch.zeros(shp, dtype=torch.float32, device=dev)
         g_r, g_t, g_c = z(g_r, (F, N, 4)), z(g_t, (F, N, 3)), z(g_c, (F, N, 1))
         with torch.cuda.device(dev):
@@ -261,7 +261,7 @@ class PoseNetFn(torch.autograd.Function):
         _cabi.check(rc, "plr2_posenet_backward")
         grads = _unpack_grads(NET_POSENET, state.num_obj, gp, ctx.params, dev)
         ctx.saved = None
-        return (None, None, g_img, None, None, None) + tuple(grads)
+        return (None, None, None, g_img, None, None, None) + tuple(grads)
 
 
 class RefinerFn(torch.autograd.Function):
@@ -269,13 +269,13 @@ class RefinerFn(torch.autograd.Function):
     -> pred_r (F,4), pred_t (F,3)."""
 
     @staticmethod
-    def forward(ctx, state, precision, x, emb, obj, *params):
+    def forward(ctx, state, precision, grad_mode, x, emb, obj, *params):
         _need_cuda(x, "RefinerFn")
         dev = x.device
         F, N = x.shape[0], x.shape[1]
         xs, em = _f32c(x), _f32c(emb)
         ob = obj.detach().reshape(F).to(torch.int64).contiguous()
-        training = any(ctx.needs_input_grad)
+        training = bool(grad_mode) and any(ctx.needs_input_grad)
         packed = state.packed_for(params, precision)
         ws, nbytes = state.workspace(F, N, training, dev)
         pred_r = torch.empty((F, 4), dtype=torch.float32, device=dev)
@@ -309,4 +309,15 @@ class RefinerFn(torch.autograd.Function):
         _cabi.check(rc, "plr2_refiner_backward")
         grads = _unpack_grads(NET_REFINER, state.num_obj, gp, ctx.params, dev)
         ctx.saved = None
-        return (None, None, None, None, None) + tuple(grads)
+        return (None, None, None, None, None, None) + tuple(grads)
+
+
+def tensor_core_profile(fn):
+    """Run fn() with the tcgen05 launches bracketed by CUDA events; returns (result, ms, launches, flops)."""
+    import ctypes as C
+    L = _cabi.lib()
+    L.plr2_profile_begin()
+    out = fn()
+    ms, n, fl = C.c_double(), C.c_longlong(), C.c_double()
+    _cabi.check(L.plr2_profile_end(C.byref(ms), C.byref(n), C.byref(fl)), "plr2_profile_end")
+    return out, ms.value, n.value, fl.value

@@ -1,0 +1,117 @@
+"""Frame-batched DenseFusion inference / evaluation pipeline — the call a user of this repo makes.
+
+Reproduces, for F independent frames at once, the reference's per-frame test loop
+(tools/train.py:182-188):
+
+    pred_r, pred_t, pred_c, emb = estimator(img, points, choose, idx)
+    _, dis, new_points, new_target = criterion(pred_r, pred_t, pred_c, target, model_points, idx, points, w, refine_start)
+    for ite in range(iteration):                       # kernel (5): stays on the device, no host sync
+        pred_r, pred_t = refiner(new_points, emb, idx)
+        dis, new_points, new_target = criterion_refine(pred_r, pred_t, new_target, model_points, idx, new_points)
+
+with the PSPNet backbone left out (its output `out_img` is the input here).  Frames are processed in
+chunks so the activation workspace stays bounded; `infer_host` streams chunks from pinned host memory
+on a copy stream while the previous chunk computes.
+"""
+import torch
+
+from . import ops
+from .lib.loss import Loss
+from .lib.loss_refiner import Loss_refine
+from .lib.network import PoseNet, PoseRefineNet
+
+INPUT_KEYS = ("out_img", "points", "choose", "obj", "target", "model_points")
+
+
+class DenseFusionPipeline:
+    def __init__(self, num_points, num_obj, num_mesh, sym_list, device="cuda", precision=ops.PREC_BF16X2,
+                 knn_mode=ops.KNN_EXACT, refine_iters=2, chunk_frames=64, w=0.015, refine_start=True,
+                 with_backbone=False):
+        self.device = torch.device(device)
+        self.estimator = PoseNet(num_points, num_obj, precision=precision)
+        if not with_backbone:
+            self.estimator.cnn = torch.nn.Identity()
+        self.estimator = self.estimator.to(self.device).eval()
+        self.refiner = PoseRefineNet(num_points, num_obj, precision=precision).to(self.device).eval()
+        self.criterion = Loss(num_mesh, list(sym_list), knn_mode)
+        self.criterion_refine = Loss_refine(num_mesh, list(sym_list), knn_mode)
+        self.refine_iters = refine_iters
+        self.chunk_frames = chunk_frames
+        self.w = w
+        self.refine_start = refine_start
+        self._staging = None
+
+    def load_params(self, posenet_params, refiner_params):
+        """dicts name -> numpy/torch array in the reference's state-dict naming."""
+        as_t = lambda d: {k: torch.as_tensor(v) for k, v in d.items()}
+        self.estimator.load_state_dict(as_t(posenet_params), strict=False)
+        self.refiner.load_state_dict(as_t(refiner_params))
+
+    # -- one chunk, everything already on the device -------------------------------------------
+    def _chunk(self, out_img, points, choose, obj, target, model_points):
+        pr, pt, pc, emb = self.estimator.forward_features(out_img, points, choose, obj)
+        _, dis, new_points, new_target = self.criterion(pr, pt, pc, target, model_points, obj, points, self.w,
+                                                        self.refine_start)
+        if dis.dim() == 0:
+            dis = dis.reshape(1)
+        for _ in range(self.refine_iters):
+            rr, rt = self.refiner(new_points, emb, obj)
+            dis, new_points, new_target = self.criterion_refine(rr, rt, new_target, model_points, obj, new_points)
+        return dis
+
+    @torch.no_grad()
+    def infer(self, out_img, points, choose, obj, target, model_points):
+        """Device-resident inputs (F, ...).  Returns the final ADD / ADD-S distance per frame (F,)."""
+        F = out_img.shape[0]
+        out = torch.empty(F, dtype=torch.float32, device=out_img.device)
+        for a in range(0, F, self.chunk_frames):
+            b = min(F, a + self.chunk_frames)
+            out[a:b] = self._chunk(out_img[a:b], points[a:b], choose[a:b], obj[a:b], target[a:b], model_points[a:b])
+        return out
+
+    @torch.no_grad()
+    def infer_host(self, host):
+        """`host`: dict of PINNED CPU tensors with the INPUT_KEYS.  Chunks are copied on a side stream
+        into two alternating device staging sets while the previous chunk computes; the per-frame
+        result comes back to (pinned) host memory.  Returns a CPU tensor (F,)."""
+        F = host["out_img"].shape[0]
+        cf = min(self.chunk_frames, F)
+        dev = self.device
+        if self._staging is None or self._staging[0]["out_img"].shape[0] != cf or \
+                any(self._staging[0][k].shape[1:] != host[k].shape[1:] for k in INPUT_KEYS):
+            self._staging = [{k: torch.empty((cf,) + tuple(host[k].shape[1:]), dtype=host[k].dtype, device=dev)
+                              for k in INPUT_KEYS} for _ in range(2)]
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._ready = [torch.cuda.Event() for _ in range(2)]
+            self._free = [torch.cuda.Event() for _ in range(2)]
+        res_dev = torch.empty(F, dtype=torch.float32, device=dev)
+        res_host = torch.empty(F, dtype=torch.float32, pin_memory=True)
+        main = torch.cuda.current_stream(dev)
+        chunks = [(a, min(F, a + cf)) for a in range(0, F, cf)]
+
+        def issue_copy(i):
+            a, b = chunks[i]
+            s = self._staging[i & 1]
+            with torch.cuda.stream(self._copy_stream):
+                if i >= 2:
+                    self._copy_stream.wait_event(self._free[i & 1])   # compute of chunk i-2 has finished
+                for k in INPUT_KEYS:
+                    s[k][: b - a].copy_(host[k][a:b], non_blocking=True)
+                self._ready[i & 1].record(self._copy_stream)
+
+        issue_copy(0)
+        for i, (a, b) in enumerate(chunks):
+            if i + 1 < len(chunks):
+                issue_copy(i + 1)
+            main.wait_event(self._ready[i & 1])
+            s = self._staging[i & 1]
+            n = b - a
+            res_dev[a:b] = self._chunk(*(s[k][:n] for k in INPUT_KEYS))
+            self._free[i & 1].record(main)
+        res_host.copy_(res_dev, non_blocking=True)
+        main.synchronize()
+        return res_host
+
+    @staticmethod
+    def bytes_per_frame(host):
+        return sum(int(host[k][0].numel()) * host[k].element_size() for k in INPUT_KEYS)

@@ -202,7 +202,9 @@ def test_posenet_inference_tensor_core_matches_reference_golden(name):
     points = tt(fr["points"], "cuda")[None]
     idx = tt(fr["idx"], "cuda").reshape(1, 1)
     with torch.no_grad():
-        pr, pt, pc, emb = net(tt(fr["out_img"], "cuda")[None], points, tt(fr["choose"], "cuda")[None, None], idx)
+        (pr, pt, pc, emb), _, n_tc, _ = ops.tensor_core_profile(
+            lambda: net(tt(fr["out_img"], "cuda")[None], points, tt(fr["choose"], "cuda")[None, None], idx))
+        assert n_tc == 7, "PoseNet inference must run its 7 tcgen05 GEMM launches"
         crit = Loss(shp.num_mesh, list(shp.sym_list))
         loss, dis, npts, ntgt = crit(pr, pt, pc, tt(fr["target"], "cuda")[None], tt(fr["model_points"], "cuda")[None],
                                      idx, points, float(g["w"]), bool(g["refine"]))
@@ -226,7 +228,8 @@ def test_refiner_inference_tensor_core_matches_reference_golden(name):
     emb = tt(fr["out_img"].reshape(32, -1)[:, fr["choose"]], "cuda")[None]
     idx = tt(fr["idx"], "cuda").reshape(1, 1)
     with torch.no_grad():
-        pr, pt = net(tt(g["in_points"], "cuda")[None], emb, idx)
+        (pr, pt), _, n_tc, _ = ops.tensor_core_profile(lambda: net(tt(g["in_points"], "cuda")[None], emb, idx))
+    assert n_tc == 4, "PoseRefineNet inference must run its 4 tcgen05 GEMM launches"
     assert_close(pr.cpu().numpy(), g["it0.pred_r"], "pred_r", frac=1.0)
     assert_close(pt.cpu().numpy(), g["it0.pred_t"], "pred_t", frac=1.0)
 
@@ -240,7 +243,9 @@ def test_tensor_core_full_size_vs_oracle_and_fp32_path(frames):
     frs = [synth.make_frame(shp, 70 + i) for i in range(frames)]
     st = lambda key: tt(np.stack([f[key] for f in frs]), "cuda")
     with torch.no_grad():
-        pr, pt, pc, emb = net(st("out_img"), st("points"), st("choose")[:, None], st("idx")[:, None])
+        (pr, pt, pc, emb), _, n_tc, flops = ops.tensor_core_profile(
+            lambda: net(st("out_img"), st("points"), st("choose")[:, None], st("idx")[:, None]))
+    assert n_tc == 7 and flops > 3.5e9 * frames
     p = {k: tt(v) for k, v in synth.make_params("posenet", shp.num_obj, 41).items()}
     for i, fr in enumerate(frs):
         with torch.no_grad():
@@ -253,4 +258,7 @@ def test_tensor_core_full_size_vs_oracle_and_fp32_path(frames):
     if frames > 1:
         with torch.no_grad():
             a = net(st("out_img")[2:3], st("points")[2:3], st("choose")[2:3, None], st("idx")[2:3, None])
-        assert torch.equal(a[0][0], pr[2]) and torch.equal(a[1][0], pt[2]) and torch.equal(a[2][0], pc[2])
+        # the fused average pool sums in 32-row groups, so the summation order (not the math) depends on
+        # where the frame starts in the batch: equal to fp32 rounding, not bit for bit
+        for x, y in zip(a[:3], (pr, pt, pc)):
+            assert_close(x[0].cpu().numpy(), y[2].cpu().numpy(), "batched vs single", rtol=1e-4, frac=1.0)
