@@ -26,8 +26,10 @@ namespace plr2 {
 using namespace tc;
 
 constexpr int TC_BM = 128, TC_BK = 64;
-constexpr int TC_THREADS = 256;
-constexpr int TC_EPI_PITCH = 36;                       // floats per staged row (32 + 4 pad: conflict-free float4)
+constexpr int TC_EPI_WARPS = 8;                        // two warpgroups: each TMEM lane quarter is served by 2 warps
+constexpr int TC_THREADS = 128 + 32 * TC_EPI_WARPS;
+constexpr int TC_EPI_COLS = 16;                        // columns per epilogue chunk
+constexpr int TC_EPI_PITCH = 20;                       // floats per staged row (16 + 4 pad: conflict-free float4 stores)
 constexpr int TC_EPI_FLOATS = 32 * TC_EPI_PITCH;        // per epilogue warp
 
 template <int BN> struct TcCfg {
@@ -36,7 +38,9 @@ template <int BN> struct TcCfg {
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;                      // two accumulator stages
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 4 * 32 * 36 * 4 /*epilogue slabs*/;
+  static constexpr int EPI_BYTES = TC_EPI_WARPS * TC_EPI_FLOATS * 4;          // transpose slabs
+  static constexpr int BIAS_BYTES = 2 * 2 * BN * 4;                          // [acc stage][frame a|b][BN] staged bias
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + EPI_BYTES + BIAS_BYTES;
 };
 
 struct TcKernelArgs {
@@ -76,7 +80,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     prefetch_tensormap(&tmA_hi); prefetch_tensormap(&tmA_lo);
     prefetch_tensormap(&tmB_hi); prefetch_tensormap(&tmB_lo);
     for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar + s, 1); mbar_init(tempty_bar + s, 128); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar + s, 1); mbar_init(tempty_bar + s, 32 * TC_EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
@@ -139,111 +143,133 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
-    const int wq = warp - 4;                              // TMEM lane quarter == warp % 4
+    const int we = warp - 4;                              // 0..7
+    const int wq = warp & 3;                              // TMEM lane quarter == warp % 4
+    const int half = we >> 2;                             // which half of the column chunks this warpgroup takes
+    const int te = threadIdx.x - 128;                     // 0..255 among epilogue threads
+    float *sT = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256) + we * TC_EPI_FLOATS;
+    float *sBias = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + Cfg::EPI_BYTES);
     int as = 0; uint32_t aphase = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int z = t / tiles_per_z, r = t % tiles_per_z;
       const int m0 = (r / g.n_tiles) * TC_BM, n0 = (r % g.n_tiles) * BN;
       const float *bias = g.bias ? g.bias + z * g.bias_z : nullptr;
+      // Stage bias[n] (+ frame_bias[frame][n]) of this tile's <= 2 frames: sB[sel][c], sel = row >= split_row
+      const int fa = m0 / g.rows_per_frame;
+      const int split_row = (fa + 1) * g.rows_per_frame;  // first row of the tile's second frame
+      float *sB = sBias + as * 2 * BN;
+      for (int i = te; i < 2 * BN; i += 32 * TC_EPI_WARPS) {
+        const int sel = i / BN, c = i - sel * BN, n = n0 + c;
+        float v = 0.f;
+        if (n < g.N) {
+          if (bias) v = __ldg(bias + n);
+          if (g.frame_bias) {
+            const long long fr = fa + sel;
+            if (fr * g.rows_per_frame < g.M) v += __ldg(g.frame_bias + fr * g.ldfb + n);
+          }
+        }
+        sB[i] = v;
+      }
+      named_bar_sync(1, 32 * TC_EPI_WARPS);
       mbar_wait(tfull_bar + as, aphase);
       fence_after_sync();
-      float *sT = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256) + wq * TC_EPI_FLOATS;
       const int rbase = m0 + wq * 32;                     // first row of this warp's 32-row slab
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = half * TC_EPI_COLS; c0 < BN; c0 += 2 * TC_EPI_COLS) {
         if (n0 + c0 >= g.N) break;                        // warp-uniform
         const int nc = n0 + c0;
-        // TMEM -> registers (thread = row) -> smem slab [32][36] -> registers (lanes along columns),
-        // so that every global store covers full 128-byte row segments.
-        uint32_t raw[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + as * BN + c0, raw);
+        // TMEM -> registers (thread = row) -> smem slab [32][20] -> registers (lanes along columns),
+        // so that every global store covers whole 32-byte sectors of a row.
+        uint32_t raw[16];
+        tmem_ld_32x16(tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + as * BN + c0, raw);
         tmem_ld_wait();
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
+        for (int q = 0; q < 4; ++q)
           *reinterpret_cast<uint4 *>(sT + lane * TC_EPI_PITCH + 4 * q) = make_uint4(raw[4 * q], raw[4 * q + 1], raw[4 * q + 2], raw[4 * q + 3]);
         __syncwarp();
         if (g.out_mode != TC_OUT_BF16X2) {
-          const int cq = lane & 7, rq = lane >> 3;        // 8 column quads x 4 rows per pass
+          const int cq = lane & 3, rq = lane >> 2;        // 4 column quads x 8 rows per pass
           const int n = nc + 4 * cq;
-          const bool vec = n + 3 < g.N;
-          float bv[4] = {0.f, 0.f, 0.f, 0.f};
-          if (bias) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) if (n + j < g.N) bv[j] = __ldg(bias + n + j);
-          }
+          const float4 b0 = *reinterpret_cast<const float4 *>(sB + c0 + 4 * cq);
+          const float4 b1 = *reinterpret_cast<const float4 *>(sB + BN + c0 + 4 * cq);
           float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
-          const int fa = rbase / g.rows_per_frame;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = 4 * i + rq, row = rbase + r;
-            const float4 a4 = *reinterpret_cast<const float4 *>(sT + r * TC_EPI_PITCH + 4 * cq);
-            float a[4] = {a4.x + bv[0], a4.y + bv[1], a4.z + bv[2], a4.w + bv[3]};
+          for (int i = 0; i < 4; ++i) {
+            const int rr = 8 * i + rq, row = rbase + rr;
+            const float4 a4 = *reinterpret_cast<const float4 *>(sT + rr * TC_EPI_PITCH + 4 * cq);
+            const bool second = row >= split_row;
+            const float4 bb = second ? b1 : b0;
+            float a[4] = {a4.x + bb.x, a4.y + bb.y, a4.z + bb.z, a4.w + bb.w};
+            if (g.relu) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) a[j] = fmaxf(a[j], 0.f);
+            }
             if (row < g.M) {
-              const int fr = row / g.rows_per_frame;
-              if (g.frame_bias) {
-                const float *fb = g.frame_bias + (long long)fr * g.ldfb + n;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) if (n + j < g.N) a[j] += __ldg(fb + j);
-              }
-              if (g.relu) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) a[j] = fmaxf(a[j], 0.f);
-              }
               if (g.out_mode == TC_OUT_F32) {
                 float *dst = g.Cf + (long long)row * g.ldc + z * g.c_col_z + n;
-                if (vec && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                if (n + 3 < g.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
                   *reinterpret_cast<float4 *>(dst) = make_float4(a[0], a[1], a[2], a[3]);
                 } else {
 #pragma unroll
                   for (int j = 0; j < 4; ++j) if (n + j < g.N) dst[j] = a[j];
                 }
-              } else {                                    // TC_OUT_POOL: <= 2 frames per 32 rows
-                if (fr == fa) { sa[0] += a[0]; sa[1] += a[1]; sa[2] += a[2]; sa[3] += a[3]; }
-                else          { sb[0] += a[0]; sb[1] += a[1]; sb[2] += a[2]; sb[3] += a[3]; }
+              } else {                                    // TC_OUT_POOL: <= 2 frames per tile
+                if (!second) { sa[0] += a[0]; sa[1] += a[1]; sa[2] += a[2]; sa[3] += a[3]; }
+                else         { sb[0] += a[0]; sb[1] += a[1]; sb[2] += a[2]; sb[3] += a[3]; }
               }
             }
           }
           if (g.out_mode == TC_OUT_POOL && rbase < g.M) {
+            // pool[(row group)][slot] : slot 0 = frame of the group's first row, slot 1 = the next frame
+            const bool first_is_a = rbase < split_row;    // warp-uniform
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              sa[j] += __shfl_xor_sync(0xffffffffu, sa[j], 8);  sa[j] += __shfl_xor_sync(0xffffffffu, sa[j], 16);
-              sb[j] += __shfl_xor_sync(0xffffffffu, sb[j], 8);  sb[j] += __shfl_xor_sync(0xffffffffu, sb[j], 16);
+#pragma unroll
+              for (int o = 4; o < 32; o <<= 1) {
+                sa[j] += __shfl_xor_sync(0xffffffffu, sa[j], o);
+                sb[j] += __shfl_xor_sync(0xffffffffu, sb[j], o);
+              }
             }
             if (rq == 0) {
               float *dst = g.pool + ((long long)(rbase >> 5) * 2) * g.N + n;
 #pragma unroll
-              for (int j = 0; j < 4; ++j) if (n + j < g.N) { dst[j] = sa[j]; dst[g.N + j] = sb[j]; }
+              for (int j = 0; j < 4; ++j)
+                if (n + j < g.N) {
+                  dst[j] = first_is_a ? sa[j] : sb[j];
+                  dst[g.N + j] = first_is_a ? sb[j] : 0.f;
+                }
             }
           }
         } else {
-          const int cq = lane & 3, rq = lane >> 2;        // 4 column octets x 8 rows per pass
+          const int cq = lane & 1, rq = lane >> 1;        // 2 column octets x 16 rows per pass
           const int n = nc + 8 * cq;
-          float bv[8];
+          float b0[8], b1[8];
+          *reinterpret_cast<float4 *>(b0) = *reinterpret_cast<const float4 *>(sB + c0 + 8 * cq);
+          *reinterpret_cast<float4 *>(b0 + 4) = *reinterpret_cast<const float4 *>(sB + c0 + 8 * cq + 4);
+          *reinterpret_cast<float4 *>(b1) = *reinterpret_cast<const float4 *>(sB + BN + c0 + 8 * cq);
+          *reinterpret_cast<float4 *>(b1 + 4) = *reinterpret_cast<const float4 *>(sB + BN + c0 + 8 * cq + 4);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) bv[j] = (bias && n + j < g.N) ? __ldg(bias + n + j) : 0.f;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int r = 8 * i + rq, row = rbase + r;
-            const float4 a0 = *reinterpret_cast<const float4 *>(sT + r * TC_EPI_PITCH + 8 * cq);
-            const float4 a1 = *reinterpret_cast<const float4 *>(sT + r * TC_EPI_PITCH + 8 * cq + 4);
+          for (int i = 0; i < 2; ++i) {
+            const int rr = 16 * i + rq, row = rbase + rr;
+            const float4 a0 = *reinterpret_cast<const float4 *>(sT + rr * TC_EPI_PITCH + 8 * cq);
+            const float4 a1 = *reinterpret_cast<const float4 *>(sT + rr * TC_EPI_PITCH + 8 * cq + 4);
             float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const bool second = row >= split_row;
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              a[j] += second ? b1[j] : b0[j];
+              if (g.relu) a[j] = fmaxf(a[j], 0.f);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const __nv_bfloat162 h = __floats2bfloat162_rn(a[2 * q], a[2 * q + 1]);
+              hi[q] = *reinterpret_cast<const uint32_t *>(&h);
+              const float h0 = __uint_as_float(hi[q] << 16), h1 = __uint_as_float(hi[q] & 0xffff0000u);
+              const __nv_bfloat162 l = __floats2bfloat162_rn(a[2 * q] - h0, a[2 * q + 1] - h1);
+              lo[q] = *reinterpret_cast<const uint32_t *>(&l);
+            }
             if (row < g.M) {
-              const float *fb = g.frame_bias ? g.frame_bias + (long long)(row / g.rows_per_frame) * g.ldfb + n : nullptr;
-              uint32_t hi[4], lo[4];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                a[j] += bv[j];
-                if (fb && n + j < g.N) a[j] += __ldg(fb + j);
-                if (g.relu) a[j] = fmaxf(a[j], 0.f);
-              }
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const __nv_bfloat16 h0 = __float2bfloat16_rn(a[2 * q]), h1 = __float2bfloat16_rn(a[2 * q + 1]);
-                const __nv_bfloat16 l0 = __float2bfloat16_rn(a[2 * q] - __bfloat162float(h0));
-                const __nv_bfloat16 l1 = __float2bfloat16_rn(a[2 * q + 1] - __bfloat162float(h1));
-                hi[q] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-                lo[q] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
-              }
               __nv_bfloat16 *dh = g.Cb + (long long)row * g.ldcb + z * g.c_col_z + n;
               __nv_bfloat16 *dl = dh + g.c_plane;
               if (n + 7 < g.N) {
@@ -263,7 +289,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         __syncwarp();
       }
       fence_before_sync();
-      mbar_arrive(tempty_bar + as);                       // 128 arrivals release the accumulator
+      mbar_arrive(tempty_bar + as);                       // 256 arrivals release the accumulator
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
   }
@@ -428,7 +454,8 @@ int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
   if (!g.A || !g.W) { set_error("gemm_bf16x2: null operand"); return PLR2_E_NULLPTR; }
   if (g.out_mode == TC_OUT_F32 && !g.Cf) { set_error("gemm_bf16x2: null Cf"); return PLR2_E_NULLPTR; }
   if (g.out_mode == TC_OUT_BF16X2 && (!g.Cb || (g.ldcb % 8) || (g.c_col_z % 8))) { set_error("gemm_bf16x2: bf16 output needs 16-byte aligned rows"); return PLR2_E_ALIGN; }
-  if (g.out_mode == TC_OUT_POOL && (!g.pool || g.rows_per_frame < 32 || g.batch != 1)) { set_error("gemm_bf16x2: pooled output needs rows_per_frame >= 32"); return PLR2_E_UNSUPPORTED; }
+  if (g.out_mode == TC_OUT_POOL && (!g.pool || g.batch != 1)) { set_error("gemm_bf16x2: pooled output needs batch == 1"); return PLR2_E_UNSUPPORTED; }
+  if ((g.out_mode == TC_OUT_POOL || g.frame_bias) && g.rows_per_frame < TC_BM) { set_error("gemm_bf16x2: per-frame epilogues need rows_per_frame >= %d", TC_BM); return PLR2_E_UNSUPPORTED; }
   if (g.N >= 256) return launch_tc<256>(g, st);
   return launch_tc<128>(g, st);
 }

@@ -58,7 +58,7 @@ static int feat_forward(const float *pk, const NetLayout &L, const NetWorkspace 
 // ---------------------------------------------------------------------------------------------
 // Tensor-core inference path (PLR2_PREC_BF16X2, no activations kept for backward).
 static bool use_tc(int precision, int training, int n_points) {
-  return precision == PLR2_PREC_BF16X2 && !training && n_points >= 32;
+  return precision == PLR2_PREC_BF16X2 && !training && n_points >= 128;   // per-frame epilogues: <= 2 frames per 128-row tile
 }
 
 static int check_tc_ws(const NetLayout &L, void *ws, size_t bytes, int frames, int n, TcWorkspace &W) {
