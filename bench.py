@@ -227,6 +227,13 @@ def run_ours(args, world, rank, local):
     for _ in range(max(args.warmup, 3)):
         pipe.infer(*(devw[k] for k in INPUT_KEYS))
     barrier()
+    if args.profile_step:
+        # for `ncu --profile-from-start off`: exactly one device-resident step inside the capture range
+        torch.cuda.profiler.start()
+        pipe.infer(*(devw[k] for k in INPUT_KEYS))
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return
     sampler = ClockSampler(local) if rank == 0 else None
     launches0 = L.plr2_launch_count()
     L.plr2_profile_begin()
@@ -316,6 +323,8 @@ def main():
     ap.add_argument("--chunk", type=int, default=64, help="frames per launch chunk")
     ap.add_argument("--knn", default="exact", choices=["exact", "fast"])
     ap.add_argument("--cpu-frames", type=int, default=8, help="frames of the CPU baseline sample (0 = skip)")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="run ONE step between cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)")
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the reference arm")
     args = ap.parse_args()
     world, rank, local = dist_setup(args)

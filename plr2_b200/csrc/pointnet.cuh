@@ -21,6 +21,12 @@ int select_outputs(const float *raw, const NetLayout &L, const int64_t *obj, int
                    float *pred_r, float *pred_t, float *pred_c, cudaStream_t st);
 int select_outputs_bwd(float *raw, const NetLayout &L, const int64_t *obj, int rows_per_frame, size_t rows,
                        const float *g_r, const float *g_t, const float *g_c, cudaStream_t st);
+// heads.cu
+int frame_linear(const float *X, long long ldx, const float *W, long long ldw, const float *bias, float *Y,
+                 long long ldy, int M, int N, int K, int relu, int batch, long long zX, long long zW, long long zB,
+                 long long zY, cudaStream_t st);
+int head_out(const float *H, long long ldh, const float *W4, const float *b4, const int64_t *obj, int num_obj,
+             int frames, int rows_per_frame, float *pred_r, float *pred_t, float *pred_c, cudaStream_t st);
 int net_copy_params(const NetLayout &L, const plr2_param_table *P, float *packed, bool to_packed, int round,
                     cudaStream_t st);
 

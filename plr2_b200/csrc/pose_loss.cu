@@ -3,6 +3,9 @@
 // that neither the (N, M, 3) prediction tensor nor the KNN index tensor is ever materialised.
 // Reference: lib/loss.py:12-69, lib/loss_refiner.py:12-62.
 #include "knn_core.cuh"
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
 
 namespace plr2 {
 
@@ -215,25 +218,25 @@ __device__ __forceinline__ void stage_targets(const float *__restrict__ tb, int 
   }
 }
 
-// Per-thread ADD-S accumulation over the mesh points j = j_first + i*blockDim (i < QPT) ... of one
-// pose: transform, 1-NN over the staged targets, residual to the nearest target.
+// Per-thread ADD-S accumulation over the mesh points j in [j_beg, j_end) (QPT per thread and pass) of
+// one pose: transform, 1-NN over the staged targets, residual to the nearest target.
 constexpr int ADDS_QPT = 4;
-template <bool FAST, bool JAC>
+template <bool FAST, bool JAC, int QPT>
 __device__ __forceinline__ void adds_accumulate(const Pose &P, const float *__restrict__ mb,
-                                                const float *__restrict__ tb, int M, int Mp,
+                                                const float *__restrict__ tb, int M, int Mp, int j_beg, int j_end,
                                                 const float *sx, const float *sy, const float *sz,
                                                 const float *sw, float cx, float cy, float cz, Acc &A) {
   const int lane = threadIdx.x & 31;
   const int stride = blockDim.x;
-  for (int j0 = 0; j0 < M; j0 += stride * ADDS_QPT) {
-    float mx[ADDS_QPT], my[ADDS_QPT], mz[ADDS_QPT], px[ADDS_QPT], py[ADDS_QPT], pz[ADDS_QPT];
-    float nqx[ADDS_QPT], nqy[ADDS_QPT], nqz[ADDS_QPT], best[ADDS_QPT];
-    int bchunk[ADDS_QPT];
+  for (int j0 = j_beg; j0 < j_end; j0 += stride * QPT) {
+    float mx[QPT], my[QPT], mz[QPT], px[QPT], py[QPT], pz[QPT];
+    float nqx[QPT], nqy[QPT], nqz[QPT], best[QPT];
+    int bchunk[QPT];
 #pragma unroll
-    for (int i = 0; i < ADDS_QPT; ++i) {
+    for (int i = 0; i < QPT; ++i) {
       const int j = j0 + i * stride + threadIdx.x;
       mx[i] = my[i] = mz[i] = 0.f;
-      if (j < M) { mx[i] = __ldg(mb + 3 * j); my[i] = __ldg(mb + 3 * j + 1); mz[i] = __ldg(mb + 3 * j + 2); }
+      if (j < j_end) { mx[i] = __ldg(mb + 3 * j); my[i] = __ldg(mb + 3 * j + 1); mz[i] = __ldg(mb + 3 * j + 2); }
       px[i] = fmaf(P.R[0], mx[i], fmaf(P.R[1], my[i], fmaf(P.R[2], mz[i], P.s[0])));
       py[i] = fmaf(P.R[3], mx[i], fmaf(P.R[4], my[i], fmaf(P.R[5], mz[i], P.s[1])));
       pz[i] = fmaf(P.R[6], mx[i], fmaf(P.R[7], my[i], fmaf(P.R[8], mz[i], P.s[2])));
@@ -245,11 +248,13 @@ __device__ __forceinline__ void adds_accumulate(const Pose &P, const float *__re
       best[i] = CUDART_INF_F;
       bchunk[i] = 0;
     }
-    nn_scan<FAST, ADDS_QPT>(sx, sy, sz, sw, Mp, 0, nqx, nqy, nqz, best, bchunk);
+    // warps whose queries all lie beyond the slice skip the scan (warp-uniform)
+    if (j0 + (int)(threadIdx.x & ~31u) >= j_end) continue;
+    nn_scan<FAST, QPT>(sx, sy, sz, sw, Mp, 0, nqx, nqy, nqz, best, bchunk);
 #pragma unroll
-    for (int i = 0; i < ADDS_QPT; ++i) {
+    for (int i = 0; i < QPT; ++i) {
       const int j = j0 + i * stride + threadIdx.x;
-      if (j < M) {
+      if (j < j_end) {
         const int win = nn_resolve_smem<FAST>(sx, sy, sz, sw, M, bchunk[i], best[i], nqx[i], nqy[i], nqz[i], lane);
         const float tx = __ldg(tb + 3 * win), ty = __ldg(tb + 3 * win + 1), tz = __ldg(tb + 3 * win + 2);
         acc_pair<JAC>(A, px[i], py[i], pz[i], tx, ty, tz, mx[i], my[i], mz[i]);
@@ -287,7 +292,7 @@ adds_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pre
   __syncthreads();
   Acc A;
   acc_zero(A);
-  adds_accumulate<FAST, JAC>(P, mb, tb, M, Mp, sx, sy, sz, sw, cx, cy, cz, A);
+  adds_accumulate<FAST, JAC, ADDS_QPT>(P, mb, tb, M, Mp, 0, M, sx, sy, sz, sw, cx, cy, cz, A);
   acc_block_reduce<JAC>(A, red);
   if (threadIdx.x == 0) {
     const float invM = 1.0f / (float)M;
@@ -416,26 +421,34 @@ pose_select_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
 }
 
 // ---------------------------------------------------------------------------------------------
-// Refiner loss, lib/loss_refiner.py:12-62: one pose per frame, one CTA per frame.
-constexpr int REFINE_THREADS = 256;
+// Refiner loss, lib/loss_refiner.py:12-62: one pose per frame.  One thread-block CLUSTER per frame:
+// CTA s of the cluster owns mesh points [s*slice, (s+1)*slice) (each CTA stages all M targets for the
+// ADD-S scan) and the matching slices of the re-centring; the per-CTA partial sums are combined in
+// rank order by CTA 0 through distributed shared memory (deterministic, no global scratch).
+constexpr int REFINE_THREADS = 128;
+constexpr int REFINE_QPT = 3;
+constexpr int REFINE_MAX_CLUSTER = 8;
 template <bool FAST, bool JAC>
 __global__ void __launch_bounds__(REFINE_THREADS)
 refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
                    const float *__restrict__ target, const float *__restrict__ model,
                    const float *__restrict__ points, const int64_t *__restrict__ obj,
-                   const uint8_t *__restrict__ sym_lut, int num_obj, int N, int M,
+                   const uint8_t *__restrict__ sym_lut, int num_obj, int N, int M, int slice,
                    float *__restrict__ dis, float *__restrict__ new_points,
                    float *__restrict__ new_target, float *__restrict__ jac_r,
                    float *__restrict__ jac_t, float *__restrict__ pose_out) {
   extern __shared__ __align__(16) float dyn[];
   __shared__ float red[(REFINE_THREADS / 32) * 13];
-  __shared__ float sR[9], sT[3];
-  const int f = blockIdx.x;
+  __shared__ float part[13];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int S = gridDim.x, s = blockIdx.x;      // cluster = the whole x extent
+  const int f = blockIdx.y;
   const float *tb = target + (size_t)f * M * 3;
   const float *mb = model + (size_t)f * M * 3;
   Pose P;
   make_pose(pred_r + (size_t)f * 4, P);
   P.s[0] = pred_t[(size_t)f * 3]; P.s[1] = pred_t[(size_t)f * 3 + 1]; P.s[2] = pred_t[(size_t)f * 3 + 2];
+  const int j_beg = min(M, s * slice), j_end = min(M, j_beg + slice);
   Acc A;
   acc_zero(A);
   if (frame_is_sym(obj, sym_lut, num_obj, f)) {
@@ -445,9 +458,9 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
     if (FAST) { cx = __ldg(tb); cy = __ldg(tb + 1); cz = __ldg(tb + 2); }
     stage_targets<FAST>(tb, M, Mp, sx, sy, sz, sw, cx, cy, cz);
     __syncthreads();
-    adds_accumulate<FAST, JAC>(P, mb, tb, M, Mp, sx, sy, sz, sw, cx, cy, cz, A);
+    adds_accumulate<FAST, JAC, REFINE_QPT>(P, mb, tb, M, Mp, j_beg, j_end, sx, sy, sz, sw, cx, cy, cz, A);
   } else {
-    for (int j = threadIdx.x; j < M; j += blockDim.x) {
+    for (int j = j_beg + threadIdx.x; j < j_end; j += blockDim.x) {
       const float mx = __ldg(mb + 3 * j), my = __ldg(mb + 3 * j + 1), mz = __ldg(mb + 3 * j + 2);
       const float px = fmaf(P.R[0], mx, fmaf(P.R[1], my, fmaf(P.R[2], mz, P.s[0])));
       const float py = fmaf(P.R[3], mx, fmaf(P.R[4], my, fmaf(P.R[5], mz, P.s[1])));
@@ -457,6 +470,24 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
   }
   acc_block_reduce<JAC>(A, red);
   if (threadIdx.x == 0) {
+    part[0] = A.dis;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) part[1 + i] = JAC ? A.gs[i] : 0.f;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) part[4 + i] = JAC ? A.G[i] : 0.f;
+  }
+  cluster.sync();
+  if (s == 0 && threadIdx.x == 0) {
+    for (int r = 1; r < S; ++r) {                 // fixed rank order
+      const float *rp = cluster.map_shared_rank(part, r);
+      A.dis += rp[0];
+      if (JAC) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) A.gs[i] += rp[1 + i];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) A.G[i] += rp[4 + i];
+      }
+    }
     const float invM = 1.0f / (float)M;
     dis[f] = A.dis * invM;
     if (JAC) {
@@ -469,10 +500,6 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
 #pragma unroll
       for (int i = 0; i < 3; ++i) jac_t[(size_t)f * 3 + i] = A.gs[i] * invM;
     }
-#pragma unroll
-    for (int i = 0; i < 9; ++i) sR[i] = P.R[i];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) sT[i] = P.s[i];
     if (pose_out) {
 #pragma unroll
       for (int i = 0; i < 9; ++i) pose_out[(size_t)f * 12 + i] = P.R[i];
@@ -480,9 +507,16 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
       for (int i = 0; i < 3; ++i) pose_out[(size_t)f * 12 + 9 + i] = P.s[i];
     }
   }
-  __syncthreads();
-  if (new_points) recentre_rows(points + (size_t)f * N * 3, new_points + (size_t)f * N * 3, N, sR, sT);
-  if (new_target) recentre_rows(tb, new_target + (size_t)f * M * 3, M, sR, sT);
+  // re-centring (lib/loss_refiner.py:50-59): every CTA takes its share of the rows
+  if (new_points) {
+    const int per = (N + S - 1) / S, a = min(N, s * per), b = min(N, a + per);
+    recentre_rows(points + ((size_t)f * N + a) * 3, new_points + ((size_t)f * N + a) * 3, b - a, P.R, P.s);
+  }
+  if (new_target) {
+    const int per = (M + S - 1) / S, a = min(M, s * per), b = min(M, a + per);
+    recentre_rows(tb + (size_t)a * 3, new_target + ((size_t)f * M + a) * 3, b - a, P.R, P.s);
+  }
+  cluster.sync();        // partials must stay mapped until CTA 0 has read them
 }
 
 static int set_dyn_smem(const void *fn, size_t bytes) {
@@ -573,7 +607,7 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
                                     int n_mesh, int knn_mode, float *dis, float *new_points,
                                     float *new_target, float *jac_r, float *jac_t, float *pose_out,
                                     void *stream) {
-  if (frames < 0 || n_points < 0 || n_mesh <= 0) { set_error("plr2_refine_loss_fwd: bad shape"); return PLR2_E_SHAPE; }
+  if (frames < 0 || n_points < 0 || n_mesh <= 0 || frames > 65535) { set_error("plr2_refine_loss_fwd: bad shape"); return PLR2_E_SHAPE; }
   if (frames == 0) return 0;
   if (!pred_r || !pred_t || !target || !model_points || !dis || (new_points && !points) ||
       ((jac_r == nullptr) != (jac_t == nullptr))) { set_error("plr2_refine_loss_fwd: null pointer"); return PLR2_E_NULLPTR; }
@@ -582,11 +616,31 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
   const bool fast = knn_mode == PLR2_KNN_FAST, jac = jac_r != nullptr;
   const bool may_sym = sym_lut != nullptr && obj != nullptr;
   const size_t smem = may_sym ? (size_t)knn_pad(n_mesh) * sizeof(float) * (fast ? 4 : 3) : 0;
-#define ARGS pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, dis, new_points, new_target, jac_r, jac_t, pose_out
-  if (fast && jac) PLR2_LAUNCH_ADDS(refine_loss_kernel, true, true, frames, REFINE_THREADS, smem, st, ARGS);
-  else if (fast) PLR2_LAUNCH_ADDS(refine_loss_kernel, true, false, frames, REFINE_THREADS, smem, st, ARGS);
-  else if (jac) PLR2_LAUNCH_ADDS(refine_loss_kernel, false, true, frames, REFINE_THREADS, smem, st, ARGS);
-  else PLR2_LAUNCH_ADDS(refine_loss_kernel, false, false, frames, REFINE_THREADS, smem, st, ARGS);
-#undef ARGS
+  // cluster size: one full pass of REFINE_THREADS*REFINE_QPT mesh points per CTA, at most 8 CTAs
+  const int pass = REFINE_THREADS * REFINE_QPT;
+  int S = (n_mesh + pass - 1) / pass;
+  if (S > REFINE_MAX_CLUSTER) S = REFINE_MAX_CLUSTER;
+  int slice = (n_mesh + S - 1) / S;
+  slice = (slice + pass - 1) / pass * pass;
+  void (*kfn)(const float *, const float *, const float *, const float *, const float *, const int64_t *,
+              const uint8_t *, int, int, int, int, float *, float *, float *, float *, float *, float *);
+  if (fast && jac) kfn = refine_loss_kernel<true, true>;
+  else if (fast) kfn = refine_loss_kernel<true, false>;
+  else if (jac) kfn = refine_loss_kernel<false, true>;
+  else kfn = refine_loss_kernel<false, false>;
+  int rc = set_dyn_smem((const void *)kfn, smem);
+  if (rc) return rc;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(S, frames, 1);
+  cfg.blockDim = dim3(REFINE_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = S; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kfn, pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj,
+                                     n_points, n_mesh, slice, dis, new_points, new_target, jac_r, jac_t, pose_out);
+  if (e != cudaSuccess) { set_error("plr2_refine_loss_fwd: launch: %s", cudaGetErrorString(e)); return (int)e; }
   return check_launch("plr2_refine_loss_fwd");
 }

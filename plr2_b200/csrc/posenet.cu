@@ -108,9 +108,8 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   const long long wplane = (long long)L.total;
   __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *h1 = (__nv_bfloat16 *)W.h1, *h2 = (__nv_bfloat16 *)W.h2;
   RC(feat_forward_tc(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, st));
-  GemmArgs s = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.hb, 1920, F, 1920, 1024);     // per-frame bias (FP32)
-  s.bias = pk + L.h1b;
-  RC(gemm_f32(s, 1, st));
+  // per-frame bias of conv1_{r,t,c}: hb[F,1920] = ap W1[:,384:]^T + b1 (FP32)
+  RC(frame_linear(W.ap, 1024, pk + L.h1ap, 1024, pk + L.h1b, W.hb, 1920, F, 1920, 1024, 0, 1, 0, 0, 0, 0, st));
   TcGemm g;
   g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.h1pf; g.ldw = 384; g.w_plane = wplane;
   g.M = R; g.N = 1920; g.K = 384; g.frame_bias = W.hb; g.rows_per_frame = N; g.ldfb = 1920; g.relu = 1;
@@ -128,14 +127,8 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   g.bias = pk + L.h3b; g.relu = 1;
   g.out_mode = TC_OUT_F32; g.Cf = W.h3; g.ldc = 384;
   RC(gemm_bf16x2(g, st));                                                            // conv3_* (FP32 out)
-  size_t row = 0;
-  for (int h = 0; h < 3; ++h) {                                                      // conv4_* (FP32 SIMT)
-    GemmArgs c = gemm_nt(W.h3 + h * 128, 384, pk + L.h4w + row * 128, 128, W.out + L.oc[h], L.ldo, R, L.on[h], 128);
-    c.bias = pk + L.h4b + row;
-    RC(gemm_f32(c, 1, st));
-    row += L.on[h];
-  }
-  RC(select_outputs(W.out, L, obj, N, (size_t)R, pred_r, pred_t, pred_c, st));
+  // conv4_{r,t,c} for the frame's class only + sigmoid (FP32 SIMT)
+  RC(head_out(W.h3, 384, pk + L.h4w, pk + L.h4b, obj, L.O, F, N, pred_r, pred_t, pred_c, st));
   return 0;
 }
 
@@ -143,20 +136,10 @@ static int refiner_forward_tc(const float *pk, const NetLayout &L, const TcWorks
                               const float *emb, const int64_t *obj, int F, int N, float *pred_r, float *pred_t,
                               cudaStream_t st) {
   RC(feat_forward_tc(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, st));
-  GemmArgs g = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.hb, 1024, F, 1024, 1024);
-  g.bias = pk + L.h1b; g.relu = 1;
-  RC(gemm_f32(g, 1, st));
-  g = gemm_nt(W.hb, 1024, pk + L.h2w, 512, W.h3, 256, F, 128, 512);
-  g.bias = pk + L.h2b; g.relu = 1; g.batch = 2; g.zA = 512; g.zB = 128 * 512; g.zC = 128; g.zbias = 128;
-  RC(gemm_f32(g, 1, st));
-  size_t row = 0;
-  for (int h = 0; h < 2; ++h) {
-    g = gemm_nt(W.h3 + h * 128, 256, pk + L.h4w + row * 128, 128, W.out + L.oc[h], L.ldo, F, L.on[h], 128);
-    g.bias = pk + L.h4b + row;
-    RC(gemm_f32(g, 1, st));
-    row += L.on[h];
-  }
-  RC(select_outputs(W.out, L, obj, 1, (size_t)F, pred_r, pred_t, nullptr, st));
+  // Linear 1024->512 (x2 heads), 512->128 (x2), 128->7 for the frame's class: M = frames, FP32 SIMT
+  RC(frame_linear(W.ap, 1024, pk + L.h1ap, 1024, pk + L.h1b, W.hb, 1024, F, 1024, 1024, 1, 1, 0, 0, 0, 0, st));
+  RC(frame_linear(W.hb, 1024, pk + L.h2w, 512, pk + L.h2b, W.h3, 256, F, 128, 512, 1, 2, 512, 128 * 512, 128, 128, st));
+  RC(head_out(W.h3, 256, pk + L.h4w, pk + L.h4b, obj, L.O, F, 1, pred_r, pred_t, nullptr, st));
   return 0;
 }
 
