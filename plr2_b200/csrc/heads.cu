@@ -11,9 +11,11 @@ namespace plr2 {
 
 // ---------------------------------------------------------------------------------------------
 constexpr int FLN_ROWS = 64;      // rows (frames) per CTA: 2 per lane
-constexpr int FLN_COLS = 16;      // output columns per CTA: 4 per warp
+constexpr int FLN_COLS = 16;      // output columns per CTA: 4 per warp of a K group
 constexpr int FLN_KC = 64;        // K chunk staged in shared memory
-constexpr int FLN_THREADS = 128;
+constexpr int FLN_KG = 2;         // K groups per CTA (4 warps each), partial sums combined at the end
+constexpr int FLN_GT = 128;       // threads per K group
+constexpr int FLN_THREADS = FLN_KG * FLN_GT;
 
 struct FrameLinearArgs {
   const float *X; long long ldx;
@@ -26,12 +28,16 @@ struct FrameLinearArgs {
 
 __global__ void __launch_bounds__(FLN_THREADS)
 frame_linear_kernel(const FrameLinearArgs g) {
-  __shared__ __align__(16) float Xs[2][FLN_KC][FLN_ROWS + 1];   // [k][row]
-  __shared__ __align__(16) float Ws[2][FLN_KC][FLN_COLS];       // [k][col]
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ __align__(16) float Xs[FLN_KG][FLN_KC][FLN_ROWS + 1];   // [group][k][row]
+  __shared__ __align__(16) float Ws[FLN_KG][FLN_KC][FLN_COLS];       // [group][k][col]
+  const int grp = threadIdx.x / FLN_GT, tid = threadIdx.x - grp * FLN_GT;
+  const int lane = tid & 31, warp = tid >> 5;
   const int n0 = blockIdx.x * FLN_COLS, m0 = blockIdx.y * FLN_ROWS, z = blockIdx.z;
   const float *X = g.X + z * g.zX, *W = g.W + z * g.zW;
   float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+  // this group's K range: whole chunks, split evenly
+  const int nchunks = (g.K + FLN_KC - 1) / FLN_KC;
+  const int c_beg = nchunks * grp / FLN_KG, c_end = nchunks * (grp + 1) / FLN_KG;
 
   // global -> registers for one K chunk: X tile 64 rows x 64 k = 1024 float4 (8 per thread),
   // W tile 16 cols x 64 k = 256 float4 (2 per thread); rows are K-contiguous in both.
@@ -41,7 +47,7 @@ frame_linear_kernel(const FrameLinearArgs g) {
   auto load_chunk = [&](int k0) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const int e = tid + i * FLN_THREADS, r = e >> 4, kq = (e & 15) * 4;
+      const int e = tid + i * FLN_GT, r = e >> 4, kq = (e & 15) * 4;
       const int m = m0 + r, k = k0 + kq;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (m < g.M) {
@@ -58,7 +64,7 @@ frame_linear_kernel(const FrameLinearArgs g) {
     }
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
-      const int e = tid + i * FLN_THREADS, c = e >> 4, kq = (e & 15) * 4;
+      const int e = tid + i * FLN_GT, c = e >> 4, kq = (e & 15) * 4;
       const int n = n0 + c, k = k0 + kq;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (n < g.N) {
@@ -74,41 +80,47 @@ frame_linear_kernel(const FrameLinearArgs g) {
       wr[i] = v;
     }
   };
-  auto store_chunk = [&](int b) {
+  auto store_chunk = [&]() {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const int e = tid + i * FLN_THREADS, r = e >> 4, kq = (e & 15) * 4;
-      Xs[b][kq][r] = xr[i].x; Xs[b][kq + 1][r] = xr[i].y; Xs[b][kq + 2][r] = xr[i].z; Xs[b][kq + 3][r] = xr[i].w;
+      const int e = tid + i * FLN_GT, r = e >> 4, kq = (e & 15) * 4;
+      Xs[grp][kq][r] = xr[i].x; Xs[grp][kq + 1][r] = xr[i].y; Xs[grp][kq + 2][r] = xr[i].z; Xs[grp][kq + 3][r] = xr[i].w;
     }
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
-      const int e = tid + i * FLN_THREADS, c = e >> 4, kq = (e & 15) * 4;
-      Ws[b][kq][c] = wr[i].x; Ws[b][kq + 1][c] = wr[i].y; Ws[b][kq + 2][c] = wr[i].z; Ws[b][kq + 3][c] = wr[i].w;
+      const int e = tid + i * FLN_GT, c = e >> 4, kq = (e & 15) * 4;
+      Ws[grp][kq][c] = wr[i].x; Ws[grp][kq + 1][c] = wr[i].y; Ws[grp][kq + 2][c] = wr[i].z; Ws[grp][kq + 3][c] = wr[i].w;
     }
   };
+  auto group_sync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(FLN_GT) : "memory"); };
 
-  load_chunk(0);
-  store_chunk(0);
-  __syncthreads();
-  int b = 0;
-  for (int k0 = 0; k0 < g.K; k0 += FLN_KC) {
-    const bool more = k0 + FLN_KC < g.K;
-    if (more) load_chunk(k0 + FLN_KC);
+  if (c_beg < c_end) load_chunk(c_beg * FLN_KC);
+  for (int c = c_beg; c < c_end; ++c) {
+    store_chunk();
+    group_sync();
+    if (c + 1 < c_end) load_chunk((c + 1) * FLN_KC);       // in flight while this chunk is consumed
 #pragma unroll 8
     for (int k = 0; k < FLN_KC; ++k) {
-      const float x0 = Xs[b][k][lane], x1 = Xs[b][k][lane + 32];
-      const float4 w = *reinterpret_cast<const float4 *>(&Ws[b][k][warp * 4]);
+      const float x0 = Xs[grp][k][lane], x1 = Xs[grp][k][lane + 32];
+      const float4 w = *reinterpret_cast<const float4 *>(&Ws[grp][k][warp * 4]);
       acc0[0] = fmaf(x0, w.x, acc0[0]); acc0[1] = fmaf(x0, w.y, acc0[1]);
       acc0[2] = fmaf(x0, w.z, acc0[2]); acc0[3] = fmaf(x0, w.w, acc0[3]);
       acc1[0] = fmaf(x1, w.x, acc1[0]); acc1[1] = fmaf(x1, w.y, acc1[1]);
       acc1[2] = fmaf(x1, w.z, acc1[2]); acc1[3] = fmaf(x1, w.w, acc1[3]);
     }
-    if (more) {
-      store_chunk(b ^ 1);
-      __syncthreads();
-      b ^= 1;
-    }
+    group_sync();
   }
+  // combine the K groups through shared memory (fixed order: group 0 + group 1)
+  __syncthreads();
+  float *part = &Xs[0][0][0];                               // >= 128 threads x 8 floats
+  if (grp == 1) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { part[(j * 2) * FLN_GT + tid] = acc0[j]; part[(j * 2 + 1) * FLN_GT + tid] = acc1[j]; }
+  }
+  __syncthreads();
+  if (grp != 0) return;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { acc0[j] += part[(j * 2) * FLN_GT + tid]; acc1[j] += part[(j * 2 + 1) * FLN_GT + tid]; }
   const float *bias = g.bias ? g.bias + z * g.zB : nullptr;
   float *Y = g.Y + z * g.zY;
 #pragma unroll

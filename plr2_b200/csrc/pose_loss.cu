@@ -162,6 +162,80 @@ add_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred
   }
 }
 
+// Inference variant (no Jacobians): thread = 4 hypotheses x 1/8 of the mesh, so that one broadcast
+// LDS.128 pair (mesh point, target point) feeds 4 pair evaluations; sqrt.approx (<= 1 ulp-level error,
+// far inside the rtol 1e-3 budget) instead of the IEEE sequence.
+constexpr int ADDI_H = 4, ADDI_S = 8, ADDI_THREADS = 256;
+constexpr int ADDI_NPB = (ADDI_THREADS / ADDI_S) * ADDI_H;   // 128 hypotheses per block
+
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+__global__ void __launch_bounds__(ADDI_THREADS)
+add_dis_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
+               const float *__restrict__ target, const float *__restrict__ model,
+               const float *__restrict__ points, const int64_t *__restrict__ obj,
+               const uint8_t *__restrict__ sym_lut, int num_obj, int N, int M, int skip_sym,
+               float *__restrict__ dis) {
+  const int f = blockIdx.y;
+  if (skip_sym && frame_is_sym(obj, sym_lut, num_obj, f)) return;  // handled by adds_loss_kernel
+  __shared__ float4 sm[ADD_JT];
+  __shared__ float4 st[ADD_JT];
+  const int tid = threadIdx.x;
+  const int slice = tid & (ADDI_S - 1);
+  const int n0 = blockIdx.x * ADDI_NPB + (tid >> 3) * ADDI_H;
+  float R[ADDI_H][9], sft[ADDI_H][3], acc[ADDI_H];
+#pragma unroll
+  for (int h = 0; h < ADDI_H; ++h) {
+    const size_t fn = (size_t)f * N + min(n0 + h, N - 1);
+    Pose P;
+    make_pose(pred_r + fn * 4, P);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[h][i] = P.R[i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) sft[h][i] = points[fn * 3 + i] + pred_t[fn * 3 + i];   // lib/loss.py:37
+    acc[h] = 0.f;
+  }
+  const float *mb = model + (size_t)f * M * 3;
+  const float *tb = target + (size_t)f * M * 3;
+  for (int j0 = 0; j0 < M; j0 += ADD_JT) {
+    const int jt = min(ADD_JT, M - j0);
+    __syncthreads();
+    for (int j = tid; j < jt; j += ADDI_THREADS) {
+      const float *m = mb + (size_t)(j0 + j) * 3;
+      const float *t = tb + (size_t)(j0 + j) * 3;
+      sm[j] = make_float4(__ldg(m), __ldg(m + 1), __ldg(m + 2), 0.f);
+      st[j] = make_float4(__ldg(t), __ldg(t + 1), __ldg(t + 2), 0.f);
+    }
+    __syncthreads();
+#pragma unroll 2
+    for (int j = slice; j < jt; j += ADDI_S) {
+      const float4 m = sm[j], t = st[j];
+#pragma unroll
+      for (int h = 0; h < ADDI_H; ++h) {
+        const float dx = fmaf(R[h][0], m.x, fmaf(R[h][1], m.y, fmaf(R[h][2], m.z, sft[h][0]))) - t.x;
+        const float dy = fmaf(R[h][3], m.x, fmaf(R[h][4], m.y, fmaf(R[h][5], m.z, sft[h][1]))) - t.y;
+        const float dz = fmaf(R[h][6], m.x, fmaf(R[h][7], m.y, fmaf(R[h][8], m.z, sft[h][2]))) - t.z;
+        acc[h] += sqrt_approx(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
+      }
+    }
+  }
+#pragma unroll
+  for (int h = 0; h < ADDI_H; ++h) {
+#pragma unroll
+    for (int o = 1; o < ADDI_S; o <<= 1) acc[h] += __shfl_xor_sync(0xffffffffu, acc[h], o);
+  }
+  if (slice == 0) {
+    const float invM = 1.0f / (float)M;
+#pragma unroll
+    for (int h = 0; h < ADDI_H; ++h)
+      if (n0 + h < N) dis[(size_t)f * N + n0 + h] = acc[h] * invM;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Block-wide sum of an Acc; result valid in thread 0.  `red` needs (blockDim/32)*13 floats.
 template <bool JAC>
@@ -425,9 +499,78 @@ pose_select_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
 // CTA s of the cluster owns mesh points [s*slice, (s+1)*slice) (each CTA stages all M targets for the
 // ADD-S scan) and the matching slices of the re-centring; the per-CTA partial sums are combined in
 // rank order by CTA 0 through distributed shared memory (deterministic, no global scratch).
-constexpr int REFINE_THREADS = 128;
+constexpr int REFINE_RS = 3;                       // reference ranges scanned concurrently per query
+constexpr int REFINE_QT = 96;                      // query threads per range (3 warps)
+constexpr int REFINE_THREADS = REFINE_RS * REFINE_QT;
 constexpr int REFINE_QPT = 3;
+constexpr int REFINE_PASS = REFINE_QT * REFINE_QPT;   // 288 queries per CTA pass
 constexpr int REFINE_MAX_CLUSTER = 8;
+
+// ADD-S accumulation for the refiner: thread (r, qt) scans reference range r for REFINE_QPT queries;
+// the per-range candidates meet in shared memory and range-0 threads finish (lowest range wins ties,
+// so the lowest reference index still wins, knn.cu:158).
+template <bool FAST, bool JAC>
+__device__ __forceinline__ void adds_accumulate_split(const Pose &P, const float *__restrict__ mb,
+                                                      const float *__restrict__ tb, int M, int Mp, int j_beg,
+                                                      int j_end, const float *sx, const float *sy, const float *sz,
+                                                      const float *sw, float cx, float cy, float cz,
+                                                      float (*cand_d)[REFINE_PASS], int (*cand_c)[REFINE_PASS], Acc &A) {
+  const int lane = threadIdx.x & 31;
+  const int r = threadIdx.x / REFINE_QT, qt = threadIdx.x - r * REFINE_QT;
+  const int nchunk = Mp / KNN_CHUNK;
+  const int c_beg = (int)((long long)nchunk * r / REFINE_RS), c_end = (int)((long long)nchunk * (r + 1) / REFINE_RS);
+  for (int j0 = j_beg; j0 < j_end; j0 += REFINE_PASS) {
+    float mx[REFINE_QPT], my[REFINE_QPT], mz[REFINE_QPT], px[REFINE_QPT], py[REFINE_QPT], pz[REFINE_QPT];
+    float nqx[REFINE_QPT], nqy[REFINE_QPT], nqz[REFINE_QPT], best[REFINE_QPT];
+    int bchunk[REFINE_QPT];
+#pragma unroll
+    for (int i = 0; i < REFINE_QPT; ++i) {
+      const int j = j0 + i * REFINE_QT + qt;
+      mx[i] = my[i] = mz[i] = 0.f;
+      if (j < j_end) { mx[i] = __ldg(mb + 3 * j); my[i] = __ldg(mb + 3 * j + 1); mz[i] = __ldg(mb + 3 * j + 2); }
+      px[i] = fmaf(P.R[0], mx[i], fmaf(P.R[1], my[i], fmaf(P.R[2], mz[i], P.s[0])));
+      py[i] = fmaf(P.R[3], mx[i], fmaf(P.R[4], my[i], fmaf(P.R[5], mz[i], P.s[1])));
+      pz[i] = fmaf(P.R[6], mx[i], fmaf(P.R[7], my[i], fmaf(P.R[8], mz[i], P.s[2])));
+      if (FAST) {
+        nqx[i] = -2.f * (px[i] - cx); nqy[i] = -2.f * (py[i] - cy); nqz[i] = -2.f * (pz[i] - cz);
+      } else {
+        nqx[i] = -px[i]; nqy[i] = -py[i]; nqz[i] = -pz[i];
+      }
+      best[i] = CUDART_INF_F;
+      bchunk[i] = c_beg;
+    }
+    if (j0 + (qt & ~31) < j_end)        // warp-uniform: warps whose queries all lie beyond the slice skip the scan
+      nn_scan<FAST, REFINE_QPT>(sx + c_beg * KNN_CHUNK, sy + c_beg * KNN_CHUNK, sz + c_beg * KNN_CHUNK,
+                                sw + (FAST ? c_beg * KNN_CHUNK : 0), (c_end - c_beg) * KNN_CHUNK, c_beg, nqx, nqy, nqz,
+                                best, bchunk);
+#pragma unroll
+    for (int i = 0; i < REFINE_QPT; ++i) {
+      cand_d[r][i * REFINE_QT + qt] = best[i];
+      cand_c[r][i * REFINE_QT + qt] = bchunk[i];
+    }
+    __syncthreads();
+    if (r == 0) {
+#pragma unroll
+      for (int i = 0; i < REFINE_QPT; ++i) {
+        const int j = j0 + i * REFINE_QT + qt;
+        if (j < j_end) {
+          float b = best[i];
+          int bc = bchunk[i];
+#pragma unroll
+          for (int rr = 1; rr < REFINE_RS; ++rr) {
+            const float d = cand_d[rr][i * REFINE_QT + qt];
+            if (d < b) { b = d; bc = cand_c[rr][i * REFINE_QT + qt]; }
+          }
+          const int win = nn_resolve_smem<FAST>(sx, sy, sz, sw, M, bc, b, nqx[i], nqy[i], nqz[i], lane);
+          const float tx = __ldg(tb + 3 * win), ty = __ldg(tb + 3 * win + 1), tz = __ldg(tb + 3 * win + 2);
+          acc_pair<JAC>(A, px[i], py[i], pz[i], tx, ty, tz, mx[i], my[i], mz[i]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
 template <bool FAST, bool JAC>
 __global__ void __launch_bounds__(REFINE_THREADS)
 refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
@@ -440,6 +583,8 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
   extern __shared__ __align__(16) float dyn[];
   __shared__ float red[(REFINE_THREADS / 32) * 13];
   __shared__ float part[13];
+  __shared__ float cand_d[REFINE_RS][REFINE_PASS];
+  __shared__ int cand_c[REFINE_RS][REFINE_PASS];
   cg::cluster_group cluster = cg::this_cluster();
   const int S = gridDim.x, s = blockIdx.x;      // cluster = the whole x extent
   const int f = blockIdx.y;
@@ -458,7 +603,7 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
     if (FAST) { cx = __ldg(tb); cy = __ldg(tb + 1); cz = __ldg(tb + 2); }
     stage_targets<FAST>(tb, M, Mp, sx, sy, sz, sw, cx, cy, cz);
     __syncthreads();
-    adds_accumulate<FAST, JAC, REFINE_QPT>(P, mb, tb, M, Mp, j_beg, j_end, sx, sy, sz, sw, cx, cy, cz, A);
+    adds_accumulate_split<FAST, JAC>(P, mb, tb, M, Mp, j_beg, j_end, sx, sy, sz, sw, cx, cy, cz, cand_d, cand_c, A);
   } else {
     for (int j = j_beg + threadIdx.x; j < j_end; j += blockDim.x) {
       const float mx = __ldg(mb + 3 * j), my = __ldg(mb + 3 * j + 1), mz = __ldg(mb + 3 * j + 2);
@@ -559,8 +704,10 @@ extern "C" int plr2_pose_loss_fwd(const float *pred_r, const float *pred_t, cons
   dim3 g1((n_points + ADD_NPB - 1) / ADD_NPB, frames);
   if (jac)
     add_loss_kernel<true><<<g1, ADD_SLICES * ADD_NPB, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, may_sym ? 1 : 0, dis, jac_r, jac_t);
-  else
-    add_loss_kernel<false><<<g1, ADD_SLICES * ADD_NPB, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, may_sym ? 1 : 0, dis, jac_r, jac_t);
+  else {
+    dim3 gi((n_points + ADDI_NPB - 1) / ADDI_NPB, frames);
+    add_dis_kernel<<<gi, ADDI_THREADS, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, may_sym ? 1 : 0, dis);
+  }
   if (may_sym) {
     if (n_mesh > 8192) { set_error("plr2_pose_loss_fwd: ADD-S needs n_mesh <= 8192 (got %d)", n_mesh); return PLR2_E_UNSUPPORTED; }
     const bool fast = knn_mode == PLR2_KNN_FAST;
@@ -617,7 +764,7 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
   const bool may_sym = sym_lut != nullptr && obj != nullptr;
   const size_t smem = may_sym ? (size_t)knn_pad(n_mesh) * sizeof(float) * (fast ? 4 : 3) : 0;
   // cluster size: one full pass of REFINE_THREADS*REFINE_QPT mesh points per CTA, at most 8 CTAs
-  const int pass = REFINE_THREADS * REFINE_QPT;
+  const int pass = REFINE_PASS;
   int S = (n_mesh + pass - 1) / pass;
   if (S > REFINE_MAX_CLUSTER) S = REFINE_MAX_CLUSTER;
   int slice = (n_mesh + S - 1) / S;

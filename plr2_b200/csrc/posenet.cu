@@ -82,9 +82,10 @@ static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspac
   g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.c2w; g.ldw = 64; g.w_plane = wplane;
   g.M = R; g.N = 128; g.K = 64; g.bias = pk + L.c2b; g.relu = 1;
   g.out_mode = TC_OUT_BF16X2; g.Cb = pf + 128; g.ldcb = 384; g.c_plane = W.pf_plane;
-  RC(gemm_bf16x2(g, st));                                                            // conv2
-  g.A = pf + 64; g.W = wb + L.e2w; g.bias = pk + L.e2b; g.Cb = pf + 256;
-  RC(gemm_bf16x2(g, st));                                                            // e_conv2
+  // conv2 and e_conv2 in one launch (batch = branch): x1 -> pf[:,128:256), e1 -> pf[:,256:384)
+  g.batch = 2; g.a_col_z = 64; g.b_row_z = (int)((L.e2w - L.c2w) / 64); g.c_col_z = 128;
+  g.bias_z = (long long)(L.e2b - L.c2b);
+  RC(gemm_bf16x2(g, st));
   g = TcGemm();
   g.A = L.c5k == 256 ? pf + 128 : pf; g.lda = 384; g.a_plane = W.pf_plane;
   g.W = wb + L.c5w; g.ldw = L.c5k; g.w_plane = wplane;
