@@ -19,6 +19,7 @@
 #include "tc_ptx.cuh"
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include <vector>
 
 namespace plr2 {
@@ -32,20 +33,30 @@ constexpr int TC_EPI_COLS = 16;                        // columns per epilogue c
 constexpr int TC_EPI_PITCH = 20;                       // floats per staged row (16 + 4 pad: conflict-free float4 stores)
 constexpr int TC_EPI_FLOATS = 32 * TC_EPI_PITCH;        // per epilogue warp
 
-template <int BN> struct TcCfg {
-  static constexpr int STAGES = BN == 256 ? 2 : 3;
+// BN = output-tile width, NPROD = 3 (hi+lo activations) | 2 (hi-only activations: X_hi W_hi + X_hi W_lo),
+// CG = 1 (one CTA per tile of 128 rows) | 2 (CTA pair, cta_group::2: one 256-row tile per pair, each CTA
+// stages its own 128 rows of X and HALF of the W tile, so the L2->smem traffic per FLOP drops by a third
+// and a third pipeline stage fits).
+template <int BN, int NPROD, int CG> struct TcCfg {
   static constexpr int A_BYTES = TC_BM * TC_BK * 2;            // one plane
-  static constexpr int B_BYTES = BN * TC_BK * 2;
-  static constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
+  static constexpr int B_ROWS = BN / CG;                       // W rows staged by this CTA
+  static constexpr int B_BYTES = B_ROWS * TC_BK * 2;
+  static constexpr int A_PLANES = NPROD == 3 ? 2 : 1;
+  static constexpr int STAGE_BYTES = A_PLANES * A_BYTES + 2 * B_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;                      // two accumulator stages
   static constexpr int EPI_BYTES = TC_EPI_WARPS * TC_EPI_FLOATS * 4;          // transpose slabs
   static constexpr int BIAS_BYTES = 2 * 2 * BN * 4;                          // [acc stage][frame a|b][BN] staged bias
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + EPI_BYTES + BIAS_BYTES;
+  static constexpr int FIXED_BYTES = 1024 /*align slack*/ + 256 /*barriers*/ + EPI_BYTES + BIAS_BYTES;
+  static constexpr int STAGES_FIT = (232448 - FIXED_BYTES) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES;
+  static_assert(STAGES >= 2, "pipeline needs two stages");
+  static_assert(2 * STAGES + 4 <= 30, "barrier area");
 };
 
 struct TcKernelArgs {
   int M, N, K, batch;
-  int m_tiles, n_tiles;
+  int m_tiles, n_tiles;          // m_tiles counts tiles of 128*CG rows
   int a_col_z, b_row_z;          // per-batch offsets: A K-coordinate (elements), W row
   long long c_col_z, bias_z;
   const float *bias, *frame_bias;
@@ -56,22 +67,25 @@ struct TcKernelArgs {
   float *pool;                   // [ceil(M/32)][2][N]
 };
 
-template <int BN>
+template <int BN, int NPROD, int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                    const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
                    const TcKernelArgs g) {
-  using Cfg = TcCfg<BN>;
+  using Cfg = TcCfg<BN, NPROD, CG>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
-  uint64_t *full_bar = bars;                       // [STAGES]  TMA -> MMA
+  uint64_t *full_bar = bars;                       // [STAGES]  TMA -> MMA   (CG == 2: the leader's is used)
   uint64_t *empty_bar = bars + Cfg::STAGES;        // [STAGES]  MMA -> TMA
   uint64_t *tfull_bar = bars + 2 * Cfg::STAGES;    // [2]       MMA -> epilogue
-  uint64_t *tempty_bar = tfull_bar + 2;            // [2]       epilogue -> MMA
+  uint64_t *tempty_bar = tfull_bar + 2;            // [2]       epilogue -> MMA (CG == 2: the leader's is used)
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = CG == 2 ? (int)cluster_ctarank() : 0;      // 0 = leader (issues the MMAs)
+  const int unit = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;       // tile-processing unit (CTA or pair)
+  const int n_units = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   const int num_kb = g.K / TC_BK;
   const int tiles_per_z = g.m_tiles * g.n_tiles;
   const int num_tiles = tiles_per_z * g.batch;
@@ -80,64 +94,82 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     prefetch_tensormap(&tmA_hi); prefetch_tensormap(&tmA_lo);
     prefetch_tensormap(&tmB_hi); prefetch_tensormap(&tmB_lo);
     for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar + s, 1); mbar_init(tempty_bar + s, 32 * TC_EPI_WARPS); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar + s, 1); mbar_init(tempty_bar + s, CG * TC_EPI_WARPS); }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  if (warp == 2) {
+    if (CG == 2) tmem_alloc_cg2(tmem_slot, Cfg::TMEM_COLS);
+    else tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  }
   fence_before_sync();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
+    // ===================== TMA producer (both CTAs of a pair) =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = unit; t < num_tiles; t += n_units) {
         const int z = t / tiles_per_z, r = t % tiles_per_z;
-        const int m0 = (r / g.n_tiles) * TC_BM, n0 = (r % g.n_tiles) * BN;
+        const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = (r % g.n_tiles) * BN + rank * Cfg::B_ROWS;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty_bar + stage, phase ^ 1);
           uint8_t *sA = smem + stage * Cfg::STAGE_BYTES;
-          uint8_t *sB = sA + 2 * Cfg::A_BYTES;
-          mbar_arrive_expect_tx(full_bar + stage, Cfg::STAGE_BYTES);
+          uint8_t *sB = sA + Cfg::A_PLANES * Cfg::A_BYTES;
           const int ka = z * g.a_col_z + kb * TC_BK, kw = kb * TC_BK, rw = z * g.b_row_z + n0;
-          tma_load_2d(sA, &tmA_hi, full_bar + stage, ka, m0);
-          tma_load_2d(sA + Cfg::A_BYTES, &tmA_lo, full_bar + stage, ka, m0);
-          tma_load_2d(sB, &tmB_hi, full_bar + stage, kw, rw);
-          tma_load_2d(sB + Cfg::B_BYTES, &tmB_lo, full_bar + stage, kw, rw);
+          if (CG == 2) {
+            const uint32_t bar = mapa_u32(smem_u32(full_bar + stage), 0);      // the leader's barrier
+            if (rank == 0) mbar_arrive_expect_tx(full_bar + stage, 2 * Cfg::STAGE_BYTES);
+            tma_load_2d_cg2(sA, &tmA_hi, bar, ka, m0);
+            if (NPROD == 3) tma_load_2d_cg2(sA + Cfg::A_BYTES, &tmA_lo, bar, ka, m0);
+            tma_load_2d_cg2(sB, &tmB_hi, bar, kw, rw);
+            tma_load_2d_cg2(sB + Cfg::B_BYTES, &tmB_lo, bar, kw, rw);
+          } else {
+            mbar_arrive_expect_tx(full_bar + stage, Cfg::STAGE_BYTES);
+            tma_load_2d(sA, &tmA_hi, full_bar + stage, ka, m0);
+            if (NPROD == 3) tma_load_2d(sA + Cfg::A_BYTES, &tmA_lo, full_bar + stage, ka, m0);
+            tma_load_2d(sB, &tmB_hi, full_bar + stage, kw, rw);
+            tma_load_2d(sB + Cfg::B_BYTES, &tmB_lo, full_bar + stage, kw, rw);
+          }
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(TC_BM, BN);
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(TC_BM * CG, BN);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        mbar_wait(tempty_bar + as, aphase ^ 1);          // epilogue has drained this accumulator
+      for (int t = unit; t < num_tiles; t += n_units) {
+        mbar_wait(tempty_bar + as, aphase ^ 1);          // epilogues (of both CTAs) have drained this accumulator
         fence_after_sync();
         const uint32_t tmem_d = tmem_base + as * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(full_bar + stage, phase);
           fence_after_sync();
           const uint32_t sA = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-          const uint32_t sB = sA + 2 * Cfg::A_BYTES;
+          const uint32_t sB = sA + Cfg::A_PLANES * Cfg::A_BYTES;
           const uint64_t a_hi = make_desc_k128(sA), a_lo = make_desc_k128(sA + Cfg::A_BYTES);
           const uint64_t b_hi = make_desc_k128(sB), b_lo = make_desc_k128(sB + Cfg::B_BYTES);
 #pragma unroll
           for (int k = 0; k < TC_BK / 16; ++k) {          // small cross terms first, then hi*hi
             const uint64_t adv = static_cast<uint64_t>(k * 2);   // 32 bytes >> 4 inside the swizzle atom
-            mma_f16(tmem_d, a_lo + adv, b_hi + adv, idesc, (kb | k) != 0);
-            mma_f16(tmem_d, a_hi + adv, b_lo + adv, idesc, 1);
-            mma_f16(tmem_d, a_hi + adv, b_hi + adv, idesc, 1);
+            if (CG == 2) {
+              if (NPROD == 3) mma_f16_cg2(tmem_d, a_lo + adv, b_hi + adv, idesc, (kb | k) != 0);
+              mma_f16_cg2(tmem_d, a_hi + adv, b_lo + adv, idesc, NPROD == 3 ? 1 : (kb | k) != 0);
+              mma_f16_cg2(tmem_d, a_hi + adv, b_hi + adv, idesc, 1);
+            } else {
+              if (NPROD == 3) mma_f16(tmem_d, a_lo + adv, b_hi + adv, idesc, (kb | k) != 0);
+              mma_f16(tmem_d, a_hi + adv, b_lo + adv, idesc, NPROD == 3 ? 1 : (kb | k) != 0);
+              mma_f16(tmem_d, a_hi + adv, b_hi + adv, idesc, 1);
+            }
           }
-          mma_commit(empty_bar + stage);                  // smem slot reusable once these MMAs retire
+          if (CG == 2) mma_commit_cg2(empty_bar + stage, 3); else mma_commit(empty_bar + stage);   // smem slot reusable
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
-        mma_commit(tfull_bar + as);                       // accumulator complete
+        if (CG == 2) mma_commit_cg2(tfull_bar + as, 3); else mma_commit(tfull_bar + as);           // accumulator complete
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
@@ -150,9 +182,9 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     float *sT = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256) + we * TC_EPI_FLOATS;
     float *sBias = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + Cfg::EPI_BYTES);
     int as = 0; uint32_t aphase = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    for (int t = unit; t < num_tiles; t += n_units) {
       const int z = t / tiles_per_z, r = t % tiles_per_z;
-      const int m0 = (r / g.n_tiles) * TC_BM, n0 = (r % g.n_tiles) * BN;
+      const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = (r % g.n_tiles) * BN;
       const float *bias = g.bias ? g.bias + z * g.bias_z : nullptr;
       // Stage bias[n] (+ frame_bias[frame][n]) of this tile's <= 2 frames: sB[sel][c], sel = row >= split_row
       const int fa = m0 / g.rows_per_frame;
@@ -289,16 +321,21 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         __syncwarp();
       }
       fence_before_sync();
-      mbar_arrive(tempty_bar + as);                       // 256 arrivals release the accumulator
+      __syncwarp();
+      if (lane == 0) {                                    // one arrival per epilogue warp (CG * 8 in total)
+        if (CG == 2) mbar_arrive_cluster(mapa_u32(smem_u32(tempty_bar + as), 0));
+        else mbar_arrive(tempty_bar + as);
+      }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
   }
 
   fence_before_sync();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 2) {
     fence_after_sync();
-    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if (CG == 2) tmem_dealloc_cg2(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
@@ -412,40 +449,74 @@ static cudaEvent_t prof_event() {
   return g_prof.ev[g_prof.used++];
 }
 
-template <int BN>
+static int max_pairs_resident(const void *fn, int smem_bytes) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * sm_count(), 1, 1);
+  cfg.blockDim = dim3(TC_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, fn, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); n = sm_count() / 2; }
+  return n;
+}
+
+template <int BN, int NPROD, int CG>
 static int launch_tc(const TcGemm &g, cudaStream_t st) {
-  using Cfg = TcCfg<BN>;
+  using Cfg = TcCfg<BN, NPROD, CG>;
   CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
   const long long a_cols = (long long)g.a_col_z * (g.batch - 1) + g.K;
   const long long w_rows = (long long)g.b_row_z * (g.batch - 1) + g.N;
   int rc;
   if ((rc = make_map(&ma_hi, g.A, a_cols, g.M, g.lda, TC_BM))) return rc;
-  if ((rc = make_map(&ma_lo, g.A + g.a_plane, a_cols, g.M, g.lda, TC_BM))) return rc;
-  if ((rc = make_map(&mb_hi, g.W, g.K, w_rows, g.ldw, BN))) return rc;
-  if ((rc = make_map(&mb_lo, g.W + g.w_plane, g.K, w_rows, g.ldw, BN))) return rc;
+  if ((rc = make_map(&ma_lo, g.A + (NPROD == 3 ? g.a_plane : 0), a_cols, g.M, g.lda, TC_BM))) return rc;
+  if ((rc = make_map(&mb_hi, g.W, g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
+  if ((rc = make_map(&mb_lo, g.W + g.w_plane, g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
   TcKernelArgs k{};
   k.M = g.M; k.N = g.N; k.K = g.K; k.batch = g.batch;
-  k.m_tiles = (g.M + TC_BM - 1) / TC_BM; k.n_tiles = (g.N + BN - 1) / BN;
+  k.m_tiles = (g.M + TC_BM * CG - 1) / (TC_BM * CG); k.n_tiles = (g.N + BN - 1) / BN;
   k.a_col_z = g.a_col_z; k.b_row_z = g.b_row_z; k.c_col_z = g.c_col_z; k.bias_z = g.bias_z;
   k.bias = g.bias; k.frame_bias = g.frame_bias; k.rows_per_frame = g.rows_per_frame > 0 ? g.rows_per_frame : 1; k.ldfb = g.ldfb;
   k.relu = g.relu; k.out_mode = g.out_mode;
   k.Cf = g.Cf; k.ldc = g.ldc; k.Cb = g.Cb; k.ldcb = g.ldcb; k.c_plane = g.c_plane; k.pool = g.pool;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16x2_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+  auto kfn = gemm_bf16x2_kernel<BN, NPROD, CG>;
+  static int units_max = 0;            // per instantiation: CTAs (CG == 1) or CTA pairs (CG == 2) resident at once
+  if (!units_max) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess) { set_error("gemm_bf16x2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
-    attr_set = true;
+    units_max = CG == 2 ? max_pairs_resident((const void *)kfn, Cfg::SMEM_BYTES) : sm_count();
   }
   const long long tiles = (long long)k.m_tiles * k.n_tiles * k.batch;
-  const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  const int units = (int)(tiles < units_max ? tiles : units_max);
   if (g_prof.on) cudaEventRecord(prof_event(), st);
-  gemm_bf16x2_kernel<BN><<<grid, TC_THREADS, Cfg::SMEM_BYTES, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, k);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(units * CG, 1, 1);
+  cfg.blockDim = dim3(TC_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kfn, ma_hi, ma_lo, mb_hi, mb_lo, k);
+  if (e != cudaSuccess) { set_error("gemm_bf16x2: launch: %s", cudaGetErrorString(e)); return (int)e; }
   if (g_prof.on) {
     cudaEventRecord(prof_event(), st);
     g_prof.flops += 2.0 * g.M * g.N * g.K * g.batch;
     g_prof.launches += 1;
   }
   return check_launch("gemm_bf16x2");
+}
+
+static int tc_cta_group() {             // PLR2_TC_CTA_GROUP=1 selects the single-CTA kernel (debugging aid)
+  static int cg = 0;
+  if (!cg) {
+    const char *e = getenv("PLR2_TC_CTA_GROUP");
+    cg = (e && e[0] == '1') ? 1 : 2;
+  }
+  return cg;
 }
 
 int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
@@ -456,8 +527,13 @@ int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
   if (g.out_mode == TC_OUT_BF16X2 && (!g.Cb || (g.ldcb % 8) || (g.c_col_z % 8))) { set_error("gemm_bf16x2: bf16 output needs 16-byte aligned rows"); return PLR2_E_ALIGN; }
   if (g.out_mode == TC_OUT_POOL && (!g.pool || g.batch != 1)) { set_error("gemm_bf16x2: pooled output needs batch == 1"); return PLR2_E_UNSUPPORTED; }
   if ((g.out_mode == TC_OUT_POOL || g.frame_bias) && g.rows_per_frame < TC_BM) { set_error("gemm_bf16x2: per-frame epilogues need rows_per_frame >= %d", TC_BM); return PLR2_E_UNSUPPORTED; }
-  if (g.N >= 256) return launch_tc<256>(g, st);
-  return launch_tc<128>(g, st);
+  const bool hi_only = g.a_hi_only != 0;
+  if (tc_cta_group() == 2) {
+    if (g.N >= 256) return hi_only ? launch_tc<256, 2, 2>(g, st) : launch_tc<256, 3, 2>(g, st);
+    return hi_only ? launch_tc<128, 2, 2>(g, st) : launch_tc<128, 3, 2>(g, st);
+  }
+  if (g.N >= 256) return hi_only ? launch_tc<256, 2, 1>(g, st) : launch_tc<256, 3, 1>(g, st);
+  return hi_only ? launch_tc<128, 2, 1>(g, st) : launch_tc<128, 3, 1>(g, st);
 }
 
 }  // namespace plr2

@@ -17,6 +17,7 @@ struct TcGemm {
   int a_col_z = 0, b_row_z = 0; long long c_col_z = 0, bias_z = 0;
   const float *bias = nullptr, *frame_bias = nullptr; int rows_per_frame = 1; long long ldfb = 0;
   int relu = 0, out_mode = TC_OUT_F32;
+  int a_hi_only = 0;          // 1: use only the hi plane of X (2 MMAs per MAC; for layers whose output is only pooled)
   float *Cf = nullptr; long long ldc = 0;
   __nv_bfloat16 *Cb = nullptr; long long ldcb = 0, c_plane = 0;
   float *pool = nullptr;      // TC_OUT_POOL: [ceil(M/32)][2][N] partial column sums

@@ -500,9 +500,9 @@ pose_select_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
 // ADD-S scan) and the matching slices of the re-centring; the per-CTA partial sums are combined in
 // rank order by CTA 0 through distributed shared memory (deterministic, no global scratch).
 constexpr int REFINE_RS = 3;                       // reference ranges scanned concurrently per query
-constexpr int REFINE_QT = 96;                      // query threads per range (3 warps)
+constexpr int REFINE_QT = 288;                     // query threads per range (9 warps)
 constexpr int REFINE_THREADS = REFINE_RS * REFINE_QT;
-constexpr int REFINE_QPT = 3;
+constexpr int REFINE_QPT = 1;                      // few pairs in total: maximise warps, not register reuse
 constexpr int REFINE_PASS = REFINE_QT * REFINE_QPT;   // 288 queries per CTA pass
 constexpr int REFINE_MAX_CLUSTER = 8;
 
@@ -768,7 +768,7 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
   int S = (n_mesh + pass - 1) / pass;
   if (S > REFINE_MAX_CLUSTER) S = REFINE_MAX_CLUSTER;
   int slice = (n_mesh + S - 1) / S;
-  slice = (slice + pass - 1) / pass * pass;
+  slice = (slice + 31) / 32 * 32;               // warp granularity
   void (*kfn)(const float *, const float *, const float *, const float *, const float *, const int64_t *,
               const uint8_t *, int, int, int, int, float *, float *, float *, float *, float *, float *);
   if (fast && jac) kfn = refine_loss_kernel<true, true>;
