@@ -103,13 +103,17 @@ int plr2_pose_select(const float *pred_r, const float *pred_t, const float *pred
  *   pred_r [F][4], pred_t [F][3]; target/model_points [F][M][3]; points [F][N][3]
  *   ADD-S iff sym_lut[obj[f]] (always, lib/loss_refiner.py:40)
  *   dis [F]; new_points [F][N][3]; new_target [F][M][3]; jac_r [F][4], jac_t [F][3] (nullable)
- *   pose_out [F][12] nullable.  Needs n_mesh <= 8192. */
+ *   pose_out [F][12] nullable.  Needs n_mesh <= 8192.
+ *   workspace: plr2_refine_loss_workspace_bytes(frames, n_mesh) bytes, 16-byte aligned, contents
+ *   irrelevant on entry (per-frame arrival counters + per-CTA partial sums). */
+size_t plr2_refine_loss_workspace_bytes(int frames, int n_mesh);
 int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t,
                          const float *target, const float *model_points, const float *points,
                          const int64_t *obj, const uint8_t *sym_lut, int num_obj,
                          int frames, int n_points, int n_mesh, int knn_mode,
                          float *dis, float *new_points, float *new_target,
-                         float *jac_r, float *jac_t, float *pose_out, void *stream);
+                         float *jac_r, float *jac_t, float *pose_out,
+                         void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---- (2) dense contractions --------------------------------------------------------------
  * General FP32 GEMM with fused epilogue, C(m,n) (+)= f(sum_k A(m,k) B(k,n)):

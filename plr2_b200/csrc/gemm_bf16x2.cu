@@ -304,15 +304,16 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
             if (row < g.M) {
               __nv_bfloat16 *dh = g.Cb + (long long)row * g.ldcb + z * g.c_col_z + n;
               __nv_bfloat16 *dl = dh + g.c_plane;
+              const bool want_lo = g.c_plane != 0;        // c_plane == 0: the consumer only reads the hi plane
               if (n + 7 < g.N) {
                 *reinterpret_cast<uint4 *>(dh) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4 *>(dl) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                if (want_lo) *reinterpret_cast<uint4 *>(dl) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
               } else {
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
                   if (n + j < g.N) {
                     dh[j] = __ushort_as_bfloat16((unsigned short)(hi[j >> 1] >> ((j & 1) * 16)));
-                    dl[j] = __ushort_as_bfloat16((unsigned short)(lo[j >> 1] >> ((j & 1) * 16)));
+                    if (want_lo) dl[j] = __ushort_as_bfloat16((unsigned short)(lo[j >> 1] >> ((j & 1) * 16)));
                   }
               }
             }

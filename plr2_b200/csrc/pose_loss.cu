@@ -3,10 +3,6 @@
 // that neither the (N, M, 3) prediction tensor nor the KNN index tensor is ever materialised.
 // Reference: lib/loss.py:12-69, lib/loss_refiner.py:12-62.
 #include "knn_core.cuh"
-#include <cooperative_groups.h>
-
-namespace cg = cooperative_groups;
-
 namespace plr2 {
 
 // ---------------------------------------------------------------------------------------------
@@ -495,16 +491,17 @@ pose_select_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
 }
 
 // ---------------------------------------------------------------------------------------------
-// Refiner loss, lib/loss_refiner.py:12-62: one pose per frame.  One thread-block CLUSTER per frame:
-// CTA s of the cluster owns mesh points [s*slice, (s+1)*slice) (each CTA stages all M targets for the
-// ADD-S scan) and the matching slices of the re-centring; the per-CTA partial sums are combined in
-// rank order by CTA 0 through distributed shared memory (deterministic, no global scratch).
+// Refiner loss, lib/loss_refiner.py:12-62: one pose per frame, up to 32 CTAs per frame: CTA s owns mesh
+// points [s*slice, (s+1)*slice) (each CTA stages all M targets for the ADD-S scan) and the matching
+// slices of the re-centring; per-CTA partial sums meet in the caller's workspace and are combined in
+// slice order by the last CTA to arrive (deterministic).  [A thread-block-cluster/DSMEM version was
+// measured first: 64 clusters of 8 cost ~75 us per launch regardless of the work inside.]
 constexpr int REFINE_RS = 3;                       // reference ranges scanned concurrently per query
-constexpr int REFINE_QT = 288;                     // query threads per range (9 warps)
+constexpr int REFINE_QT = 96;                      // query threads per range (3 warps)
 constexpr int REFINE_THREADS = REFINE_RS * REFINE_QT;
 constexpr int REFINE_QPT = 1;                      // few pairs in total: maximise warps, not register reuse
-constexpr int REFINE_PASS = REFINE_QT * REFINE_QPT;   // 288 queries per CTA pass
-constexpr int REFINE_MAX_CLUSTER = 8;
+constexpr int REFINE_PASS = REFINE_QT * REFINE_QPT;   // 96 queries per CTA pass
+constexpr int REFINE_MAX_SPLIT = 32;               // CTAs per frame
 
 // ADD-S accumulation for the refiner: thread (r, qt) scans reference range r for REFINE_QPT queries;
 // the per-range candidates meet in shared memory and range-0 threads finish (lowest range wins ties,
@@ -577,16 +574,16 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
                    const float *__restrict__ target, const float *__restrict__ model,
                    const float *__restrict__ points, const int64_t *__restrict__ obj,
                    const uint8_t *__restrict__ sym_lut, int num_obj, int N, int M, int slice,
+                   unsigned int *__restrict__ counters, float *__restrict__ partials,
                    float *__restrict__ dis, float *__restrict__ new_points,
                    float *__restrict__ new_target, float *__restrict__ jac_r,
                    float *__restrict__ jac_t, float *__restrict__ pose_out) {
   extern __shared__ __align__(16) float dyn[];
   __shared__ float red[(REFINE_THREADS / 32) * 13];
-  __shared__ float part[13];
+  __shared__ int s_last;
   __shared__ float cand_d[REFINE_RS][REFINE_PASS];
   __shared__ int cand_c[REFINE_RS][REFINE_PASS];
-  cg::cluster_group cluster = cg::this_cluster();
-  const int S = gridDim.x, s = blockIdx.x;      // cluster = the whole x extent
+  const int S = gridDim.x, s = blockIdx.x;
   const int f = blockIdx.y;
   const float *tb = target + (size_t)f * M * 3;
   const float *mb = model + (size_t)f * M * 3;
@@ -614,25 +611,33 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
     }
   }
   acc_block_reduce<JAC>(A, red);
+  // Per-CTA partial sums go to the workspace; the CTA that arrives LAST for this frame adds them up
+  // in slice order (deterministic) and writes the frame's outputs, then re-arms the counter.
   if (threadIdx.x == 0) {
-    part[0] = A.dis;
+    float *pp = partials + ((size_t)f * S + s) * 13;
+    pp[0] = A.dis;
 #pragma unroll
-    for (int i = 0; i < 3; ++i) part[1 + i] = JAC ? A.gs[i] : 0.f;
+    for (int i = 0; i < 3; ++i) pp[1 + i] = JAC ? A.gs[i] : 0.f;
 #pragma unroll
-    for (int i = 0; i < 9; ++i) part[4 + i] = JAC ? A.G[i] : 0.f;
+    for (int i = 0; i < 9; ++i) pp[4 + i] = JAC ? A.G[i] : 0.f;
+    __threadfence();
+    s_last = atomicAdd(counters + f, 1u) == (unsigned)(S - 1);
   }
-  cluster.sync();
-  if (s == 0 && threadIdx.x == 0) {
-    for (int r = 1; r < S; ++r) {                 // fixed rank order
-      const float *rp = cluster.map_shared_rank(part, r);
-      A.dis += rp[0];
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    acc_zero(A);
+    for (int r = 0; r < S; ++r) {                 // fixed slice order
+      const float *rp = partials + ((size_t)f * S + r) * 13;
+      A.dis += __ldcg(rp);
       if (JAC) {
 #pragma unroll
-        for (int i = 0; i < 3; ++i) A.gs[i] += rp[1 + i];
+        for (int i = 0; i < 3; ++i) A.gs[i] += __ldcg(rp + 1 + i);
 #pragma unroll
-        for (int i = 0; i < 9; ++i) A.G[i] += rp[4 + i];
+        for (int i = 0; i < 9; ++i) A.G[i] += __ldcg(rp + 4 + i);
       }
     }
+    counters[f] = 0;
     const float invM = 1.0f / (float)M;
     dis[f] = A.dis * invM;
     if (JAC) {
@@ -661,7 +666,6 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
     const int per = (M + S - 1) / S, a = min(M, s * per), b = min(M, a + per);
     recentre_rows(tb + (size_t)a * 3, new_target + ((size_t)f * M + a) * 3, b - a, P.R, P.s);
   }
-  cluster.sync();        // partials must stay mapped until CTA 0 has read them
 }
 
 static int set_dyn_smem(const void *fn, size_t bytes) {
@@ -748,46 +752,52 @@ extern "C" int plr2_pose_select(const float *pred_r, const float *pred_t, const 
   return check_launch("plr2_pose_select");
 }
 
+static int refine_split(int n_mesh) {
+  int S = (n_mesh + REFINE_PASS - 1) / REFINE_PASS;
+  return S > REFINE_MAX_SPLIT ? REFINE_MAX_SPLIT : (S < 1 ? 1 : S);
+}
+
+// workspace: [frames] arrival counters (u32, padded to 128 B) then [frames][S][13] partial sums
+extern "C" size_t plr2_refine_loss_workspace_bytes(int frames, int n_mesh) {
+  if (frames <= 0 || n_mesh <= 0) return 0;
+  const size_t cnt = ((size_t)frames * sizeof(unsigned int) + 127) / 128 * 128;
+  return cnt + (size_t)frames * refine_split(n_mesh) * 13 * sizeof(float);
+}
+
 extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, const float *target,
                                     const float *model_points, const float *points, const int64_t *obj,
                                     const uint8_t *sym_lut, int num_obj, int frames, int n_points,
                                     int n_mesh, int knn_mode, float *dis, float *new_points,
                                     float *new_target, float *jac_r, float *jac_t, float *pose_out,
-                                    void *stream) {
+                                    void *workspace, size_t workspace_bytes, void *stream) {
   if (frames < 0 || n_points < 0 || n_mesh <= 0 || frames > 65535) { set_error("plr2_refine_loss_fwd: bad shape"); return PLR2_E_SHAPE; }
   if (frames == 0) return 0;
   if (!pred_r || !pred_t || !target || !model_points || !dis || (new_points && !points) ||
       ((jac_r == nullptr) != (jac_t == nullptr))) { set_error("plr2_refine_loss_fwd: null pointer"); return PLR2_E_NULLPTR; }
   if (n_mesh > 8192) { set_error("plr2_refine_loss_fwd: n_mesh <= 8192 required (got %d)", n_mesh); return PLR2_E_UNSUPPORTED; }
+  if (!workspace || workspace_bytes < plr2_refine_loss_workspace_bytes(frames, n_mesh) ||
+      (reinterpret_cast<uintptr_t>(workspace) & 15)) {
+    set_error("plr2_refine_loss_fwd: workspace missing, misaligned or smaller than plr2_refine_loss_workspace_bytes");
+    return PLR2_E_WORKSPACE;
+  }
   cudaStream_t st = (cudaStream_t)stream;
   const bool fast = knn_mode == PLR2_KNN_FAST, jac = jac_r != nullptr;
   const bool may_sym = sym_lut != nullptr && obj != nullptr;
   const size_t smem = may_sym ? (size_t)knn_pad(n_mesh) * sizeof(float) * (fast ? 4 : 3) : 0;
-  // cluster size: one full pass of REFINE_THREADS*REFINE_QPT mesh points per CTA, at most 8 CTAs
-  const int pass = REFINE_PASS;
-  int S = (n_mesh + pass - 1) / pass;
-  if (S > REFINE_MAX_CLUSTER) S = REFINE_MAX_CLUSTER;
+  const int S = refine_split(n_mesh);
   int slice = (n_mesh + S - 1) / S;
   slice = (slice + 31) / 32 * 32;               // warp granularity
-  void (*kfn)(const float *, const float *, const float *, const float *, const float *, const int64_t *,
-              const uint8_t *, int, int, int, int, float *, float *, float *, float *, float *, float *);
-  if (fast && jac) kfn = refine_loss_kernel<true, true>;
-  else if (fast) kfn = refine_loss_kernel<true, false>;
-  else if (jac) kfn = refine_loss_kernel<false, true>;
-  else kfn = refine_loss_kernel<false, false>;
-  int rc = set_dyn_smem((const void *)kfn, smem);
-  if (rc) return rc;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(S, frames, 1);
-  cfg.blockDim = dim3(REFINE_THREADS, 1, 1);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = S; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kfn, pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj,
-                                     n_points, n_mesh, slice, dis, new_points, new_target, jac_r, jac_t, pose_out);
-  if (e != cudaSuccess) { set_error("plr2_refine_loss_fwd: launch: %s", cudaGetErrorString(e)); return (int)e; }
+  const size_t cnt_bytes = ((size_t)frames * sizeof(unsigned int) + 127) / 128 * 128;
+  unsigned int *counters = reinterpret_cast<unsigned int *>(workspace);
+  float *partials = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(workspace) + cnt_bytes);
+  cudaError_t e = cudaMemsetAsync(counters, 0, cnt_bytes, st);
+  if (e != cudaSuccess) { set_error("plr2_refine_loss_fwd: memset: %s", cudaGetErrorString(e)); return (int)e; }
+  dim3 grid(S, frames);
+#define ARGS pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, slice, counters, partials, dis, new_points, new_target, jac_r, jac_t, pose_out
+  if (fast && jac) PLR2_LAUNCH_ADDS(refine_loss_kernel, true, true, grid, REFINE_THREADS, smem, st, ARGS);
+  else if (fast) PLR2_LAUNCH_ADDS(refine_loss_kernel, true, false, grid, REFINE_THREADS, smem, st, ARGS);
+  else if (jac) PLR2_LAUNCH_ADDS(refine_loss_kernel, false, true, grid, REFINE_THREADS, smem, st, ARGS);
+  else PLR2_LAUNCH_ADDS(refine_loss_kernel, false, false, grid, REFINE_THREADS, smem, st, ARGS);
+#undef ARGS
   return check_launch("plr2_refine_loss_fwd");
 }

@@ -85,17 +85,26 @@ static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspac
   // conv2 and e_conv2 in one launch (batch = branch): x1 -> pf[:,128:256), e1 -> pf[:,256:384)
   g.batch = 2; g.a_col_z = 64; g.b_row_z = (int)((L.e2w - L.c2w) / 64); g.c_col_z = 128;
   g.bias_z = (long long)(L.e2b - L.c2b);
+  // Layers whose output is consumed ONLY through the per-frame average pool (conv5, conv6; in the refiner
+  // also conv2/e_conv2) read just the hi plane of their activations (2 MMAs per MAC instead of 3): the
+  // bf16 rounding of an activation is unbiased and independent from point to point, so it averages out
+  // over the num_points rows of the pool (error ~2^-9/sqrt(N)), while weights keep hi+lo.
+  const bool pooled_only = L.net == PLR2_NET_REFINER;
+  g.a_hi_only = pooled_only ? 1 : 0;
+  if (pooled_only) g.c_plane = 0;
   RC(gemm_bf16x2(g, st));
   g = TcGemm();
   g.A = L.c5k == 256 ? pf + 128 : pf; g.lda = 384; g.a_plane = W.pf_plane;
   g.W = wb + L.c5w; g.ldw = L.c5k; g.w_plane = wplane;
   g.M = R; g.N = 512; g.K = L.c5k; g.bias = pk + L.c5b; g.relu = 1;
-  g.out_mode = TC_OUT_BF16X2; g.Cb = x5; g.ldcb = 512; g.c_plane = W.x5_plane;
+  g.out_mode = TC_OUT_BF16X2; g.Cb = x5; g.ldcb = 512; g.c_plane = 0;                // hi plane only (see above)
+  g.a_hi_only = 1;
   RC(gemm_bf16x2(g, st));                                                            // conv5
   g = TcGemm();
   g.A = x5; g.lda = 512; g.a_plane = W.x5_plane; g.W = wb + L.c6w; g.ldw = 512; g.w_plane = wplane;
   g.M = R; g.N = 1024; g.K = 512; g.bias = pk + L.c6b; g.relu = 1;
   g.out_mode = TC_OUT_POOL; g.pool = W.pool; g.rows_per_frame = N;
+  g.a_hi_only = 1;
   RC(gemm_bf16x2(g, st));                                                            // conv6 + AvgPool partials
   RC(pool_finish(W.pool, F, N, R, 1024, W.ap, st));
   return 0;

@@ -114,12 +114,14 @@ class RefineLossFn(torch.autograd.Function):
         jac_t = torch.empty((F, 3), dtype=torch.float32, device=dev) if need_jac else None
         new_points = torch.empty((F, N, 3), dtype=torch.float32, device=dev)
         new_target = torch.empty((F, M, 3), dtype=torch.float32, device=dev)
+        nws = _cabi.lib().plr2_refine_loss_workspace_bytes(F, M)
+        ws = torch.empty(nws, dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             rc = _cabi.lib().plr2_refine_loss_fwd(_cabi.ptr(pr), _cabi.ptr(pt), _cabi.ptr(tg), _cabi.ptr(mp),
                                                   _cabi.ptr(ps), _cabi.ptr(ob), _cabi.ptr(lut), int(lut.numel()),
                                                   F, N, M, int(knn_mode), _cabi.ptr(dis), _cabi.ptr(new_points),
                                                   _cabi.ptr(new_target), _cabi.ptr(jac_r), _cabi.ptr(jac_t), None,
-                                                  _cabi.stream_ptr(dev))
+                                                  _cabi.ptr(ws), nws, _cabi.stream_ptr(dev))
         _cabi.check(rc, "plr2_refine_loss_fwd")
         if need_jac:
             ctx.save_for_backward(jac_r, jac_t)

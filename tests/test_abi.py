@@ -45,7 +45,8 @@ def test_argument_validation_without_gpu(lib):
     assert lib.plr2_knn_f32(None, None, None, None, 1, 3, 5, 0, 1, 0, None, 0, None) == 0     # empty query set
     assert lib.plr2_knn_f32(None, None, None, None, 0, 3, 5, 9, 1, 0, None, 0, None) == 0     # empty batch
     assert lib.plr2_pose_loss_fwd(*([None] * 8), 21, 1, 0, 500, 0.015, 0, 0, *([None] * 5)) == -2
-    assert lib.plr2_refine_loss_fwd(*([None] * 7), 21, 1, 1000, 9000, 0, *([None] * 7)) in (-1, -3)
+    assert lib.plr2_refine_loss_fwd(*([None] * 7), 21, 1, 1000, 9000, 0, *([None] * 6), None, 0, None) in (-1, -3)
+    assert lib.plr2_refine_loss_workspace_bytes(64, 2300) == 128 * 2 + 64 * 24 * 13 * 4
 
 
 def test_missing_library_fails_loudly(monkeypatch):
