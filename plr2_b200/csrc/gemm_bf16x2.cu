@@ -65,16 +65,21 @@ struct TcKernelArgs {
   float *Cf; long long ldc;
   __nv_bfloat16 *Cb; long long ldcb, c_plane;
   float *pool;                   // [ceil(M/32)][2][N]
+  int tma_store;                 // tile outputs leave through TMA stores (maps tmC_*)
+  int debug;                     // PLR2_TC_DEBUG (timing experiments only): 1 = no global stores, 2 = no epilogue work
 };
 
 template <int BN, int NPROD, int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                    const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
+                   const __grid_constant__ CUtensorMap tmC_hi, const __grid_constant__ CUtensorMap tmC_lo,
                    const TcKernelArgs g) {
   using Cfg = TcCfg<BN, NPROD, CG>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment (128B swizzle atoms) by OFFSETTING the shared symbol: keeps the pointer's
+  // address space visible to the compiler (STS/LDS instead of generic ST/LD in the epilogue)
+  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
   uint64_t *full_bar = bars;                       // [STAGES]  TMA -> MMA   (CG == 2: the leader's is used)
   uint64_t *empty_bar = bars + Cfg::STAGES;        // [STAGES]  MMA -> TMA
@@ -206,9 +211,112 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
       mbar_wait(tfull_bar + as, aphase);
       fence_after_sync();
       const int rbase = m0 + wq * 32;                     // first row of this warp's 32-row slab
+      if (g.out_mode == TC_OUT_POOL || g.tma_store) {
+        // ---- fast path: warpgroup `half` owns columns [half*BN/2, +BN/2) in chunks of 16; the TMEM load
+        // of chunk i+1 is in flight while chunk i is processed; tile outputs leave through per-warp
+        // shared-memory slabs and TMA stores (no LSU traffic), pooled sums through a halving butterfly.
+        constexpr int NCH = BN / 2 / TC_EPI_COLS;
+        const int cbase = half * (BN / 2);
+        const uint32_t tbase = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + as * BN + cbase;
+        const int row = rbase + lane;
+        const bool second = row >= split_row;
+        const float *bsel = sB + (second ? BN : 0) + cbase;
+        uint8_t *slab = reinterpret_cast<uint8_t *>(sT);
+        uint32_t raw[2][16];
+        if (g.debug != 2) tmem_ld_32x16(tbase, raw[0]);
+#pragma unroll
+        for (int ci = 0; ci < NCH; ++ci) {
+          const int c0 = ci * TC_EPI_COLS;
+          if (n0 + cbase + c0 >= g.N || g.debug == 2) break;          // warp-uniform
+          tmem_ld_wait();
+          if (ci + 1 < NCH && n0 + cbase + c0 + TC_EPI_COLS < g.N) tmem_ld_32x16(tbase + c0 + TC_EPI_COLS, raw[(ci + 1) & 1]);
+          float a[16];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 bb = *reinterpret_cast<const float4 *>(bsel + c0 + 4 * q);
+            a[4 * q + 0] = __uint_as_float(raw[ci & 1][4 * q + 0]) + bb.x;
+            a[4 * q + 1] = __uint_as_float(raw[ci & 1][4 * q + 1]) + bb.y;
+            a[4 * q + 2] = __uint_as_float(raw[ci & 1][4 * q + 2]) + bb.z;
+            a[4 * q + 3] = __uint_as_float(raw[ci & 1][4 * q + 3]) + bb.w;
+          }
+          if (g.relu) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) a[j] = fmaxf(a[j], 0.f);
+          }
+          const int ncol = z * (int)g.c_col_z + n0 + cbase + c0;      // first output column of this chunk
+          if (g.out_mode == TC_OUT_POOL) {
+            // per-column sums over this warp's 32 rows, split at the frame boundary if it falls inside
+            const bool straddle = rbase < split_row && rbase + 31 >= split_row;       // warp-uniform
+            const bool live = row < g.M;
+            float va[16], vb[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float v = live ? a[j] : 0.f;
+              va[j] = (straddle && second) ? 0.f : v;       // first frame present in the slab (or the only one)
+              vb[j] = (straddle && second) ? v : 0.f;
+            }
+            auto butterfly = [&](float (&v)[16]) {
+#pragma unroll
+              for (int w = 8; w >= 1; w >>= 1) {            // lane bit (2w) selects which half it keeps
+                const bool up = lane & (2 * w);
+#pragma unroll
+                for (int j = 0; j < w; ++j) {
+                  const float send = up ? v[j] : v[j + w];
+                  const float keep = up ? v[j + w] : v[j];
+                  v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 2 * w);
+                }
+              }
+              v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+            };
+            butterfly(va);
+            if (straddle) butterfly(vb);
+            const int n = n0 + cbase + c0 + (lane >> 1);    // column held by this lane pair
+            if ((lane & 1) == 0 && n < g.N && rbase < g.M && g.debug != 1) {
+              // pool[(row group)][slot]: slot 0 = frame of the group's first row, slot 1 = the next frame
+              float *dst = g.pool + ((long long)(rbase >> 5) * 2) * g.N + n;
+              dst[0] = va[0];
+              dst[g.N] = straddle ? vb[0] : 0.f;
+            }
+          } else if (g.out_mode == TC_OUT_F32) {
+            if (ci > 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              *reinterpret_cast<float4 *>(slab + lane * 64 + 16 * q) = make_float4(a[4 * q], a[4 * q + 1], a[4 * q + 2], a[4 * q + 3]);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0 && g.debug != 1) { tma_store_2d(&tmC_hi, slab, ncol, rbase); bulk_commit(); }
+          } else {
+            uint32_t hi[8], lo[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const __nv_bfloat162 h = __floats2bfloat162_rn(a[2 * q], a[2 * q + 1]);
+              hi[q] = *reinterpret_cast<const uint32_t *>(&h);
+              const float h0 = __uint_as_float(hi[q] << 16), h1 = __uint_as_float(hi[q] & 0xffff0000u);
+              const __nv_bfloat162 l = __floats2bfloat162_rn(a[2 * q] - h0, a[2 * q + 1] - h1);
+              lo[q] = *reinterpret_cast<const uint32_t *>(&l);
+            }
+            const bool want_lo = g.c_plane != 0;          // c_plane == 0: the consumer only reads the hi plane
+            if (ci > 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+            *reinterpret_cast<uint4 *>(slab + lane * 32) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4 *>(slab + lane * 32 + 16) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+            if (want_lo) {
+              *reinterpret_cast<uint4 *>(slab + 1024 + lane * 32) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+              *reinterpret_cast<uint4 *>(slab + 1024 + lane * 32 + 16) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0 && g.debug != 1) {
+              tma_store_2d(&tmC_hi, slab, ncol, rbase);
+              if (want_lo) tma_store_2d(&tmC_lo, slab + 1024, ncol, rbase);
+              bulk_commit();
+            }
+          }
+        }
+        if (g.out_mode != TC_OUT_POOL) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }   // slab reusable by the next tile
+      } else {
 #pragma unroll 1
       for (int c0 = half * TC_EPI_COLS; c0 < BN; c0 += 2 * TC_EPI_COLS) {
-        if (n0 + c0 >= g.N) break;                        // warp-uniform
+        if (n0 + c0 >= g.N || g.debug == 2) break;        // warp-uniform
         const int nc = n0 + c0;
         // TMEM -> registers (thread = row) -> smem slab [32][20] -> registers (lanes along columns),
         // so that every global store covers whole 32-byte sectors of a row.
@@ -236,7 +344,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
 #pragma unroll
               for (int j = 0; j < 4; ++j) a[j] = fmaxf(a[j], 0.f);
             }
-            if (row < g.M) {
+            if (row < g.M && g.debug != 1) {
               if (g.out_mode == TC_OUT_F32) {
                 float *dst = g.Cf + (long long)row * g.ldc + z * g.c_col_z + n;
                 if (n + 3 < g.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
@@ -301,7 +409,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
               const __nv_bfloat162 l = __floats2bfloat162_rn(a[2 * q] - h0, a[2 * q + 1] - h1);
               lo[q] = *reinterpret_cast<const uint32_t *>(&l);
             }
-            if (row < g.M) {
+            if (row < g.M && g.debug != 1) {
               __nv_bfloat16 *dh = g.Cb + (long long)row * g.ldcb + z * g.c_col_z + n;
               __nv_bfloat16 *dl = dh + g.c_plane;
               const bool want_lo = g.c_plane != 0;        // c_plane == 0: the consumer only reads the hi plane
@@ -321,6 +429,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         }
         __syncwarp();
       }
+      }
       fence_before_sync();
       __syncwarp();
       if (lane == 0) {                                    // one arrival per epilogue warp (CG * 8 in total)
@@ -331,6 +440,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     }
   }
 
+  if (warp >= 4 && lane == 0) bulk_wait_all();            // outstanding TMA stores of this thread
   fence_before_sync();
   if (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 2) {
@@ -420,6 +530,23 @@ static int make_map(CUtensorMap *m, const __nv_bfloat16 *base, long long cols, l
   return 0;
 }
 
+// Row-major output matrix [rows][cols] (pitch ld elements) written in boxes of 16 columns x 32 rows from a
+// dense (unswizzled) shared-memory slab.
+static int make_store_map(CUtensorMap *m, void *base, bool f32, long long cols, long long rows, long long ld) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled unavailable"); return PLR2_E_UNSUPPORTED; }
+  const int esz = f32 ? 4 : 2;
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * esz};
+  cuuint32_t box[2] = {(cuuint32_t)TC_EPI_COLS, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstride, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (store) failed (%d): cols=%lld rows=%lld ld=%lld", (int)r, cols, rows, ld); return PLR2_E_UNSUPPORTED; }
+  return 0;
+}
+
 static int sm_count() {
   static int n = 0;
   if (!n) {
@@ -475,13 +602,32 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   if ((rc = make_map(&ma_lo, g.A + (NPROD == 3 ? g.a_plane : 0), a_cols, g.M, g.lda, TC_BM))) return rc;
   if ((rc = make_map(&mb_hi, g.W, g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
   if ((rc = make_map(&mb_lo, g.W + g.w_plane, g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
+  // Output maps: TMA stores need 16-byte aligned base and pitch; with batch > 1 a partial last chunk would
+  // spill into the next problem's columns, so N must then be a multiple of the chunk width.
+  CUtensorMap mc_hi = ma_hi, mc_lo = ma_hi;
+  int tma_store = 0;
+  const long long c_cols = g.c_col_z * (g.batch - 1) + g.N;
+  if (g.out_mode == TC_OUT_F32) {
+    if ((g.ldc % 4) == 0 && (reinterpret_cast<uintptr_t>(g.Cf) & 15) == 0 && (g.batch == 1 || g.N % TC_EPI_COLS == 0)) {
+      if ((rc = make_store_map(&mc_hi, g.Cf, true, c_cols, g.M, g.ldc))) return rc;
+      tma_store = 1;
+    }
+  } else if (g.out_mode == TC_OUT_BF16X2) {
+    if ((reinterpret_cast<uintptr_t>(g.Cb) & 15) == 0 && (g.c_plane % 8) == 0 && (g.batch == 1 || g.N % TC_EPI_COLS == 0)) {
+      if ((rc = make_store_map(&mc_hi, g.Cb, false, c_cols, g.M, g.ldcb))) return rc;
+      if (g.c_plane != 0 && (rc = make_store_map(&mc_lo, g.Cb + g.c_plane, false, c_cols, g.M, g.ldcb))) return rc;
+      tma_store = 1;
+    }
+  }
   TcKernelArgs k{};
+  k.tma_store = tma_store;
   k.M = g.M; k.N = g.N; k.K = g.K; k.batch = g.batch;
   k.m_tiles = (g.M + TC_BM * CG - 1) / (TC_BM * CG); k.n_tiles = (g.N + BN - 1) / BN;
   k.a_col_z = g.a_col_z; k.b_row_z = g.b_row_z; k.c_col_z = g.c_col_z; k.bias_z = g.bias_z;
   k.bias = g.bias; k.frame_bias = g.frame_bias; k.rows_per_frame = g.rows_per_frame > 0 ? g.rows_per_frame : 1; k.ldfb = g.ldfb;
   k.relu = g.relu; k.out_mode = g.out_mode;
   k.Cf = g.Cf; k.ldc = g.ldc; k.Cb = g.Cb; k.ldcb = g.ldcb; k.c_plane = g.c_plane; k.pool = g.pool;
+  { static int dbg = -1; if (dbg < 0) { const char *e = getenv("PLR2_TC_DEBUG"); dbg = e ? atoi(e) : 0; } k.debug = dbg; }
   auto kfn = gemm_bf16x2_kernel<BN, NPROD, CG>;
   static int units_max = 0;            // per instantiation: CTAs (CG == 1) or CTA pairs (CG == 2) resident at once
   if (!units_max) {
@@ -501,7 +647,7 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kfn, ma_hi, ma_lo, mb_hi, mb_lo, k);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kfn, ma_hi, ma_lo, mb_hi, mb_lo, mc_hi, mc_lo, k);
   if (e != cudaSuccess) { set_error("gemm_bf16x2: launch: %s", cudaGetErrorString(e)); return (int)e; }
   if (g_prof.on) {
     cudaEventRecord(prof_event(), st);

@@ -3,9 +3,9 @@
 # of one 64-frame step.  Usage: tools/gpu_round.sh <tag>
 tag=${1:-x}
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/pytest_$tag.log
+timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/pytest_$tag.log
 tail -3 gpurun_out/pytest_$tag.log
-python bench.py --steps 5 --warmup 3 > gpurun_out/bench_$tag.log 2> gpurun_out/bench_$tag.err || { tail -5 gpurun_out/bench_$tag.err; exit 1; }
+timeout 300 python bench.py --steps 5 --warmup 3 > gpurun_out/bench_$tag.log 2> gpurun_out/bench_$tag.err || { tail -5 gpurun_out/bench_$tag.err; exit 1; }
 cat gpurun_out/bench_$tag.log
 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_$tag.csv \
   python bench.py --frames 64 --steps 1 --warmup 3 --profile-step > gpurun_out/ncu_$tag.log 2>&1
