@@ -31,7 +31,10 @@ constexpr int TC_EPI_WARPS = 8;                        // two warpgroups: each T
 constexpr int TC_THREADS = 128 + 32 * TC_EPI_WARPS;
 constexpr int TC_EPI_COLS = 16;                        // columns per epilogue chunk
 constexpr int TC_EPI_PITCH = 20;                       // floats per staged row (16 + 4 pad: conflict-free float4 stores)
-constexpr int TC_EPI_FLOATS = 32 * TC_EPI_PITCH;        // per epilogue warp
+constexpr int TC_EPI_FLOATS = 32 * TC_EPI_PITCH;        // per epilogue warp (fallback store path)
+constexpr int TC_SLAB_BYTES = 2048;                    // one 32-row x 16-column chunk: fp32, or bf16 hi + lo
+constexpr int TC_SLABS = 2;                            // slabs per epilogue warp (TMA store of one in flight while the next fills)
+static_assert(TC_EPI_FLOATS * 4 <= TC_SLABS * TC_SLAB_BYTES, "fallback transpose slab fits");
 
 // BN = output-tile width, NPROD = 3 (hi+lo activations) | 2 (hi-only activations: X_hi W_hi + X_hi W_lo),
 // CG = 1 (one CTA per tile of 128 rows) | 2 (CTA pair, cta_group::2: one 256-row tile per pair, each CTA
@@ -44,9 +47,9 @@ template <int BN, int NPROD, int CG> struct TcCfg {
   static constexpr int A_PLANES = NPROD == 3 ? 2 : 1;
   static constexpr int STAGE_BYTES = A_PLANES * A_BYTES + 2 * B_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;                      // two accumulator stages
-  static constexpr int EPI_BYTES = TC_EPI_WARPS * TC_EPI_FLOATS * 4;          // transpose slabs
-  static constexpr int BIAS_BYTES = 2 * 2 * BN * 4;                          // [acc stage][frame a|b][BN] staged bias
-  static constexpr int FIXED_BYTES = 1024 /*align slack*/ + 256 /*barriers*/ + EPI_BYTES + BIAS_BYTES;
+  static constexpr int EPI_BYTES = TC_EPI_WARPS * TC_SLABS * TC_SLAB_BYTES;   // per-warp rings of output slabs
+  static constexpr int BIAS_BYTES = 2 * BN * 4;                             // [frame a|b][BN] staged bias of the current tile
+  static constexpr int FIXED_BYTES = 256 /*barriers*/ + EPI_BYTES + BIAS_BYTES;
   static constexpr int STAGES_FIT = (232448 - FIXED_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES;
@@ -76,10 +79,11 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
                    const __grid_constant__ CUtensorMap tmC_hi, const __grid_constant__ CUtensorMap tmC_lo,
                    const TcKernelArgs g) {
   using Cfg = TcCfg<BN, NPROD, CG>;
-  extern __shared__ uint8_t smem_raw[];
-  // 1024-byte alignment (128B swizzle atoms) by OFFSETTING the shared symbol: keeps the pointer's
-  // address space visible to the compiler (STS/LDS instead of generic ST/LD in the epilogue)
-  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // The 128B-swizzled operand tiles need 1024-byte alignment; the dynamic shared window of a kernel
+  // without static shared memory starts on such a boundary (checked, not assumed).
+  uint8_t *smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
   uint64_t *full_bar = bars;                       // [STAGES]  TMA -> MMA   (CG == 2: the leader's is used)
   uint64_t *empty_bar = bars + Cfg::STAGES;        // [STAGES]  MMA -> TMA
@@ -184,29 +188,48 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     const int wq = warp & 3;                              // TMEM lane quarter == warp % 4
     const int half = we >> 2;                             // which half of the column chunks this warpgroup takes
     const int te = threadIdx.x - 128;                     // 0..255 among epilogue threads
-    float *sT = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256) + we * TC_EPI_FLOATS;
-    float *sBias = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + Cfg::EPI_BYTES);
+    uint8_t *slabs = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + we * (TC_SLABS * TC_SLAB_BYTES);
+    float *sT = reinterpret_cast<float *>(slabs);         // fallback store path: [32][20] transpose slab
+    float *sB = reinterpret_cast<float *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + Cfg::EPI_BYTES);
     int as = 0; uint32_t aphase = 0;
-    for (int t = unit; t < num_tiles; t += n_units) {
+    unsigned slab_i = 0;                                  // ring position, runs across tiles
+    // bias (+ per-frame bias) of a tile for this thread's staging slots i = te, te + 256 (< 2*BN)
+    auto load_bias = [&](int t, float (&bv)[2]) {
       const int z = t / tiles_per_z, r = t % tiles_per_z;
       const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = (r % g.n_tiles) * BN;
       const float *bias = g.bias ? g.bias + z * g.bias_z : nullptr;
-      // Stage bias[n] (+ frame_bias[frame][n]) of this tile's <= 2 frames: sB[sel][c], sel = row >= split_row
       const int fa = m0 / g.rows_per_frame;
-      const int split_row = (fa + 1) * g.rows_per_frame;  // first row of the tile's second frame
-      float *sB = sBias + as * 2 * BN;
-      for (int i = te; i < 2 * BN; i += 32 * TC_EPI_WARPS) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int i = te + u * 32 * TC_EPI_WARPS;
         const int sel = i / BN, c = i - sel * BN, n = n0 + c;
         float v = 0.f;
-        if (n < g.N) {
+        if (i < 2 * BN && n < g.N) {
           if (bias) v = __ldg(bias + n);
           if (g.frame_bias) {
             const long long fr = fa + sel;
             if (fr * g.rows_per_frame < g.M) v += __ldg(g.frame_bias + fr * g.ldfb + n);
           }
         }
-        sB[i] = v;
+        bv[u] = v;
       }
+    };
+    float bnext[2] = {0.f, 0.f};
+    if (unit < num_tiles) load_bias(unit, bnext);
+    for (int t = unit; t < num_tiles; t += n_units) {
+      const int z = t / tiles_per_z, r = t % tiles_per_z;
+      const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = (r % g.n_tiles) * BN;
+      // Stage bias[n] (+ frame_bias[frame][n]) of this tile's <= 2 frames: sB[sel][c], sel = row >= split_row.
+      // The values were fetched while the previous tile was processed; the next tile's are requested now.
+      const int fa = m0 / g.rows_per_frame;
+      const int split_row = (fa + 1) * g.rows_per_frame;  // first row of the tile's second frame
+      named_bar_sync(2, 32 * TC_EPI_WARPS);               // every warp has finished reading the previous tile's sB
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int i = te + u * 32 * TC_EPI_WARPS;
+        if (i < 2 * BN) sB[i] = bnext[u];
+      }
+      if (t + n_units < num_tiles) load_bias(t + n_units, bnext);
       named_bar_sync(1, 32 * TC_EPI_WARPS);
       mbar_wait(tfull_bar + as, aphase);
       fence_after_sync();
@@ -221,7 +244,6 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         const int row = rbase + lane;
         const bool second = row >= split_row;
         const float *bsel = sB + (second ? BN : 0) + cbase;
-        uint8_t *slab = reinterpret_cast<uint8_t *>(sT);
         uint32_t raw[2][16];
         if (g.debug != 2) tmem_ld_32x16(tbase, raw[0]);
 #pragma unroll
@@ -278,13 +300,15 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
               dst[g.N] = straddle ? vb[0] : 0.f;
             }
           } else if (g.out_mode == TC_OUT_F32) {
-            if (ci > 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+            uint8_t *slab = slabs + (slab_i++ % TC_SLABS) * TC_SLAB_BYTES;
+            if (lane == 0) bulk_wait_read<TC_SLABS - 1>();    // the store that last used this slab has read it
+            __syncwarp();
 #pragma unroll
             for (int q = 0; q < 4; ++q)
               *reinterpret_cast<float4 *>(slab + lane * 64 + 16 * q) = make_float4(a[4 * q], a[4 * q + 1], a[4 * q + 2], a[4 * q + 3]);
             fence_proxy_async();
             __syncwarp();
-            if (lane == 0 && g.debug != 1) { tma_store_2d(&tmC_hi, slab, ncol, rbase); bulk_commit(); }
+            if (lane == 0) { if (g.debug != 1) tma_store_2d(&tmC_hi, slab, ncol, rbase); bulk_commit(); }
           } else {
             uint32_t hi[8], lo[8];
 #pragma unroll
@@ -296,7 +320,9 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
               lo[q] = *reinterpret_cast<const uint32_t *>(&l);
             }
             const bool want_lo = g.c_plane != 0;          // c_plane == 0: the consumer only reads the hi plane
-            if (ci > 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+            uint8_t *slab = slabs + (slab_i++ % TC_SLABS) * TC_SLAB_BYTES;
+            if (lane == 0) bulk_wait_read<TC_SLABS - 1>();    // the store that last used this slab has read it
+            __syncwarp();
             *reinterpret_cast<uint4 *>(slab + lane * 32) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<uint4 *>(slab + lane * 32 + 16) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
             if (want_lo) {
@@ -305,14 +331,15 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
             }
             fence_proxy_async();
             __syncwarp();
-            if (lane == 0 && g.debug != 1) {
-              tma_store_2d(&tmC_hi, slab, ncol, rbase);
-              if (want_lo) tma_store_2d(&tmC_lo, slab + 1024, ncol, rbase);
+            if (lane == 0) {
+              if (g.debug != 1) {
+                tma_store_2d(&tmC_hi, slab, ncol, rbase);
+                if (want_lo) tma_store_2d(&tmC_lo, slab + 1024, ncol, rbase);
+              }
               bulk_commit();
             }
           }
         }
-        if (g.out_mode != TC_OUT_POOL) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }   // slab reusable by the next tile
       } else {
 #pragma unroll 1
       for (int c0 = half * TC_EPI_COLS; c0 < BN; c0 += 2 * TC_EPI_COLS) {
