@@ -478,24 +478,35 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
 }
 
 // ---------------------------------------------------------------------------------------------
+// ap[f][c] = (1/N) * sum of the 32-row-group partials of frame f.  Block = 32 columns x 8 group lanes
+// (each lane takes every 8th group, then a fixed-order combine): short dependent-load chains.
 __global__ void __launch_bounds__(256)
 pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, int ncols, float *__restrict__ ap) {
+  __shared__ float red[8][33];
   const int f = blockIdx.y;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= ncols) return;
+  const int cl = threadIdx.x & 31, gl = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
   const long long r_beg = (long long)f * rows_per_frame;
   long long r_end = r_beg + rows_per_frame;
   if (r_end > M) r_end = M;
   float s = 0.f;
-  for (long long g = r_beg >> 5; g <= (r_end - 1) >> 5; ++g) {
-    const int fa = (int)((g << 5) / rows_per_frame);        // frame of the group's first row
-    s += pool[(g * 2 + (fa == f ? 0 : 1)) * ncols + c];
+  if (c < ncols)
+    for (long long g = (r_beg >> 5) + gl; g <= (r_end - 1) >> 5; g += 8) {
+      const int fa = (int)((g << 5) / rows_per_frame);        // frame of the group's first row
+      s += pool[(g * 2 + (fa == f ? 0 : 1)) * ncols + c];
+    }
+  red[gl][cl] = s;
+  __syncthreads();
+  if (gl == 0 && c < ncols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][cl];
+    ap[(long long)f * ncols + c] = t / (float)rows_per_frame;
   }
-  ap[(long long)f * ncols + c] = s / (float)rows_per_frame;
 }
 
 int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap, cudaStream_t st) {
-  dim3 grid((ncols + 255) / 256, frames);
+  dim3 grid((ncols + 31) / 32, frames);
   pool_finish_kernel<<<grid, 256, 0, st>>>(pool, rows_per_frame, M, ncols, ap);
   return check_launch("pool_finish");
 }

@@ -12,8 +12,8 @@ namespace plr2 {
 // ---------------------------------------------------------------------------------------------
 constexpr int FLN_ROWS = 64;      // rows (frames) per CTA: 2 per lane
 constexpr int FLN_COLS = 16;      // output columns per CTA: 4 per warp of a K group
-constexpr int FLN_KC = 64;        // K chunk staged in shared memory
-constexpr int FLN_KG = 2;         // K groups per CTA (4 warps each), partial sums combined at the end
+constexpr int FLN_KC = 32;        // K chunk staged in shared memory
+constexpr int FLN_KG = 4;         // K groups per CTA (4 warps each), partial sums combined at the end
 constexpr int FLN_GT = 128;       // threads per K group
 constexpr int FLN_THREADS = FLN_KG * FLN_GT;
 
@@ -39,15 +39,16 @@ frame_linear_kernel(const FrameLinearArgs g) {
   const int nchunks = (g.K + FLN_KC - 1) / FLN_KC;
   const int c_beg = nchunks * grp / FLN_KG, c_end = nchunks * (grp + 1) / FLN_KG;
 
-  // global -> registers for one K chunk: X tile 64 rows x 64 k = 1024 float4 (8 per thread),
-  // W tile 16 cols x 64 k = 256 float4 (2 per thread); rows are K-contiguous in both.
-  float4 xr[8], wr[2];
+  // global -> registers for one K chunk: X tile 64 rows x 32 k = 512 float4 (4 per thread),
+  // W tile 16 cols x 32 k = 128 float4 (1 per thread); rows are K-contiguous in both.
+  constexpr int XV = FLN_ROWS * FLN_KC / 4 / FLN_GT, WV = FLN_COLS * FLN_KC / 4 / FLN_GT, KQ = FLN_KC / 4;
+  float4 xr[XV], wr[WV];
   const bool vec = ((g.ldx | g.ldw | g.zX | g.zW) & 3) == 0 && (g.K & 3) == 0 &&
                    ((reinterpret_cast<uintptr_t>(g.X) | reinterpret_cast<uintptr_t>(g.W)) & 15) == 0;
   auto load_chunk = [&](int k0) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int e = tid + i * FLN_GT, r = e >> 4, kq = (e & 15) * 4;
+    for (int i = 0; i < XV; ++i) {
+      const int e = tid + i * FLN_GT, r = e / KQ, kq = (e % KQ) * 4;
       const int m = m0 + r, k = k0 + kq;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (m < g.M) {
@@ -63,8 +64,8 @@ frame_linear_kernel(const FrameLinearArgs g) {
       xr[i] = v;
     }
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int e = tid + i * FLN_GT, c = e >> 4, kq = (e & 15) * 4;
+    for (int i = 0; i < WV; ++i) {
+      const int e = tid + i * FLN_GT, c = e / KQ, kq = (e % KQ) * 4;
       const int n = n0 + c, k = k0 + kq;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (n < g.N) {
@@ -82,13 +83,13 @@ frame_linear_kernel(const FrameLinearArgs g) {
   };
   auto store_chunk = [&]() {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int e = tid + i * FLN_GT, r = e >> 4, kq = (e & 15) * 4;
+    for (int i = 0; i < XV; ++i) {
+      const int e = tid + i * FLN_GT, r = e / KQ, kq = (e % KQ) * 4;
       Xs[grp][kq][r] = xr[i].x; Xs[grp][kq + 1][r] = xr[i].y; Xs[grp][kq + 2][r] = xr[i].z; Xs[grp][kq + 3][r] = xr[i].w;
     }
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int e = tid + i * FLN_GT, c = e >> 4, kq = (e & 15) * 4;
+    for (int i = 0; i < WV; ++i) {
+      const int e = tid + i * FLN_GT, c = e / KQ, kq = (e % KQ) * 4;
       Ws[grp][kq][c] = wr[i].x; Ws[grp][kq + 1][c] = wr[i].y; Ws[grp][kq + 2][c] = wr[i].z; Ws[grp][kq + 3][c] = wr[i].w;
     }
   };
@@ -110,17 +111,25 @@ frame_linear_kernel(const FrameLinearArgs g) {
     }
     group_sync();
   }
-  // combine the K groups through shared memory (fixed order: group 0 + group 1)
+  // combine the K groups through shared memory in fixed order (group 0 + 1 + 2 + 3)
   __syncthreads();
-  float *part = &Xs[0][0][0];                               // >= 128 threads x 8 floats
-  if (grp == 1) {
+  float *part = &Xs[0][0][0];                               // (FLN_KG - 1) x 8 x 128 floats <= sizeof(Xs)
+  if (grp > 0) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { part[(j * 2) * FLN_GT + tid] = acc0[j]; part[(j * 2 + 1) * FLN_GT + tid] = acc1[j]; }
+    for (int j = 0; j < 4; ++j) {
+      part[((grp - 1) * 8 + j * 2) * FLN_GT + tid] = acc0[j];
+      part[((grp - 1) * 8 + j * 2 + 1) * FLN_GT + tid] = acc1[j];
+    }
   }
   __syncthreads();
   if (grp != 0) return;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) { acc0[j] += part[(j * 2) * FLN_GT + tid]; acc1[j] += part[(j * 2 + 1) * FLN_GT + tid]; }
+  for (int gq = 1; gq < FLN_KG; ++gq)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      acc0[j] += part[((gq - 1) * 8 + j * 2) * FLN_GT + tid];
+      acc1[j] += part[((gq - 1) * 8 + j * 2 + 1) * FLN_GT + tid];
+    }
   const float *bias = g.bias ? g.bias + z * g.zB : nullptr;
   float *Y = g.Y + z * g.zY;
 #pragma unroll

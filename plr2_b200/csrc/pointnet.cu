@@ -95,7 +95,7 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
       }
       __nv_bfloat16 *d = pfb + row * 384 + o8 * 8;
       *reinterpret_cast<uint4 *>(d) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-      *reinterpret_cast<uint4 *>(d + pf_plane) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      if (pf_plane != 0) *reinterpret_cast<uint4 *>(d + pf_plane) = make_uint4(lo[0], lo[1], lo[2], lo[3]);   // 0: hi-only consumers
     } else {
       float4 *d = reinterpret_cast<float4 *>(pf + row * 384 + o8 * 8);
       d[0] = make_float4(v[0], v[1], v[2], v[3]);

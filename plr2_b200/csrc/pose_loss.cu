@@ -161,15 +161,15 @@ add_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred
 // Inference variant (no Jacobians): thread = 4 hypotheses x 1/8 of the mesh, so that one broadcast
 // LDS.128 pair (mesh point, target point) feeds 4 pair evaluations; sqrt.approx (<= 1 ulp-level error,
 // far inside the rtol 1e-3 budget) instead of the IEEE sequence.
-constexpr int ADDI_H = 4, ADDI_S = 8, ADDI_THREADS = 256;
-constexpr int ADDI_NPB = (ADDI_THREADS / ADDI_S) * ADDI_H;   // 128 hypotheses per block
+constexpr int ADDI_H = 4, ADDI_THREADS = 256;
 
 __device__ __forceinline__ float sqrt_approx(float x) {
   float r;
-  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));     // one MUFU.SQRT (no denormal fix-up path)
   return r;
 }
 
+template <int ADDI_S>   // mesh slices per hypothesis group: 8, 4 or 2 (chosen so that the grid is ~one wave)
 __global__ void __launch_bounds__(ADDI_THREADS)
 add_dis_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
                const float *__restrict__ target, const float *__restrict__ model,
@@ -181,8 +181,9 @@ add_dis_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_
   __shared__ float4 sm[ADD_JT];
   __shared__ float4 st[ADD_JT];
   const int tid = threadIdx.x;
+  constexpr int ADDI_NPB = (ADDI_THREADS / ADDI_S) * ADDI_H;     // hypotheses per block
   const int slice = tid & (ADDI_S - 1);
-  const int n0 = blockIdx.x * ADDI_NPB + (tid >> 3) * ADDI_H;
+  const int n0 = blockIdx.x * ADDI_NPB + (tid / ADDI_S) * ADDI_H;
   float R[ADDI_H][9], sft[ADDI_H][3], acc[ADDI_H];
 #pragma unroll
   for (int h = 0; h < ADDI_H; ++h) {
@@ -709,8 +710,18 @@ extern "C" int plr2_pose_loss_fwd(const float *pred_r, const float *pred_t, cons
   if (jac)
     add_loss_kernel<true><<<g1, ADD_SLICES * ADD_NPB, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, may_sym ? 1 : 0, dis, jac_r, jac_t);
   else {
-    dim3 gi((n_points + ADDI_NPB - 1) / ADDI_NPB, frames);
-    add_dis_kernel<<<gi, ADDI_THREADS, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, may_sym ? 1 : 0, dis);
+    // Most slices whose grid still fits the ~3 resident blocks per SM at once (a 1.15-wave grid costs
+    // almost two waves); many-wave grids use 8.
+    static int slots = 0;
+    if (!slots) { int n = plr2_device_sm_count(); slots = 3 * (n > 0 ? n : 148); }
+    auto blocks = [&](int S) { const int npb = (ADDI_THREADS / S) * ADDI_H; return (long long)((n_points + npb - 1) / npb) * frames; };
+#define ADDI_LAUNCH(S) do { const int npb = (ADDI_THREADS / S) * ADDI_H; dim3 gi((n_points + npb - 1) / npb, frames);   \
+      add_dis_kernel<S><<<gi, ADDI_THREADS, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj,  \
+                                                     n_points, n_mesh, may_sym ? 1 : 0, dis); } while (0)
+    if (blocks(8) <= slots || blocks(8) >= 4LL * slots) ADDI_LAUNCH(8);
+    else if (blocks(4) <= slots) ADDI_LAUNCH(4);
+    else ADDI_LAUNCH(2);
+#undef ADDI_LAUNCH
   }
   if (may_sym) {
     if (n_mesh > 8192) { set_error("plr2_pose_loss_fwd: ADD-S needs n_mesh <= 8192 (got %d)", n_mesh); return PLR2_E_UNSUPPORTED; }

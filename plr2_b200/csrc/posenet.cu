@@ -77,7 +77,8 @@ static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspac
   const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);   // split-bf16 weights
   const long long wplane = (long long)L.total;
   __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *x5 = (__nv_bfloat16 *)W.x5;
-  RC(first_layer_bf16(pk, L, out_img, choose, emb_in, x, F, N, hw, pf, W.pf_plane, emb_out, st));
+  // the refiner's trunk is consumed through the pool only (hi-only readers below): no lo plane needed
+  RC(first_layer_bf16(pk, L, out_img, choose, emb_in, x, F, N, hw, pf, L.net == PLR2_NET_REFINER ? 0 : W.pf_plane, emb_out, st));
   TcGemm g;
   g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.c2w; g.ldw = 64; g.w_plane = wplane;
   g.M = R; g.N = 128; g.K = 64; g.bias = pk + L.c2b; g.relu = 1;
