@@ -27,9 +27,25 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
   __shared__ __align__(16) float sw1[64 * 4];
   __shared__ __align__(16) float swe[64 * 32];
   __shared__ float sb1[64], sbe[64];
-  for (int i = threadIdx.x; i < 64 * 4; i += FL_THREADS) sw1[i] = c1w[i];
-  for (int i = threadIdx.x; i < 64 * 32; i += FL_THREADS) swe[i] = e1w[i];
-  if (threadIdx.x < 64) { sb1[threadIdx.x] = c1b[threadIdx.x]; sbe[threadIdx.x] = e1b[threadIdx.x]; }
+  // weight staging: all loads of a thread in flight at once (16-byte, packed buffer offsets are 128-byte aligned)
+  {
+    const float4 *g1 = reinterpret_cast<const float4 *>(c1w), *ge = reinterpret_cast<const float4 *>(e1w);
+    float4 v[5];
+#pragma unroll
+    for (int u = 0; u < 5; ++u) {
+      const int i = threadIdx.x + u * FL_THREADS;           // 64 + 512 float4 in total
+      v[u] = i < 64 ? __ldg(g1 + i) : (i < 64 + 512 ? __ldg(ge + (i - 64)) : make_float4(0.f, 0.f, 0.f, 0.f));
+    }
+    float bv = threadIdx.x < 64 ? __ldg(c1b + threadIdx.x) : (threadIdx.x < 128 ? __ldg(e1b + threadIdx.x - 64) : 0.f);
+#pragma unroll
+    for (int u = 0; u < 5; ++u) {
+      const int i = threadIdx.x + u * FL_THREADS;
+      if (i < 64) reinterpret_cast<float4 *>(sw1)[i] = v[u];
+      else if (i < 64 + 512) reinterpret_cast<float4 *>(swe)[i - 64] = v[u];
+    }
+    if (threadIdx.x < 64) sb1[threadIdx.x] = bv;
+    else if (threadIdx.x < 128) sbe[threadIdx.x - 64] = bv;
+  }
   __syncthreads();
   const int f = blockIdx.y;
   const int n = blockIdx.x * FL_THREADS + threadIdx.x;

@@ -184,17 +184,26 @@ add_dis_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_
   constexpr int ADDI_NPB = (ADDI_THREADS / ADDI_S) * ADDI_H;     // hypotheses per block
   const int slice = tid & (ADDI_S - 1);
   const int n0 = blockIdx.x * ADDI_NPB + (tid / ADDI_S) * ADDI_H;
-  float R[ADDI_H][9], sft[ADDI_H][3], acc[ADDI_H];
+  // Hypotheses are processed as PAIRS in packed FP32x2 registers (FFMA2/FADD2: half the issue slots):
+  // R2[p][i] = (R_{2p}[i], R_{2p+1}[i]) etc.; the mesh / target coordinates enter as broadcast operands.
+  constexpr int HP = ADDI_H / 2;
+  f32x2 R2[HP][9], s2[HP][3], acc2[HP];
 #pragma unroll
-  for (int h = 0; h < ADDI_H; ++h) {
-    const size_t fn = (size_t)f * N + min(n0 + h, N - 1);
-    Pose P;
-    make_pose(pred_r + fn * 4, P);
+  for (int p = 0; p < HP; ++p) {
+    Pose P[2];
+    float sf[2][3];
 #pragma unroll
-    for (int i = 0; i < 9; ++i) R[h][i] = P.R[i];
+    for (int e = 0; e < 2; ++e) {
+      const size_t fn = (size_t)f * N + min(n0 + 2 * p + e, N - 1);
+      make_pose(pred_r + fn * 4, P[e]);
 #pragma unroll
-    for (int i = 0; i < 3; ++i) sft[h][i] = points[fn * 3 + i] + pred_t[fn * 3 + i];   // lib/loss.py:37
-    acc[h] = 0.f;
+      for (int i = 0; i < 3; ++i) sf[e][i] = points[fn * 3 + i] + pred_t[fn * 3 + i];   // lib/loss.py:37
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R2[p][i] = pack2(P[0].R[i], P[1].R[i]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s2[p][i] = pack2(sf[0][i], sf[1][i]);
+    acc2[p] = pack2(0.f, 0.f);
   }
   const float *mb = model + (size_t)f * M * 3;
   const float *tb = target + (size_t)f * M * 3;
@@ -205,21 +214,29 @@ add_dis_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_
       const float *m = mb + (size_t)(j0 + j) * 3;
       const float *t = tb + (size_t)(j0 + j) * 3;
       sm[j] = make_float4(__ldg(m), __ldg(m + 1), __ldg(m + 2), 0.f);
-      st[j] = make_float4(__ldg(t), __ldg(t + 1), __ldg(t + 2), 0.f);
+      st[j] = make_float4(-__ldg(t), -__ldg(t + 1), -__ldg(t + 2), 0.f);   // negated: residual = pred + (-t)
     }
     __syncthreads();
 #pragma unroll 2
     for (int j = slice; j < jt; j += ADDI_S) {
       const float4 m = sm[j], t = st[j];
+      const f32x2 mx = pack2(m.x, m.x), my = pack2(m.y, m.y), mz = pack2(m.z, m.z);
+      const f32x2 tx = pack2(t.x, t.x), ty = pack2(t.y, t.y), tz = pack2(t.z, t.z);
 #pragma unroll
-      for (int h = 0; h < ADDI_H; ++h) {
-        const float dx = fmaf(R[h][0], m.x, fmaf(R[h][1], m.y, fmaf(R[h][2], m.z, sft[h][0]))) - t.x;
-        const float dy = fmaf(R[h][3], m.x, fmaf(R[h][4], m.y, fmaf(R[h][5], m.z, sft[h][1]))) - t.y;
-        const float dz = fmaf(R[h][6], m.x, fmaf(R[h][7], m.y, fmaf(R[h][8], m.z, sft[h][2]))) - t.z;
-        acc[h] += sqrt_approx(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
+      for (int p = 0; p < HP; ++p) {
+        const f32x2 dx = add2(fma2(R2[p][0], mx, fma2(R2[p][1], my, fma2(R2[p][2], mz, s2[p][0]))), tx);
+        const f32x2 dy = add2(fma2(R2[p][3], mx, fma2(R2[p][4], my, fma2(R2[p][5], mz, s2[p][1]))), ty);
+        const f32x2 dz = add2(fma2(R2[p][6], mx, fma2(R2[p][7], my, fma2(R2[p][8], mz, s2[p][2]))), tz);
+        const f32x2 d2 = fma2(dz, dz, fma2(dy, dy, mul2(dx, dx)));
+        float a, b;
+        unpack2(d2, a, b);
+        acc2[p] = add2(acc2[p], pack2(sqrt_approx(a), sqrt_approx(b)));
       }
     }
   }
+  float acc[ADDI_H];
+#pragma unroll
+  for (int p = 0; p < HP; ++p) unpack2(acc2[p], acc[2 * p], acc[2 * p + 1]);
 #pragma unroll
   for (int h = 0; h < ADDI_H; ++h) {
 #pragma unroll
