@@ -140,3 +140,58 @@ def test_refine_loss_full_size_vs_oracle(obj):
     assert_close(ntgt[0].cpu().numpy(), ont.numpy(), "new_target")
     assert_close(a.grad.cpu().numpy(), oa.grad.numpy(), "g_pred_r", frac=1.0)
     assert_close(b.grad.cpu().numpy(), ob.grad.numpy(), "g_pred_t", frac=1.0)
+
+
+@pytest.mark.parametrize("frames", [2, 64, 150])
+def test_inference_add_kernel_slice_variants(frames):
+    """The no-grad ADD path picks 8, 4 or 2 mesh slices per hypothesis group from the grid size
+    (frames = 2 / 64 / 150 at N = 1000); every variant must agree with the autograd path's kernel
+    (IEEE sqrt) and with the oracle."""
+    shp = synth.Shape(1000, 21, 300, 20, 20, tuple(synth.YCB_SYM))
+    base = [synth.make_frame(shp, 600 + i, obj=o, with_image=False) for i, o in enumerate([3, 12, 0, 19])]
+    prs = [synth.make_predictions(f, 650 + i) for i, f in enumerate(base)]
+    pick = [i % 4 for i in range(frames)]
+    st = lambda key: tt(np.stack([base[i][key] for i in pick]), "cuda")
+    B = [tt(np.stack([prs[i][k] for i in pick]), "cuda") for k in range(3)]
+    objs = tt(np.array([int(base[i]["idx"]) for i in pick])[:, None], "cuda")
+    crit = Loss(shp.num_mesh, list(shp.sym_list))
+    args = (st("target"), st("model_points"), objs, st("points"), 0.015, True)       # refine=True: plain ADD
+    with torch.no_grad():
+        loss_i, dis_i, np_i, nt_i = crit(B[0], B[1], B[2], *args)
+    Bg = [b.clone().requires_grad_(True) for b in B]
+    loss_g, dis_g, np_g, nt_g = crit(Bg[0], Bg[1], Bg[2], *args)
+    assert_close(loss_i.cpu().numpy(), loss_g.detach().cpu().numpy(), "loss inference vs autograd kernel", rtol=1e-5, frac=1.0)
+    assert_close(dis_i.cpu().numpy(), dis_g.detach().cpu().numpy(), "dis inference vs autograd kernel", rtol=1e-5, frac=1.0)
+    assert torch.equal(np_i, np_g) and torch.equal(nt_i, nt_g)
+    for i in range(2):
+        f = base[pick[i]]
+        ol, od, _, _, _ = DO.pose_loss(tt(prs[pick[i]][0]), tt(prs[pick[i]][1]), tt(prs[pick[i]][2]), tt(f["target"]),
+                                       tt(f["model_points"]), int(f["idx"]), tt(f["points"]), 0.015, True, shp.sym_list)
+        assert_close(loss_i[i].cpu().numpy(), ol.numpy(), "loss vs oracle", frac=1.0)
+        assert_close(dis_i[i].cpu().numpy(), od.numpy(), "dis vs oracle", frac=1.0)
+
+
+@pytest.mark.parametrize("n_mesh", [1, 17, 96, 97, 500, 2600])
+def test_refine_loss_ragged_mesh_sizes(n_mesh):
+    """Loss_refine splits the mesh over up to 32 CTAs per frame and the references over 3 warp groups:
+    ragged sizes, symmetric and not, against the oracle (dis, re-centred clouds, Jacobians)."""
+    shp = synth.Shape(64, 21, n_mesh, 8, 8, tuple(synth.YCB_SYM))
+    objs = [12, 3, 20]
+    frs = [synth.make_frame(shp, 4000 + n_mesh + i, obj=o, with_image=False) for i, o in enumerate(objs)]
+    rng = np.random.default_rng(n_mesh)
+    pr = np.stack([f["gt_q"] + 0.05 * rng.standard_normal(4) for f in frs]).astype(np.float32)
+    pt = np.stack([f["gt_t"] + 0.005 * rng.standard_normal(3) for f in frs]).astype(np.float32)
+    st = lambda key: tt(np.stack([f[key] for f in frs]), "cuda")
+    crit = Loss_refine(shp.num_mesh, list(shp.sym_list))
+    a, b = tt(pr, "cuda", grad=True), tt(pt, "cuda", grad=True)
+    dis, npts, ntgt = crit(a, b, st("target"), st("model_points"), tt(np.array(objs)[:, None], "cuda"), st("points"))
+    dis.sum().backward()
+    for i, f in enumerate(frs):
+        oa, ob = tt(pr[i:i + 1], grad=True), tt(pt[i:i + 1], grad=True)
+        od, onp, ont, _ = DO.refine_loss(oa, ob, tt(f["target"]), tt(f["model_points"]), objs[i], tt(f["points"]), shp.sym_list)
+        od.backward()
+        assert_close(dis[i].detach().cpu().numpy(), od.detach().numpy(), f"dis[{i}]", frac=1.0)
+        assert_close(npts[i].cpu().numpy(), onp.numpy(), "new_points")
+        assert_close(ntgt[i].cpu().numpy(), ont.numpy(), "new_target")
+        assert_close(a.grad[i].cpu().numpy(), oa.grad[0].numpy(), "g_pred_r", rtol=2e-3, frac=1.0)
+        assert_close(b.grad[i].cpu().numpy(), ob.grad[0].numpy(), "g_pred_t", rtol=2e-3, frac=1.0)
