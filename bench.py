@@ -123,6 +123,46 @@ def time_cpu_reference(work, params_pn, params_rf, frames, steps, warmup):
     return frames * steps / dt, dt
 
 
+def time_gpu_eager(work, pn, rf, frames, dev):
+    """Same-box GPU baseline: the reference's algorithm as eager PyTorch fp32 ops on the B200
+    (TF32 off), one frame at a time like tools/train.py:182-188.  Uses the oracle's restatement of the
+    network/loss (the reference's modules cannot travel) with the ADD-S nearest neighbour as torch.cdist +
+    argmin (the reference's knn.cu needs THC and cannot be built).  Reported for context only."""
+    from oracle import densefusion_oracle as DO
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    saved = DO.nearest_index
+    DO.nearest_index = lambda ref, qry, contract=True: torch.cdist(qry, ref).argmin(dim=1)
+    try:
+        p = {k: torch.from_numpy(v).to(dev) for k, v in pn.items()}
+        r = {k: torch.from_numpy(v).to(dev) for k, v in rf.items()}
+        w = {k: v[:frames].to(dev) for k, v in work.items()}
+
+        def run(n):
+            out = []
+            with torch.no_grad():
+                for f in range(n):
+                    obj = int(w["obj"][f, 0])                         # host sync, like idx[0].item() (lib/loss.py:40)
+                    pr, pt, pc, emb = DO.posenet_forward(p, w["out_img"][f], w["points"][f], w["choose"][f, 0], obj, SHAPE.num_obj)
+                    _, dis, npts, ntgt, _ = DO.pose_loss(pr, pt, pc, w["target"][f], w["model_points"][f], obj, w["points"][f],
+                                                         0.015, True, SHAPE.sym_list)
+                    for _ in range(2):
+                        rr, rt = DO.refiner_forward(r, npts, emb, obj, SHAPE.num_obj)
+                        dis, npts, ntgt, _ = DO.refine_loss(rr, rt, ntgt, w["model_points"][f], obj, npts, SHAPE.sym_list)
+                    out.append(float(dis))
+            return out
+        run(2)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        run(frames)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+    finally:
+        DO.nearest_index = saved
+    return {"value": frames / dt, "unit": "poses/s", "kind": "eager PyTorch fp32 (TF32 off) on the same B200, bs=1 loop",
+            "sample": f"{frames} frames ({dt:.2f} s)"}
+
+
 def knn_roofline(pk):
     """ADD-S 1-NN kernel at config C2 size (500 refs x 500 000 queries per frame, 8 frames)."""
     from plr2_b200.lib.knn import knn_indices
@@ -248,6 +288,7 @@ def run_ours(args, world, rank, local):
     ms_dev = max_over_ranks(e0.elapsed_time(e1))
     tc_ms, tc_n, tc_fl = C.c_double(), C.c_longlong(), C.c_double()
     L.plr2_profile_end(C.byref(tc_ms), C.byref(tc_n), C.byref(tc_fl))
+    tc_exec = float(L.plr2_profile_executed_flops())
     launches = L.plr2_launch_count() - launches0
     clocks = sampler.stop(t0, t1) if sampler else None
     value = world * frames * args.steps / (ms_dev / 1e3)
@@ -271,12 +312,18 @@ def run_ours(args, world, rank, local):
 
     # ---- rooflines, CPU baseline (rank 0, N == 1 only for the CPU leg) --------------------------
     achieved = tc_fl.value / (tc_ms.value / 1e3) / 1e12 if tc_ms.value > 0 else 0.0
+    executed = tc_exec / (tc_ms.value / 1e3) / 1e12 if tc_ms.value > 0 else 0.0
     peak = pk["bf16_tflops_sustained"]
-    roofline = {"bound": "tensor", "kernel": "gemm_bf16x2_kernel (tcgen05 kind::f16, split-bf16: 3 MMAs per algorithmic MAC)",
-                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
-                "executed_tflops": 3 * achieved, "frac_executed": 3 * achieved / peak,
+    traffic = None          # dram__bytes_{read,write}.sum per launch of this kernel, from the committed ncu capture
+    tp = os.path.join(ROOT, "profiles", "gemm_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get("avg_dram_bytes_per_launch")
+    roofline = {"bound": "tensor", "kernel": "gemm_bf16x2_kernel (tcgen05 cta_group::2 kind::f16 on split-bf16 operands: 3 MMAs per "
+                                             "algorithmic MAC, 2 for the pooled-only layers)",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                "executed_tflops": executed, "frac_executed": executed / peak,
                 "launches": int(tc_n.value), "avg_launch_ms": tc_ms.value / max(1, tc_n.value),
-                "share_of_step": tc_ms.value / (e0.elapsed_time(e1) * 0 + ms_dev) if ms_dev else None,
+                "share_of_step": tc_ms.value / ms_dev if ms_dev else None,
                 "peak_source": pk["source"] + " bf16_tflops_sustained"}
     knn = knn_roofline(pk)
     cpu = None
@@ -291,6 +338,9 @@ def run_ours(args, world, rank, local):
         ref = cpu_reference_step(work, pnt, rft, 2)
         got = [float(x) for x in res_host[:2]]
         cpu["check_first2_rel_err"] = [abs(a - b) / max(abs(b), 1e-12) for a, b in zip(got, ref)]
+    eager = None
+    if world == 1 and args.eager_frames > 0:
+        eager = time_gpu_eager(work, pn, rf, args.eager_frames, dev)
     line = {
         "metric": METRIC, "value": value, "unit": "poses/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
@@ -309,6 +359,7 @@ def run_ours(args, world, rank, local):
         "roofline_knn": knn,
         "knn_gpairs_per_s": {k: v["Gpairs_s"] for k, v in knn.items()},
         "cpu_baseline": cpu,
+        "gpu_eager_baseline": eager,
     }
     print(json.dumps(line), flush=True)
 
@@ -325,6 +376,8 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=8, help="frames of the CPU baseline sample (0 = skip)")
     ap.add_argument("--profile-step", action="store_true",
                     help="run ONE step between cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)")
+    ap.add_argument("--eager-frames", type=int, default=16,
+                    help="frames of the same-box eager-PyTorch GPU baseline (reference algorithm, fp32, bs=1 loop; 0 = skip)")
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the reference arm")
     args = ap.parse_args()
     world, rank, local = dist_setup(args)

@@ -50,6 +50,7 @@ long long   plr2_launch_count(void);        /* kernels launched by this library 
  * the summed kernel time (ms), launch count and algorithmic FLOPs (2 M N K) of those launches. */
 int         plr2_profile_begin(void);
 int         plr2_profile_end(double *ms, long long *launches, double *flops);
+double      plr2_profile_executed_flops(void);  /* bf16 MMA FLOPs issued in the last window (2-3x the algorithmic) */
 
 /* ---- (4) brute-force nearest neighbours ---------------------------------------------------
  * ref   [batch][dim][n_ref]   f32, contiguous        (lib/knn/src/knn.h:33)

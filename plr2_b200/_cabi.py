@@ -18,6 +18,7 @@ SIGNATURES = {
     "plr2_launch_count": (C.c_longlong, []),
     "plr2_profile_begin": (_i, []),
     "plr2_profile_end": (_i, [C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.POINTER(C.c_double)]),
+    "plr2_profile_executed_flops": (C.c_double, []),
     "plr2_knn_workspace_bytes": (_sz, [_i] * 5),
     "plr2_knn_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "plr2_pose_loss_fwd": (_i, [_vp] * 8 + [_i] * 4 + [_f, _i, _i] + [_vp] * 5),

@@ -602,6 +602,7 @@ struct TcProfile {
   std::vector<cudaEvent_t> ev;      // pairs
   size_t used = 0;
   double flops = 0.0;
+  double executed = 0.0;   // tensor-core FLOPs actually issued (2 or 3 MMAs per algorithmic MAC)
   long long launches = 0;
 };
 static TcProfile g_prof;
@@ -690,6 +691,7 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   if (g_prof.on) {
     cudaEventRecord(prof_event(), st);
     g_prof.flops += 2.0 * g.M * g.N * g.K * g.batch;
+    g_prof.executed += 2.0 * g.M * g.N * g.K * g.batch * NPROD;
     g_prof.launches += 1;
   }
   return check_launch("gemm_bf16x2");
@@ -745,7 +747,7 @@ extern "C" int plr2_gemm_bf16x2(const void *A_planes, long long lda, long long a
 // the number of launches and their algorithmic FLOPs (2 M N K per problem; the kernel executes 3x
 // that many bf16 tensor-core FLOPs).
 extern "C" int plr2_profile_begin(void) {
-  plr2::g_prof.on = true; plr2::g_prof.used = 0; plr2::g_prof.flops = 0.0; plr2::g_prof.launches = 0;
+  plr2::g_prof.on = true; plr2::g_prof.used = 0; plr2::g_prof.flops = 0.0; plr2::g_prof.executed = 0.0; plr2::g_prof.launches = 0;
   return 0;
 }
 extern "C" int plr2_profile_end(double *ms, long long *launches, double *flops) {
@@ -763,3 +765,6 @@ extern "C" int plr2_profile_end(double *ms, long long *launches, double *flops) 
   if (flops) *flops = g_prof.flops;
   return 0;
 }
+// bf16 tensor-core FLOPs issued by the launches of the last begin/end window (>= the algorithmic FLOPs:
+// split-bf16 layers cost 3 MMAs per MAC, hi-only-activation layers 2).
+extern "C" double plr2_profile_executed_flops(void) { return plr2::g_prof.executed; }
