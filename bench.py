@@ -240,7 +240,8 @@ def run_ours(args, world, rank, local):
     frames = args.frames
     knn_mode = ops.KNN_FAST if args.knn == "fast" else ops.KNN_EXACT
     pipe = DenseFusionPipeline(SHAPE.num_points, SHAPE.num_obj, SHAPE.num_mesh, SHAPE.sym_list, device=dev,
-                               precision=ops.PREC_BF16X2, knn_mode=knn_mode, chunk_frames=args.chunk)
+                               precision=ops.PREC_BF16X2, knn_mode=knn_mode, chunk_frames=args.chunk,
+                               host_chunk_frames=args.host_chunk)
     pn = synth.make_params("posenet", SHAPE.num_obj, 1)
     rf = synth.make_params("refiner", SHAPE.num_obj, 2)
     pipe.load_params(pn, rf)
@@ -347,7 +348,7 @@ def run_ours(args, world, rank, local):
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16x2-split operands, f32 accumulate (f32 SIMT for small layers/losses)",
         "data": "synthetic",
         "config": {"workload": "C4: YCB-shaped frames, PoseNet(out_img given)+Loss(refine)+2x(PoseRefineNet+Loss_refine ADD-S)",
-                   "frames_per_gpu_per_step": frames, "chunk_frames": args.chunk, "num_points": SHAPE.num_points,
+                   "frames_per_gpu_per_step": frames, "chunk_frames": args.chunk, "host_chunk_frames": args.host_chunk, "num_points": SHAPE.num_points,
                    "num_mesh": SHAPE.num_mesh, "num_obj": SHAPE.num_obj, "crop": [SHAPE.height, SHAPE.width],
                    "knn_mode": args.knn, "l2": "inputs (%.0f MB per step) larger than L2" % (h2d / 1e6),
                    "results_finite": finite},
@@ -371,7 +372,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=512, help="frames per GPU per step (config C4)")
-    ap.add_argument("--chunk", type=int, default=64, help="frames per launch chunk")
+    ap.add_argument("--chunk", type=int, default=512, help="frames per launch chunk, device-resident path")
+    ap.add_argument("--host-chunk", type=int, default=64, help="frames per chunk of the host (e2e) path: H2D of chunk i+1 overlaps chunk i")
     ap.add_argument("--knn", default="exact", choices=["exact", "fast"])
     ap.add_argument("--cpu-frames", type=int, default=8, help="frames of the CPU baseline sample (0 = skip)")
     ap.add_argument("--profile-step", action="store_true",

@@ -25,8 +25,8 @@ INPUT_KEYS = ("out_img", "points", "choose", "obj", "target", "model_points")
 
 class DenseFusionPipeline:
     def __init__(self, num_points, num_obj, num_mesh, sym_list, device="cuda", precision=ops.PREC_BF16X2,
-                 knn_mode=ops.KNN_EXACT, refine_iters=2, chunk_frames=64, w=0.015, refine_start=True,
-                 with_backbone=False):
+                 knn_mode=ops.KNN_EXACT, refine_iters=2, chunk_frames=512, w=0.015, refine_start=True,
+                 with_backbone=False, host_chunk_frames=64):
         self.device = torch.device(device)
         self.estimator = PoseNet(num_points, num_obj, precision=precision)
         if not with_backbone:
@@ -36,7 +36,8 @@ class DenseFusionPipeline:
         self.criterion = Loss(num_mesh, list(sym_list), knn_mode)
         self.criterion_refine = Loss_refine(num_mesh, list(sym_list), knn_mode)
         self.refine_iters = refine_iters
-        self.chunk_frames = chunk_frames
+        self.chunk_frames = chunk_frames            # device-resident path: large chunks amortise launches and tile tails
+        self.host_chunk_frames = host_chunk_frames  # host path: smaller chunks so the H2D copy of chunk i+1 overlaps chunk i
         self.w = w
         self.refine_start = refine_start
         self._staging = None
@@ -75,7 +76,7 @@ class DenseFusionPipeline:
         into two alternating device staging sets while the previous chunk computes; the per-frame
         result comes back to (pinned) host memory.  Returns a CPU tensor (F,)."""
         F = host["out_img"].shape[0]
-        cf = min(self.chunk_frames, F)
+        cf = min(self.host_chunk_frames, F)
         dev = self.device
         if self._staging is None or self._staging[0]["out_img"].shape[0] != cf or \
                 any(self._staging[0][k].shape[1:] != host[k].shape[1:] for k in INPUT_KEYS):
