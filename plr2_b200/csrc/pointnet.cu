@@ -15,6 +15,7 @@ namespace plr2 {
 // layout, and writes relu(conv1(x)) | relu(e_conv1(emb)) into columns [0,64) | [64,128) of the
 // point-major feature buffer pf (ld 384).
 constexpr int FL_THREADS = 128;
+constexpr int FL_PITCH = 144;      // bytes per staged row: 128 + 16 pad
 
 template <bool OUT_BF16>
 __global__ void __launch_bounds__(FL_THREADS)
@@ -27,6 +28,7 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
   __shared__ __align__(16) float sw1[64 * 4];
   __shared__ __align__(16) float swe[64 * 32];
   __shared__ float sb1[64], sbe[64];
+  __shared__ __align__(16) uint8_t tile[OUT_BF16 ? FL_THREADS / 32 : 1][2][OUT_BF16 ? 32 * FL_PITCH : 16];
   // weight staging: all loads of a thread in flight at once (16-byte, packed buffer offsets are 128-byte aligned)
   {
     const float4 *g1 = reinterpret_cast<const float4 *>(c1w), *ge = reinterpret_cast<const float4 *>(e1w);
@@ -48,8 +50,9 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
   }
   __syncthreads();
   const int f = blockIdx.y;
-  const int n = blockIdx.x * FL_THREADS + threadIdx.x;
-  if (n >= N) return;
+  const int n_raw = blockIdx.x * FL_THREADS + threadIdx.x;
+  const bool live = n_raw < N;
+  const int n = live ? n_raw : N - 1;               // dead lanes shadow the last point (no stores)
   const size_t row = (size_t)f * N + n;
   float e[32];
   if (choose != nullptr) {
@@ -63,12 +66,12 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
 #pragma unroll
     for (int ch = 0; ch < 32; ++ch) e[ch] = __ldg(src + (size_t)ch * N);
   }
-  if (emb_out != nullptr) {
+  if (emb_out != nullptr && live) {
     float *dst = emb_out + (size_t)f * 32 * N + n;
 #pragma unroll
     for (int ch = 0; ch < 32; ++ch) dst[(size_t)ch * N] = e[ch];
   }
-  if (embT != nullptr) {
+  if (embT != nullptr && live) {
     float4 *dst = reinterpret_cast<float4 *>(embT + row * 32);
 #pragma unroll
     for (int q = 0; q < 8; ++q) dst[q] = make_float4(e[4 * q], e[4 * q + 1], e[4 * q + 2], e[4 * q + 3]);
@@ -109,10 +112,29 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
         hi[q] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
         lo[q] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
       }
-      __nv_bfloat16 *d = pfb + row * 384 + o8 * 8;
-      *reinterpret_cast<uint4 *>(d) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-      if (pf_plane != 0) *reinterpret_cast<uint4 *>(d + pf_plane) = make_uint4(lo[0], lo[1], lo[2], lo[3]);   // 0: hi-only consumers
-    } else {
+      // Stage 64 output columns of the warp's 32 points ([32][8 x 16 B], pitch 144 B: conflict-free), then
+      // write them out as 128-byte row segments (4 rows per instruction instead of 32 scattered 16-byte pieces).
+      const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+      uint8_t *th = tile[wrp][0], *tl = tile[wrp][1];
+      *reinterpret_cast<uint4 *>(th + lane * FL_PITCH + (o8 & 7) * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      if (pf_plane != 0) *reinterpret_cast<uint4 *>(tl + lane * FL_PITCH + (o8 & 7) * 16) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      if ((o8 & 7) == 7) {
+        __syncwarp();
+        const int n_warp0 = blockIdx.x * FL_THREADS + wrp * 32;              // first point of this warp
+        const int seg = lane & 7, rsub = lane >> 3;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = 4 * i + rsub;
+          if (n_warp0 + r < N) {
+            __nv_bfloat16 *d = pfb + ((size_t)f * N + n_warp0 + r) * 384 + (o8 >> 3) * 64 + seg * 8;
+            *reinterpret_cast<uint4 *>(d) = *reinterpret_cast<const uint4 *>(th + r * FL_PITCH + seg * 16);
+            if (pf_plane != 0)                                               // 0: hi-only consumers
+              *reinterpret_cast<uint4 *>(d + pf_plane) = *reinterpret_cast<const uint4 *>(tl + r * FL_PITCH + seg * 16);
+          }
+        }
+        __syncwarp();
+      }
+    } else if (live) {
       float4 *d = reinterpret_cast<float4 *>(pf + row * 384 + o8 * 8);
       d[0] = make_float4(v[0], v[1], v[2], v[3]);
       d[1] = make_float4(v[4], v[5], v[6], v[7]);
