@@ -306,7 +306,7 @@ def run_ours(args, world, rank, local):
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
     e2e = world * frames * args.steps / (ms_e2e / 1e3)
     h2d = DenseFusionPipeline.bytes_per_frame(host) * frames
-    d2h = frames * 4
+    d2h = frames * 4 + frames * 12 * 4       # per-frame distance + refined pose (R | t)
     finite = bool(torch.isfinite(res_host).all()) and bool(torch.isfinite(res).all())
     if rank != 0:
         return

@@ -116,6 +116,11 @@ int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t,
                          float *jac_r, float *jac_t, float *pose_out,
                          void *workspace, size_t workspace_bytes, void *stream);
 
+/* Pose hand-off between refinement stages (tools/train.py:141-145; the composition DenseFusion's evaluation
+ * performs): pose_acc [F][12] (R row-major, t) <- pose_acc o pose_delta, i.e. R <- R Rd, t <- R td + t, where
+ * pose_delta is the pose_out of the NEXT stage (estimated in the frame re-centred by pose_acc). */
+int plr2_pose_compose(float *pose_acc, const float *pose_delta, int frames, void *stream);
+
 /* ---- (2) dense contractions --------------------------------------------------------------
  * General FP32 GEMM with fused epilogue, C(m,n) (+)= f(sum_k A(m,k) B(k,n)):
  *   A(m,k) = A[m*sam + k*sak],  B(k,n) = B[k*sbk + n*sbn],  C(m,n) = C[m*ldc + n]

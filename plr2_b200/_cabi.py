@@ -24,6 +24,7 @@ SIGNATURES = {
     "plr2_pose_loss_fwd": (_i, [_vp] * 8 + [_i] * 4 + [_f, _i, _i] + [_vp] * 5),
     "plr2_pose_loss_bwd": (_i, [_vp] * 7 + [_i, _i, _f] + [_vp] * 4),
     "plr2_pose_select": (_i, [_vp] * 6 + [_i] * 3 + [_vp] * 6),
+    "plr2_pose_compose": (_i, [_vp, _vp, _i, _vp]),
     "plr2_refine_loss_workspace_bytes": (_sz, [_i, _i]),
     "plr2_refine_loss_fwd": (_i, [_vp] * 7 + [_i] * 5 + [_vp] * 6 + [_vp, _sz, _vp]),
 }

@@ -686,6 +686,27 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
   }
 }
 
+// Pose composition across refinement stages (kernel (5), tools/train.py:141-145 hand-off): the stage
+// pose (Rd, td) lives in the frame re-centred by the accumulated pose (R, t), x_rc = R^T (x - t), hence
+//   R <- R Rd,   t <- R td + t.
+__global__ void __launch_bounds__(128)
+pose_compose_kernel(float *__restrict__ acc, const float *__restrict__ delta, int frames) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= frames) return;
+  float R[9], t[3], D[9], d[3];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) { R[i] = acc[(size_t)f * 12 + i]; D[i] = delta[(size_t)f * 12 + i]; }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { t[i] = acc[(size_t)f * 12 + 9 + i]; d[i] = delta[(size_t)f * 12 + 9 + i]; }
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      acc[(size_t)f * 12 + 3 * r + c] = R[3 * r] * D[c] + R[3 * r + 1] * D[3 + c] + R[3 * r + 2] * D[6 + c];
+    acc[(size_t)f * 12 + 9 + r] = R[3 * r] * d[0] + R[3 * r + 1] * d[1] + R[3 * r + 2] * d[2] + t[r];
+  }
+}
+
 static int set_dyn_smem(const void *fn, size_t bytes) {
   if (bytes <= 48 * 1024) return 0;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
@@ -828,4 +849,12 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
   else PLR2_LAUNCH_ADDS(refine_loss_kernel, false, false, grid, REFINE_THREADS, smem, st, ARGS);
 #undef ARGS
   return check_launch("plr2_refine_loss_fwd");
+}
+
+extern "C" int plr2_pose_compose(float *pose_acc, const float *pose_delta, int frames, void *stream) {
+  if (frames < 0) { set_error("plr2_pose_compose: bad shape"); return PLR2_E_SHAPE; }
+  if (frames == 0) return 0;
+  if (!pose_acc || !pose_delta) { set_error("plr2_pose_compose: null pointer"); return PLR2_E_NULLPTR; }
+  pose_compose_kernel<<<(frames + 127) / 128, 128, 0, (cudaStream_t)stream>>>(pose_acc, pose_delta, frames);
+  return check_launch("plr2_pose_compose");
 }

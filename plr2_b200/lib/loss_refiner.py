@@ -11,9 +11,11 @@ def loss_calculation(pred_r, pred_t, target, model_points, idx, points, num_poin
                      knn_mode=ops.KNN_EXACT):
     F = target.shape[0] if target.dim() == 3 else 1
     lut = ops.sym_lut(sym_list, pred_r.device)
-    return ops.RefineLossFn.apply(pred_r, pred_t, target.reshape(F, num_point_mesh, 3),
-                                  model_points.reshape(F, num_point_mesh, 3), idx,
-                                  points.reshape(F, -1, 3), lut, knn_mode)
+    dis, new_points, new_target, pose = ops.RefineLossFn.apply(
+        pred_r, pred_t, target.reshape(F, num_point_mesh, 3), model_points.reshape(F, num_point_mesh, 3), idx,
+        points.reshape(F, -1, 3), lut, knn_mode)
+    loss_calculation.last_pose = pose    # (F,12): this stage's R (row-major) | t
+    return dis, new_points, new_target
 
 
 class Loss_refine(_Loss):
@@ -25,5 +27,7 @@ class Loss_refine(_Loss):
         self.knn_mode = knn_mode
 
     def forward(self, pred_r, pred_t, target, model_points, idx, points):
-        return loss_calculation(pred_r, pred_t, target, model_points, idx, points, self.num_pt_mesh,
-                                self.sym_list, self.knn_mode)
+        out = loss_calculation(pred_r, pred_t, target, model_points, idx, points, self.num_pt_mesh,
+                               self.sym_list, self.knn_mode)
+        self.last_pose = loss_calculation.last_pose
+        return out

@@ -37,7 +37,7 @@ def _need_cuda(t, what):
 
 class PoseLossFn(torch.autograd.Function):
     """Loss (lib/loss.py:12-69) for F frames.  Returns loss (F,), dis_sel (F,), new_points (F,N,3),
-    new_target (F,M,3), dis_all (F,N), which_max (F,) int32."""
+    new_target (F,M,3), dis_all (F,N), which_max (F,) int32, pose (F,12) = selected R* (row-major) | t*."""
 
     @staticmethod
     def forward(ctx, pred_r, pred_t, pred_c, target, model_points, obj, points, w, refine, lut, knn_mode):
@@ -57,6 +57,7 @@ class PoseLossFn(torch.autograd.Function):
         dis_sel = torch.empty((F,), dtype=torch.float32, device=dev)
         new_points = torch.empty((F, N, 3), dtype=torch.float32, device=dev)
         new_target = torch.empty((F, M, 3), dtype=torch.float32, device=dev)
+        pose = torch.empty((F, 12), dtype=torch.float32, device=dev)
         L = _cabi.lib()
         with torch.cuda.device(dev):
             st = _cabi.stream_ptr(dev)
@@ -67,14 +68,14 @@ class PoseLossFn(torch.autograd.Function):
             _cabi.check(rc, "plr2_pose_loss_fwd")
             rc = L.plr2_pose_select(_cabi.ptr(pr), _cabi.ptr(pt), _cabi.ptr(pc), _cabi.ptr(dis), _cabi.ptr(tg),
                                     _cabi.ptr(ps), F, N, M, _cabi.ptr(which), _cabi.ptr(dis_sel),
-                                    _cabi.ptr(new_points), _cabi.ptr(new_target), None, st)
+                                    _cabi.ptr(new_points), _cabi.ptr(new_target), _cabi.ptr(pose), st)
             _cabi.check(rc, "plr2_pose_select")
         if need_jac:
             ctx.save_for_backward(pc, dis, jac_r, jac_t, which)
         ctx.w = float(w)
         ctx.shapes = (pred_r.shape, pred_t.shape, pred_c.shape)
-        ctx.mark_non_differentiable(new_points, new_target, dis, which)
-        return loss, dis_sel, new_points, new_target, dis, which
+        ctx.mark_non_differentiable(new_points, new_target, dis, which, pose)
+        return loss, dis_sel, new_points, new_target, dis, which, pose
 
     @staticmethod
     def backward(ctx, g_loss, g_dis_sel, *_):
@@ -114,20 +115,21 @@ class RefineLossFn(torch.autograd.Function):
         jac_t = torch.empty((F, 3), dtype=torch.float32, device=dev) if need_jac else None
         new_points = torch.empty((F, N, 3), dtype=torch.float32, device=dev)
         new_target = torch.empty((F, M, 3), dtype=torch.float32, device=dev)
+        pose = torch.empty((F, 12), dtype=torch.float32, device=dev)
         nws = _cabi.lib().plr2_refine_loss_workspace_bytes(F, M)
         ws = torch.empty(nws, dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             rc = _cabi.lib().plr2_refine_loss_fwd(_cabi.ptr(pr), _cabi.ptr(pt), _cabi.ptr(tg), _cabi.ptr(mp),
                                                   _cabi.ptr(ps), _cabi.ptr(ob), _cabi.ptr(lut), int(lut.numel()),
                                                   F, N, M, int(knn_mode), _cabi.ptr(dis), _cabi.ptr(new_points),
-                                                  _cabi.ptr(new_target), _cabi.ptr(jac_r), _cabi.ptr(jac_t), None,
-                                                  _cabi.ptr(ws), nws, _cabi.stream_ptr(dev))
+                                                  _cabi.ptr(new_target), _cabi.ptr(jac_r), _cabi.ptr(jac_t),
+                                                  _cabi.ptr(pose), _cabi.ptr(ws), nws, _cabi.stream_ptr(dev))
         _cabi.check(rc, "plr2_refine_loss_fwd")
         if need_jac:
             ctx.save_for_backward(jac_r, jac_t)
         ctx.shapes = (pred_r.shape, pred_t.shape)
-        ctx.mark_non_differentiable(new_points, new_target)
-        return dis, new_points, new_target
+        ctx.mark_non_differentiable(new_points, new_target, pose)
+        return dis, new_points, new_target, pose
 
     @staticmethod
     def backward(ctx, g_dis, *_):
@@ -312,6 +314,17 @@ class RefinerFn(torch.autograd.Function):
         grads = _unpack_grads(NET_REFINER, state.num_obj, gp, ctx.params, dev)
         ctx.saved = None
         return (None, None, None, None, None, None) + tuple(grads)
+
+
+def pose_compose_(pose_acc, pose_delta):
+    """In place: pose_acc (F,12) <- pose_acc o pose_delta (R <- R Rd, t <- R td + t)."""
+    _need_cuda(pose_acc, "pose_compose_")
+    assert pose_acc.is_contiguous() and pose_delta.is_contiguous() and pose_acc.shape == pose_delta.shape
+    with torch.cuda.device(pose_acc.device):
+        rc = _cabi.lib().plr2_pose_compose(_cabi.ptr(pose_acc), _cabi.ptr(pose_delta), pose_acc.shape[0],
+                                           _cabi.stream_ptr(pose_acc.device))
+    _cabi.check(rc, "plr2_pose_compose")
+    return pose_acc
 
 
 def tensor_core_profile(fn):

@@ -55,20 +55,25 @@ class DenseFusionPipeline:
                                                         self.refine_start)
         if dis.dim() == 0:
             dis = dis.reshape(1)
+        pose = self.criterion.last_pose.clone()          # (F,12) camera-frame pose after the best vote
         for _ in range(self.refine_iters):
             rr, rt = self.refiner(new_points, emb, obj)
             dis, new_points, new_target = self.criterion_refine(rr, rt, new_target, model_points, obj, new_points)
-        return dis
+            ops.pose_compose_(pose, self.criterion_refine.last_pose)    # stays on the device (kernel (5))
+        return dis, pose
 
     @torch.no_grad()
-    def infer(self, out_img, points, choose, obj, target, model_points):
-        """Device-resident inputs (F, ...).  Returns the final ADD / ADD-S distance per frame (F,)."""
+    def infer(self, out_img, points, choose, obj, target, model_points, return_pose=False):
+        """Device-resident inputs (F, ...).  Returns the final ADD / ADD-S distance per frame (F,) and, with
+        return_pose, the refined camera-frame poses (F,12) = R row-major | t."""
         F = out_img.shape[0]
         out = torch.empty(F, dtype=torch.float32, device=out_img.device)
+        poses = torch.empty((F, 12), dtype=torch.float32, device=out_img.device)
         for a in range(0, F, self.chunk_frames):
             b = min(F, a + self.chunk_frames)
-            out[a:b] = self._chunk(out_img[a:b], points[a:b], choose[a:b], obj[a:b], target[a:b], model_points[a:b])
-        return out
+            out[a:b], poses[a:b] = self._chunk(out_img[a:b], points[a:b], choose[a:b], obj[a:b], target[a:b],
+                                               model_points[a:b])
+        return (out, poses) if return_pose else out
 
     @torch.no_grad()
     def infer_host(self, host):
@@ -86,7 +91,9 @@ class DenseFusionPipeline:
             self._ready = [torch.cuda.Event() for _ in range(2)]
             self._free = [torch.cuda.Event() for _ in range(2)]
         res_dev = torch.empty(F, dtype=torch.float32, device=dev)
+        pose_dev = torch.empty((F, 12), dtype=torch.float32, device=dev)
         res_host = torch.empty(F, dtype=torch.float32, pin_memory=True)
+        pose_host = torch.empty((F, 12), dtype=torch.float32, pin_memory=True)
         main = torch.cuda.current_stream(dev)
         chunks = [(a, min(F, a + cf)) for a in range(0, F, cf)]
 
@@ -107,10 +114,12 @@ class DenseFusionPipeline:
             main.wait_event(self._ready[i & 1])
             s = self._staging[i & 1]
             n = b - a
-            res_dev[a:b] = self._chunk(*(s[k][:n] for k in INPUT_KEYS))
+            res_dev[a:b], pose_dev[a:b] = self._chunk(*(s[k][:n] for k in INPUT_KEYS))
             self._free[i & 1].record(main)
         res_host.copy_(res_dev, non_blocking=True)
+        pose_host.copy_(pose_dev, non_blocking=True)
         main.synchronize()
+        self.last_poses = pose_host          # (F,12) refined poses of this call
         return res_host
 
     @staticmethod

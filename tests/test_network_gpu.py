@@ -262,3 +262,42 @@ def test_tensor_core_full_size_vs_oracle_and_fp32_path(frames):
         # where the frame starts in the batch: equal to fp32 rounding, not bit for bit
         for x, y in zip(a[:3], (pr, pt, pc)):
             assert_close(x[0].cpu().numpy(), y[2].cpu().numpy(), "batched vs single", rtol=1e-4, frac=1.0)
+
+
+def test_pipeline_refined_pose_matches_oracle_composition():
+    """Kernel (5): the refine chain stays on the device and the per-stage poses are composed there
+    (R <- R Rd, t <- R td + t).  Against the oracle chain of tools/train.py:182-188 for 3 frames."""
+    from plr2_b200.pipeline import DenseFusionPipeline, INPUT_KEYS
+    shp = synth.Shape(1000, 21, 400, 40, 40, tuple(synth.YCB_SYM))
+    pipe = DenseFusionPipeline(shp.num_points, shp.num_obj, shp.num_mesh, shp.sym_list, device="cuda:0",
+                               precision=ops.PREC_BF16X2, chunk_frames=2, refine_iters=2)
+    pn = synth.make_params("posenet", shp.num_obj, 31)
+    rf = synth.make_params("refiner", shp.num_obj, 32)
+    pipe.load_params(pn, rf)
+    frs = [synth.make_frame(shp, 300 + i, obj=o) for i, o in enumerate([12, 3, 19])]
+    st = lambda k: tt(np.stack([f[k] for f in frs]), "cuda")
+    work = {"out_img": st("out_img"), "points": st("points"), "choose": st("choose")[:, None], "obj": st("idx")[:, None],
+            "target": st("target"), "model_points": st("model_points")}
+    dis, pose = pipe.infer(*(work[k] for k in INPUT_KEYS), return_pose=True)
+    p = {k: tt(v) for k, v in pn.items()}
+    r = {k: tt(v) for k, v in rf.items()}
+    for i, fr in enumerate(frs):
+        obj = int(fr["idx"])
+        with torch.no_grad():
+            pr, pt, pc, emb = DO.posenet_forward(p, tt(fr["out_img"]), tt(fr["points"]), tt(fr["choose"]), obj, shp.num_obj)
+            _, d, npts, ntgt, ex = DO.pose_loss(pr, pt, pc, tt(fr["target"]), tt(fr["model_points"]), obj, tt(fr["points"]),
+                                                0.015, True, shp.sym_list)
+            R, t = ex["R"].double(), ex["t"].double()
+            for _ in range(2):
+                rr, rt = DO.refiner_forward(r, npts, emb, obj, shp.num_obj)
+                d, npts, ntgt, ex = DO.refine_loss(rr, rt, ntgt, tt(fr["model_points"]), obj, npts, shp.sym_list)
+                t = R @ ex["t"].double() + t
+                R = R @ ex["R"].double()
+        assert_close(dis[i].cpu().numpy(), d.numpy(), "final dis", rtol=2e-3, frac=1.0)
+        assert_close(pose[i, :9].cpu().numpy(), R.numpy().reshape(-1), "composed R", frac=1.0)
+        assert_close(pose[i, 9:].cpu().numpy(), t.numpy(), "composed t", frac=1.0)
+        # the composed pose maps the model onto the (re-assembled) target cloud about as well as `dis` says
+        m = tt(fr["model_points"]).double()
+        pred = m @ R.T + t
+        if obj not in shp.sym_list:
+            assert abs(float((pred - tt(fr["target"]).double()).norm(dim=1).mean()) - float(d)) < 1e-4
