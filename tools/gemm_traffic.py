@@ -14,7 +14,7 @@ for r in data:
     if "gemm_bf16x2_kernel" not in r[idx["Kernel Name"]]:
         continue
     per.append({"kernel": r[idx["Kernel Name"]].split("(")[0].replace("void plr2::", ""),
-                "us": float(r[idx["gpu__time_duration.sum"]]),
+                "us": float(r[idx["gpu__time_duration.sum"]]) * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(units[idx["gpu__time_duration.sum"]], 1.0),
                 "dram_read": val(r, "dram__bytes_read.sum"), "dram_write": val(r, "dram__bytes_write.sum")})
 tot = sum(p["dram_read"] + p["dram_write"] for p in per)
 print(json.dumps({"source": sys.argv[1] if len(sys.argv) > 1 else "", "launches": len(per),

@@ -15,13 +15,15 @@ cols = [("gpu__time_duration.sum", "us"), ("launch__grid_size", "grid"), ("launc
         ("dram__bytes_read.sum", "dramR"), ("dram__bytes_write.sum", "dramW")]
 cols = [(m, n) for m, n in cols if m in idx]
 print(f"{'kernel':34s} " + " ".join(f"{n:>8s}" for _, n in cols))
-print(f"{'':34s} " + " ".join(f"{units[idx[m]][:8]:>8s}" for m, _ in cols))
+SCALE = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6, "byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}
+NORM = {"ns": "us", "us": "us", "ms": "us", "s": "us", "byte": "Mbyte", "Kbyte": "Mbyte", "Mbyte": "Mbyte", "Gbyte": "Mbyte"}
+print(f"{'':34s} " + " ".join(f"{NORM.get(units[idx[m]], units[idx[m]])[:8]:>8s}" for m, _ in cols))
 for r in data:
     name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "").replace("plr2::", "")[:34]
     vals = []
     for m, _ in cols:
         try:
-            vals.append(f"{float(r[idx[m]].replace(',', '')):8.1f}")
+            vals.append(f"{float(r[idx[m]].replace(',', '')) * SCALE.get(units[idx[m]], 1.0):8.1f}")
         except ValueError:
             vals.append(f"{r[idx[m]]:>8s}")
     print(f"{name:34s} " + " ".join(vals))
