@@ -49,7 +49,8 @@ template <int BN, int NPROD, int CG> struct TcCfg {
   static constexpr int TMEM_COLS = 2 * BN;                      // two accumulator stages
   static constexpr int EPI_BYTES = TC_EPI_WARPS * TC_SLABS * TC_SLAB_BYTES;   // per-warp rings of output slabs
   static constexpr int BIAS_BYTES = 2 * BN * 4;                             // [frame a|b][BN] staged bias of the current tile
-  static constexpr int FIXED_BYTES = 256 /*barriers*/ + EPI_BYTES + BIAS_BYTES;
+  static constexpr int HEAD_BYTES = BN == 128 ? (2 * 4 * 128 + 8) * 4 + 128 * 4 * 4 : 0;   // TC_OUT_HEAD: class weights + half-sum exchange
+  static constexpr int FIXED_BYTES = 256 /*barriers*/ + EPI_BYTES + BIAS_BYTES + HEAD_BYTES;
   static constexpr int STAGES_FIT = (232448 - FIXED_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES;
@@ -68,6 +69,8 @@ struct TcKernelArgs {
   float *Cf; long long ldc;
   __nv_bfloat16 *Cb; long long ldcb, c_plane;
   float *pool;                   // [ceil(M/32)][2][N]
+  const float *w4, *b4; const int64_t *obj; int num_obj;   // TC_OUT_HEAD
+  float *pred_r, *pred_t, *pred_c;
   int tma_store;                 // tile outputs leave through TMA stores (maps tmC_*)
   int debug;                     // PLR2_TC_DEBUG (timing experiments only): 1 = no global stores, 2 = no epilogue work
 };
@@ -214,8 +217,36 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         bv[u] = v;
       }
     };
-    float bnext[2] = {0.f, 0.f};
-    if (unit < num_tiles) load_bias(unit, bnext);
+    // TC_OUT_HEAD: last-layer weights of head z for the classes of the tile's <= 2 frames, slots
+    // i = te + u*256 of sW = [frame a|b][4 outputs][128] (+ 8 biases at the end)
+    float *sW = sB + 2 * BN;
+    float *sX = sW + 2 * 4 * 128 + 8;                     // [128 rows][4] partial dots of the upper column half
+    auto load_headw = [&](int t, float (&wv)[5]) {
+      const int z = t / tiles_per_z, r = t % tiles_per_z;
+      const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM;
+      const int fa = m0 / g.rows_per_frame;
+      const int nout = z == 0 ? 4 : (z == 1 ? 3 : 1), base = z == 0 ? 0 : (z == 1 ? 4 * g.num_obj : 7 * g.num_obj);
+#pragma unroll
+      for (int u = 0; u < 5; ++u) {
+        const int i = te + u * 32 * TC_EPI_WARPS;           // u == 4: the 8 biases
+        const int sel = u < 4 ? i >> 9 : (te >> 2) & 1, j = u < 4 ? (i >> 7) & 3 : te & 3;
+        long long fr = fa + sel;
+        if (fr * g.rows_per_frame >= g.M) fr = fa;
+        long long o = __ldg(g.obj + fr);
+        o = o < 0 ? 0 : (o >= g.num_obj ? g.num_obj - 1 : o);
+        float v = 0.f;
+        if (j < nout) {
+          if (u < 4) v = __ldg(g.w4 + (size_t)(base + o * nout + j) * 128 + (i & 127));
+          else if (te < 8) v = __ldg(g.b4 + base + o * nout + j);
+        }
+        wv[u] = v;
+      }
+    };
+    float bnext[2] = {0.f, 0.f}, wnext[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    if (unit < num_tiles) {
+      load_bias(unit, bnext);
+      if (BN == 128 && g.out_mode == TC_OUT_HEAD) load_headw(unit, wnext);
+    }
     for (int t = unit; t < num_tiles; t += n_units) {
       const int z = t / tiles_per_z, r = t % tiles_per_z;
       const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = (r % g.n_tiles) * BN;
@@ -229,12 +260,20 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         const int i = te + u * 32 * TC_EPI_WARPS;
         if (i < 2 * BN) sB[i] = bnext[u];
       }
-      if (t + n_units < num_tiles) load_bias(t + n_units, bnext);
+      if (BN == 128 && g.out_mode == TC_OUT_HEAD) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) sW[te + u * 32 * TC_EPI_WARPS] = wnext[u];
+        if (te < 8) sW[2 * 4 * 128 + te] = wnext[4];
+      }
+      if (t + n_units < num_tiles) {
+        load_bias(t + n_units, bnext);
+        if (BN == 128 && g.out_mode == TC_OUT_HEAD) load_headw(t + n_units, wnext);
+      }
       named_bar_sync(1, 32 * TC_EPI_WARPS);
       mbar_wait(tfull_bar + as, aphase);
       fence_after_sync();
       const int rbase = m0 + wq * 32;                     // first row of this warp's 32-row slab
-      if (g.out_mode == TC_OUT_POOL || g.tma_store) {
+      if (g.out_mode == TC_OUT_POOL || g.out_mode == TC_OUT_HEAD || g.tma_store) {
         // ---- fast path: warpgroup `half` owns columns [half*BN/2, +BN/2) in chunks of 16; the TMEM load
         // of chunk i+1 is in flight while chunk i is processed; tile outputs leave through per-warp
         // shared-memory slabs and TMA stores (no LSU traffic), pooled sums through a halving butterfly.
@@ -245,6 +284,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         const bool second = row >= split_row;
         const float *bsel = sB + (second ? BN : 0) + cbase;
         uint32_t raw[2][16];
+        float hacc[4] = {0.f, 0.f, 0.f, 0.f};             // TC_OUT_HEAD: this row's partial last-layer dots
         if (g.debug != 2) tmem_ld_32x16(tbase, raw[0]);
 #pragma unroll
         for (int ci = 0; ci < NCH; ++ci) {
@@ -297,7 +337,17 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
               // pool[(row group)][slot]: slot 0 = frame of the group's first row, slot 1 = the next frame
               float *dst = g.pool + ((long long)(rbase >> 5) * 2) * g.N + n;
               dst[0] = va[0];
-              dst[g.N] = straddle ? vb[0] : 0.f;
+              if (straddle) dst[g.N] = vb[0];             // slot 1 is read only for straddling groups
+            }
+          } else if (BN == 128 && g.out_mode == TC_OUT_HEAD) {
+            const float *wsel = sW + (second ? 4 * 128 : 0) + cbase + c0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float4 w = *reinterpret_cast<const float4 *>(wsel + j * 128 + 4 * q);
+                hacc[j] = fmaf(a[4 * q + 3], w.w, fmaf(a[4 * q + 2], w.z, fmaf(a[4 * q + 1], w.y, fmaf(a[4 * q], w.x, hacc[j]))));
+              }
             }
           } else if (g.out_mode == TC_OUT_F32) {
             uint8_t *slab = slabs + (slab_i++ % TC_SLABS) * TC_SLAB_BYTES;
@@ -338,6 +388,19 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
               }
               bulk_commit();
             }
+          }
+        }
+        if (BN == 128 && g.out_mode == TC_OUT_HEAD) {
+          const int rt = wq * 32 + lane;                  // row inside the tile
+          if (half == 1) *reinterpret_cast<float4 *>(sX + rt * 4) = make_float4(hacc[0], hacc[1], hacc[2], hacc[3]);
+          named_bar_sync(3, 32 * TC_EPI_WARPS);
+          if (half == 0 && row < g.M && g.debug != 1) {
+            const float4 o = *reinterpret_cast<const float4 *>(sX + rt * 4);
+            const float4 bb = *reinterpret_cast<const float4 *>(sW + 2 * 4 * 128 + (second ? 4 : 0));
+            const float y0 = hacc[0] + o.x + bb.x, y1 = hacc[1] + o.y + bb.y, y2 = hacc[2] + o.z + bb.z, y3 = hacc[3] + o.w + bb.w;
+            if (z == 0) *reinterpret_cast<float4 *>(g.pred_r + (size_t)row * 4) = make_float4(y0, y1, y2, y3);
+            else if (z == 1) { float *d = g.pred_t + (size_t)row * 3; d[0] = y0; d[1] = y1; d[2] = y2; }
+            else g.pred_c[row] = 1.0f / (1.0f + expf(-y0));
           }
         }
       } else {
@@ -478,35 +541,42 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
 }
 
 // ---------------------------------------------------------------------------------------------
-// ap[f][c] = (1/N) * sum of the 32-row-group partials of frame f.  Block = 32 columns x 8 group lanes
-// (each lane takes every 8th group, then a fixed-order combine): short dependent-load chains.
+// ap[f][c] = (1/N) * sum of the 32-row-group partials of frame f.  Block = 64 float4 columns x 4 group
+// lanes (each lane takes every 4th group, 16-byte loads, then a fixed-order combine).  Slot 1 of a group
+// is only ever read for the group that straddles the start of frame f (the GEMM epilogue writes it only then).
 __global__ void __launch_bounds__(256)
 pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, int ncols, float *__restrict__ ap) {
-  __shared__ float red[8][33];
+  __shared__ float4 red[4][64];
   const int f = blockIdx.y;
-  const int cl = threadIdx.x & 31, gl = threadIdx.x >> 5;
-  const int c = blockIdx.x * 32 + cl;
+  const int cl = threadIdx.x & 63, gl = threadIdx.x >> 6;
+  const int c = (blockIdx.x * 64 + cl) * 4;
   const long long r_beg = (long long)f * rows_per_frame;
   long long r_end = r_beg + rows_per_frame;
   if (r_end > M) r_end = M;
-  float s = 0.f;
-  if (c < ncols)
-    for (long long g = (r_beg >> 5) + gl; g <= (r_end - 1) >> 5; g += 8) {
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (c < ncols) {
+    const long long g0 = r_beg >> 5, g1 = (r_end - 1) >> 5;
+#pragma unroll 4
+    for (long long g = g0 + gl; g <= g1; g += 4) {
       const int fa = (int)((g << 5) / rows_per_frame);        // frame of the group's first row
-      s += pool[(g * 2 + (fa == f ? 0 : 1)) * ncols + c];
+      const float4 v = __ldg(reinterpret_cast<const float4 *>(pool + (g * 2 + (fa == f ? 0 : 1)) * ncols + c));
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
     }
+  }
   red[gl][cl] = s;
   __syncthreads();
   if (gl == 0 && c < ncols) {
-    float t = 0.f;
+    float4 t = red[0][cl];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) t += red[i][cl];
-    ap[(long long)f * ncols + c] = t / (float)rows_per_frame;
+    for (int i = 1; i < 4; ++i) { t.x += red[i][cl].x; t.y += red[i][cl].y; t.z += red[i][cl].z; t.w += red[i][cl].w; }
+    const float inv = 1.0f / (float)rows_per_frame;
+    *reinterpret_cast<float4 *>(ap + (long long)f * ncols + c) = make_float4(t.x * inv, t.y * inv, t.z * inv, t.w * inv);
   }
 }
 
 int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap, cudaStream_t st) {
-  dim3 grid((ncols + 31) / 32, frames);
+  if (ncols % 4) { set_error("pool_finish: ncols must be a multiple of 4"); return PLR2_E_SHAPE; }
+  dim3 grid((ncols / 4 + 63) / 64, frames);
   pool_finish_kernel<<<grid, 256, 0, st>>>(pool, rows_per_frame, M, ncols, ap);
   return check_launch("pool_finish");
 }
@@ -666,6 +736,7 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   k.bias = g.bias; k.frame_bias = g.frame_bias; k.rows_per_frame = g.rows_per_frame > 0 ? g.rows_per_frame : 1; k.ldfb = g.ldfb;
   k.relu = g.relu; k.out_mode = g.out_mode;
   k.Cf = g.Cf; k.ldc = g.ldc; k.Cb = g.Cb; k.ldcb = g.ldcb; k.c_plane = g.c_plane; k.pool = g.pool;
+  k.w4 = g.w4; k.b4 = g.b4; k.obj = g.obj; k.num_obj = g.num_obj; k.pred_r = g.pred_r; k.pred_t = g.pred_t; k.pred_c = g.pred_c;
   { static int dbg = -1; if (dbg < 0) { const char *e = getenv("PLR2_TC_DEBUG"); dbg = e ? atoi(e) : 0; } k.debug = dbg; }
   auto kfn = gemm_bf16x2_kernel<BN, NPROD, CG>;
   static int units_max = 0;            // per instantiation: CTAs (CG == 1) or CTA pairs (CG == 2) resident at once
@@ -713,7 +784,12 @@ int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
   if (g.out_mode == TC_OUT_F32 && !g.Cf) { set_error("gemm_bf16x2: null Cf"); return PLR2_E_NULLPTR; }
   if (g.out_mode == TC_OUT_BF16X2 && (!g.Cb || (g.ldcb % 8) || (g.c_col_z % 8))) { set_error("gemm_bf16x2: bf16 output needs 16-byte aligned rows"); return PLR2_E_ALIGN; }
   if (g.out_mode == TC_OUT_POOL && (!g.pool || g.batch != 1)) { set_error("gemm_bf16x2: pooled output needs batch == 1"); return PLR2_E_UNSUPPORTED; }
-  if ((g.out_mode == TC_OUT_POOL || g.frame_bias) && g.rows_per_frame < TC_BM) { set_error("gemm_bf16x2: per-frame epilogues need rows_per_frame >= %d", TC_BM); return PLR2_E_UNSUPPORTED; }
+  if (g.out_mode == TC_OUT_HEAD && (g.N != 128 || g.batch != 3 || !g.w4 || !g.b4 || !g.obj || !g.pred_r || !g.pred_t || !g.pred_c ||
+                                    g.num_obj <= 0 || (reinterpret_cast<uintptr_t>(g.pred_r) & 15))) {
+    set_error("gemm_bf16x2: fused head output needs N == 128, batch == 3 (r|t|c) and all head pointers");
+    return PLR2_E_UNSUPPORTED;
+  }
+  if ((g.out_mode == TC_OUT_POOL || g.out_mode == TC_OUT_HEAD || g.frame_bias) && g.rows_per_frame < TC_BM) { set_error("gemm_bf16x2: per-frame epilogues need rows_per_frame >= %d", TC_BM); return PLR2_E_UNSUPPORTED; }
   const bool hi_only = g.a_hi_only != 0;
   if (tc_cta_group() == 2) {
     if (g.N >= 256) return hi_only ? launch_tc<256, 2, 2>(g, st) : launch_tc<256, 3, 2>(g, st);

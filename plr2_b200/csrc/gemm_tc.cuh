@@ -5,7 +5,7 @@
 
 namespace plr2 {
 
-enum { TC_OUT_F32 = 0, TC_OUT_BF16X2 = 1, TC_OUT_POOL = 2 };
+enum { TC_OUT_F32 = 0, TC_OUT_BF16X2 = 1, TC_OUT_POOL = 2, TC_OUT_HEAD = 3 };
 
 // Y = epi(X W^T).  X: bf16 planes [2][rows][lda] (plane stride a_plane elements), W likewise.
 // batch > 1: problem z reads X columns [z*a_col_z, +K), W rows [z*b_row_z, +N), writes C columns
@@ -21,6 +21,11 @@ struct TcGemm {
   float *Cf = nullptr; long long ldc = 0;
   __nv_bfloat16 *Cb = nullptr; long long ldcb = 0, c_plane = 0;
   float *pool = nullptr;      // TC_OUT_POOL: [ceil(M/32)][2][N] partial column sums
+  // TC_OUT_HEAD (N == 128, batch z = head r|t|c): the 128-wide ReLU output of head z is not stored; its last
+  // layer is applied in the epilogue for the class of the row's frame only (conv4_* + select + sigmoid,
+  // lib/network.py:117-130): w4 [(4+3+1)*num_obj][128] rows r|t|c, b4 likewise.
+  const float *w4 = nullptr, *b4 = nullptr; const int64_t *obj = nullptr; int num_obj = 0;
+  float *pred_r = nullptr, *pred_t = nullptr, *pred_c = nullptr;
 };
 
 int gemm_bf16x2(const TcGemm &g, cudaStream_t st);

@@ -136,10 +136,12 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   g.A = h2; g.lda = 768; g.a_plane = W.h2_plane; g.W = wb + L.h3w; g.ldw = 256; g.w_plane = wplane;
   g.M = R; g.N = 128; g.K = 256; g.batch = 3; g.a_col_z = 256; g.b_row_z = 128; g.c_col_z = 128; g.bias_z = 128;
   g.bias = pk + L.h3b; g.relu = 1;
-  g.out_mode = TC_OUT_F32; g.Cf = W.h3; g.ldc = 384;
-  RC(gemm_bf16x2(g, st));                                                            // conv3_* (FP32 out)
-  // conv4_{r,t,c} for the frame's class only + sigmoid (FP32 SIMT)
-  RC(head_out(W.h3, 384, pk + L.h4w, pk + L.h4b, obj, L.O, F, N, pred_r, pred_t, pred_c, st));
+  // conv3_* with conv4_{r,t,c} for the frame's class + sigmoid fused into the epilogue (FP32): the
+  // 128-wide h3 activations are never written
+  g.out_mode = TC_OUT_HEAD; g.rows_per_frame = N;
+  g.w4 = pk + L.h4w; g.b4 = pk + L.h4b; g.obj = obj; g.num_obj = L.O;
+  g.pred_r = pred_r; g.pred_t = pred_t; g.pred_c = pred_c;
+  RC(gemm_bf16x2(g, st));
   return 0;
 }
 
