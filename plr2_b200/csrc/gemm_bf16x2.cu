@@ -94,7 +94,9 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
   uint64_t *tempty_bar = tfull_bar + 2;            // [2]       epilogue -> MMA (CG == 2: the leader's is used)
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty_bar + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // shuffle broadcast: tells the compiler the warp index is uniform, so TMA/MMA operands derived from it
+  // go straight to uniform registers instead of through R2UR waterfall loops
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int rank = CG == 2 ? (int)cluster_ctarank() : 0;      // 0 = leader (issues the MMAs)
   const int unit = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;       // tile-processing unit (CTA or pair)
   const int n_units = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;

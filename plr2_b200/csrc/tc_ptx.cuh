@@ -144,7 +144,9 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
   return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  // relaxed: the only ordering the consumer needs (TMEM reads done) comes from tcgen05.wait::ld +
+  // tcgen05.fence::before_thread_sync; a release at cluster scope costs MEMBAR.ALL.GPU + ERRBAR per arrival
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load whose completion is signalled on an mbarrier that may live in the PEER CTA of the pair
 __device__ __forceinline__ void tma_load_2d_cg2(void *smem_dst, const void *tmap, uint32_t bar_cluster_addr,
