@@ -245,6 +245,8 @@ def run_ours(args, world, rank, local):
     pn = synth.make_params("posenet", SHAPE.num_obj, 1)
     rf = synth.make_params("refiner", SHAPE.num_obj, 2)
     pipe.load_params(pn, rf)
+    from plr2_b200.parallel import bind_to_gpu_numa
+    numa_cpus = bind_to_gpu_numa(local) if world > 1 else None     # pinned buffers on the GPU's own node
     work = make_workload(frames, 1000 + 7919 * rank)
     host = {k: v.pin_memory() for k, v in work.items()}
     devw = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
@@ -348,7 +350,8 @@ def run_ours(args, world, rank, local):
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16x2-split operands, f32 accumulate (f32 SIMT for small layers/losses)",
         "data": "synthetic",
         "config": {"workload": "C4: YCB-shaped frames, PoseNet(out_img given)+Loss(refine)+2x(PoseRefineNet+Loss_refine ADD-S)",
-                   "frames_per_gpu_per_step": frames, "chunk_frames": args.chunk, "host_chunk_frames": args.host_chunk, "num_points": SHAPE.num_points,
+                   "frames_per_gpu_per_step": frames, "chunk_frames": args.chunk, "host_chunk_frames": args.host_chunk,
+                   "numa_bound_cpus": len(numa_cpus) if numa_cpus else None, "num_points": SHAPE.num_points,
                    "num_mesh": SHAPE.num_mesh, "num_obj": SHAPE.num_obj, "crop": [SHAPE.height, SHAPE.width],
                    "knn_mode": args.knn, "l2": "inputs (%.0f MB per step) larger than L2" % (h2d / 1e6),
                    "results_finite": finite},

@@ -94,3 +94,35 @@ def data_parallel_step(frames, step_fn, bucket, optimizer, average=True, group=N
     bucket.all_reduce(average=average, group=group)
     optimizer.step()
     return total / max(count, 1), world
+
+
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_to_gpu_numa(device_index):
+    """Restrict this process to the CPUs local to GPU `device_index` (sysfs `local_cpulist` of its PCI
+    function), so that pinned staging buffers allocated afterwards land on the NUMA node the GPU's PCIe
+    root hangs off.  With one rank per GPU, eight ranks each streaming ~50 GB/s from host memory otherwise
+    share one node's DRAM and the inter-socket link.  Returns the CPU set applied, or None when the
+    topology is not visible (containers without sysfs PCI, non-Linux): binding is an optimisation only."""
+    import os
+    try:
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/local_cpulist" % bdf) as f:
+            cpus = _parse_cpulist(f.read())
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if not cpus or cpus == allowed:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except (OSError, AttributeError, ValueError, RuntimeError):
+        return None

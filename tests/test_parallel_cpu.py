@@ -97,3 +97,11 @@ def test_bucket_aliases_param_grads_and_is_noop_without_group():
     assert b.all_reduce() is None
     b.zero()
     assert all(float(p.grad.abs().sum()) == 0.0 for p in net.parameters())
+
+
+def test_cpulist_parser_and_numa_binding_is_optional():
+    from plr2_b200.parallel import _parse_cpulist, bind_to_gpu_numa
+    assert _parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert _parse_cpulist("") == set()
+    # no CUDA device / no sysfs topology here: must be a silent no-op, never an exception
+    assert bind_to_gpu_numa(0) is None
