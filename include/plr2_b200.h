@@ -121,6 +121,33 @@ int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t,
  * pose_delta is the pose_out of the NEXT stage (estimated in the frame re-centred by pose_acc). */
 int plr2_pose_compose(float *pose_acc, const float *pose_delta, int frames, void *stream);
 
+/* ---- (6) evaluation metrics after the path ---------------------------------
+ * ADD / ADD-S between two poses applied to the same model points, per frame
+ * (src/estimation/errors.py:53-67 ADD, :69-84 ADDS; both poses are R|t [F][12], row-major R then t, the
+ * layout plr2_pose_compose / pose_out produce; a point maps to R p + t as points.apply_transform does,
+ * src/estimation/state.py:235-244):
+ *   add[f]  = mean_j || (Ra p_j + ta) - (Rb p_j + tb) ||
+ *   adds[f] = mean_j min_k || (Rb p_j + tb) - (Ra p_k + ta) ||     (model_1 = pose_a is the fitted set,
+ *             model_2 = pose_b the queries, errors.py:80-83)
+ * model_points [F][M][3] with model_stride floats between frames (0: one model shared by all frames).
+ * add or adds may be NULL (not computed). FP32 arithmetic (the reference computes in float64).
+ * workspace: plr2_pose_metric_workspace_bytes(frames) bytes, contents irrelevant. n_mesh <= 8192. */
+size_t plr2_pose_metric_workspace_bytes(int frames);
+int plr2_pose_metric(const float *model_points, long long model_stride, const float *pose_a,
+                     const float *pose_b, int frames, int n_mesh, float *add, float *adds,
+                     void *workspace, size_t workspace_bytes, void *stream);
+
+/* Area under the accuracy-threshold curve of the YCB-Video toolbox
+ * (replace_ycb_toolbox/plot_accuracy_keyframe.m:38-52 and VOCap :150-170): distances above max_distance
+ * (0.1 there) count as misses, accuracy(d) = rank/n over the sorted distances, AUC = integral of the
+ * accuracy envelope over [0, max_distance] divided by max_distance. Computed without a sort (rank and
+ * predecessor of every distinct value by brute force over all pairs), accumulated in float64.
+ *   out[0] = AUC in [0,1] (the script prints it x100), out[1] = fraction of distances < below (0.02 there).
+ * n == 0 or no distance <= max_distance gives out[0] = 0. workspace: plr2_auc_workspace_bytes(n). */
+size_t plr2_auc_workspace_bytes(int n);
+int plr2_auc_f32(const float *dist, int n, double max_distance, double below, double *out,
+                 void *workspace, size_t workspace_bytes, void *stream);
+
 /* ---- (2) dense contractions --------------------------------------------------------------
  * General FP32 GEMM with fused epilogue, C(m,n) (+)= f(sum_k A(m,k) B(k,n)):
  *   A(m,k) = A[m*sam + k*sak],  B(k,n) = B[k*sbk + n*sbn],  C(m,n) = C[m*ldc + n]

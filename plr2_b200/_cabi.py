@@ -25,6 +25,10 @@ SIGNATURES = {
     "plr2_pose_loss_bwd": (_i, [_vp] * 7 + [_i, _i, _f] + [_vp] * 4),
     "plr2_pose_select": (_i, [_vp] * 6 + [_i] * 3 + [_vp] * 6),
     "plr2_pose_compose": (_i, [_vp, _vp, _i, _vp]),
+    "plr2_pose_metric_workspace_bytes": (_sz, [_i]),
+    "plr2_pose_metric": (_i, [_vp, C.c_longlong, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    "plr2_auc_workspace_bytes": (_sz, [_i]),
+    "plr2_auc_f32": (_i, [_vp, _i, C.c_double, C.c_double, _vp, _vp, _sz, _vp]),
     "plr2_refine_loss_workspace_bytes": (_sz, [_i, _i]),
     "plr2_refine_loss_fwd": (_i, [_vp] * 7 + [_i] * 5 + [_vp] * 6 + [_vp, _sz, _vp]),
 }
