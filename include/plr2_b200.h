@@ -148,6 +148,42 @@ size_t plr2_auc_workspace_bytes(int n);
 int plr2_auc_f32(const float *dist, int n, double max_distance, double below, double *out,
                  void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---- (7) input step before the path ---------------------------------------
+ * What datasets/ycb/dataset.py:177-197,215-219 (and src/loaders_v2/dataset_ycb.py:91-119) do per frame with
+ * numpy on the host, for F frames on the device. Images are full frames [F][img_h][img_w]; bbox [F][4] int32 =
+ * (rmin, rmax, cmin, cmax) from get_bbox (half-open, the crop is [rmin,rmax) x [cmin,cmax)).
+ *
+ * plr2_choose_from_mask: `choose = mask[rmin:rmax, cmin:cmax].flatten().nonzero()[0]` (ascending crop-flat
+ *   indices), then exactly n_points of them:
+ *     count <= n_points : np.pad(choose, (0, n_points - count), 'wrap')         (dataset.py:184)
+ *     count >  n_points : an order-preserving subset of n_points entries          (dataset.py:179-182)
+ *       keep != NULL: entry k of the nonzero list is kept iff keep[f*keep_stride + k] != 0 - the c_mask of the
+ *                     reference, so a caller that draws it with numpy's RNG reproduces the reference exactly;
+ *       keep == NULL: a uniformly random subset drawn on the device from (seed, frame, k) hash keys
+ *                     (the n_points smallest keys; same distribution, not numpy's Mersenne-Twister stream).
+ *   mask: uint8, non-zero = object pixel with valid depth (mask_depth * mask_label, dataset.py:126-128).
+ *   count_out[f] = number of non-zero crop pixels (0: choose[f] is zero-filled; the reference raises there).
+ *   workspace: plr2_choose_workspace_bytes(frames, max_crop_pixels) bytes.
+ *
+ * plr2_backproject: cloud[f][n] = ((col - cx) * z / fx, (row - cy) * z / fy, z), z = depth / cam_scale, with
+ *   row = rmin + c / crop_w, col = cmin + c % crop_w for c = choose[f][n] (xmap holds the row index, ymap the
+ *   column: dataset.py:83-84,186-194), every operation rounded to float32 exactly as numpy does on float32
+ *   arrays; add_t [F][3] (float64, NULL = none) is added in float64 and rounded once (dataset.py:195-196,226).
+ *   depth is uint16 (depth_is_u16 != 0, the PNG's type) or float32. cam [F][5] float32 = (cx, cy, fx, fy, scale).
+ *
+ * plr2_transform_target: target[f][j] = model_points[f][j] . R[f]^T + t[f] (+ add_t[f]) in float64, rounded
+ *   to float32 (dataset.py:215-219,229); R [F][9] row-major, t [F][3], add_t [F][3] or NULL, all float64. */
+size_t plr2_choose_workspace_bytes(int frames, int max_crop_pixels);
+int plr2_choose_from_mask(const uint8_t *mask, int img_h, int img_w, const int32_t *bbox, int frames,
+                          int n_points, const uint8_t *keep, long long keep_stride, unsigned long long seed,
+                          int64_t *choose, int32_t *count_out, void *workspace, size_t workspace_bytes,
+                          void *stream);
+int plr2_backproject(const void *depth, int depth_is_u16, int img_h, int img_w, const int32_t *bbox,
+                     const int64_t *choose, const float *cam, const double *add_t, int frames, int n_points,
+                     float *cloud, void *stream);
+int plr2_transform_target(const float *model_points, const double *R, const double *t, const double *add_t,
+                          int frames, int n_mesh, float *target, void *stream);
+
 /* ---- (2) dense contractions --------------------------------------------------------------
  * General FP32 GEMM with fused epilogue, C(m,n) (+)= f(sum_k A(m,k) B(k,n)):
  *   A(m,k) = A[m*sam + k*sak],  B(k,n) = B[k*sbk + n*sbn],  C(m,n) = C[m*ldc + n]

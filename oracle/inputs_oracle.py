@@ -1,0 +1,54 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY (never imported by plr2_b200/).
+
+numpy restatement of the reference's per-frame input step, statement for statement:
+
+    compute_choose    <- datasets/ycb/dataset.py:177-184  (= src/loaders_v2/dataset_ycb.py:91-106)
+    pointcloud        <- datasets/ycb/dataset.py:186-196  (= src/loaders_v2/dataset_ycb.py:108-119)
+    transform_target  <- datasets/ycb/dataset.py:215-219,229
+
+The reference's dataset classes need the YCB-Video files on disk and cannot be instantiated here; these
+functions are the same numpy calls on explicit arrays (numpy itself is the third-party arithmetic, so the
+float32/float64 promotion rules are the reference's own).  xmap holds the row index and ymap the column index
+(dataset.py:83-84).
+"""
+import numpy as np
+
+
+def compute_choose(mask, bbox, num_pt, c_mask=None):
+    """mask (H,W) bool/uint8, bbox (rmin,rmax,cmin,cmax); c_mask: the shuffled 0/1 vector of the reference
+    (drawn by the caller so that the test controls the RNG).  Returns (choose (num_pt,), count)."""
+    rmin, rmax, cmin, cmax = [int(v) for v in bbox]
+    choose = mask[rmin:rmax, cmin:cmax].flatten().nonzero()[0]
+    count = len(choose)
+    if count > num_pt:
+        assert c_mask is not None and len(c_mask) >= count and int(np.sum(c_mask[:count] != 0)) == num_pt
+        choose = choose[np.asarray(c_mask[:count]).nonzero()]
+    else:
+        choose = np.pad(choose, (0, num_pt - count), 'wrap')
+    return choose, count
+
+
+def pointcloud(depth, bbox, choose, cam_cx, cam_cy, cam_fx, cam_fy, cam_scale, add_t=None):
+    rmin, rmax, cmin, cmax = [int(v) for v in bbox]
+    h, w = depth.shape
+    xmap = np.array([[j for i in range(w)] for j in range(h)])
+    ymap = np.array([[i for i in range(w)] for j in range(h)])
+    depth_masked = depth[rmin:rmax, cmin:cmax].flatten()[choose][:, np.newaxis].astype(np.float32)
+    xmap_masked = xmap[rmin:rmax, cmin:cmax].flatten()[choose][:, np.newaxis].astype(np.float32)
+    ymap_masked = ymap[rmin:rmax, cmin:cmax].flatten()[choose][:, np.newaxis].astype(np.float32)
+    pt2 = depth_masked / cam_scale
+    pt0 = (ymap_masked - cam_cx) * pt2 / cam_fx
+    pt1 = (xmap_masked - cam_cy) * pt2 / cam_fy
+    cloud = np.concatenate((pt0, pt1, pt2), axis=1)
+    if add_t is not None:
+        cloud = np.add(cloud, add_t)
+    return cloud.astype(np.float32)
+
+
+def transform_target(model_points, target_r, target_t, add_t=None):
+    target = np.dot(model_points, target_r.T)
+    if add_t is not None:
+        target = np.add(target, target_t + add_t)
+    else:
+        target = np.add(target, target_t)
+    return target.astype(np.float32)
