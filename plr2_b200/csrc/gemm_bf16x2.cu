@@ -547,7 +547,8 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
 // lanes (each lane takes every 4th group, 16-byte loads, then a fixed-order combine).  Slot 1 of a group
 // is only ever read for the group that straddles the start of frame f (the GEMM epilogue writes it only then).
 __global__ void __launch_bounds__(256)
-pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, int ncols, float *__restrict__ ap) {
+pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, int ncols, float *__restrict__ ap,
+                   __nv_bfloat16 *__restrict__ apb, long long apb_plane) {
   __shared__ float4 red[4][64];
   const int f = blockIdx.y;
   const int cl = threadIdx.x & 63, gl = threadIdx.x >> 6;
@@ -572,14 +573,26 @@ pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, in
 #pragma unroll
     for (int i = 1; i < 4; ++i) { t.x += red[i][cl].x; t.y += red[i][cl].y; t.z += red[i][cl].z; t.w += red[i][cl].w; }
     const float inv = 1.0f / (float)rows_per_frame;
-    *reinterpret_cast<float4 *>(ap + (long long)f * ncols + c) = make_float4(t.x * inv, t.y * inv, t.z * inv, t.w * inv);
+    const float4 o = make_float4(t.x * inv, t.y * inv, t.z * inv, t.w * inv);
+    *reinterpret_cast<float4 *>(ap + (long long)f * ncols + c) = o;
+    if (apb) {                                                  // operand planes of the M = frames GEMMs
+      const __nv_bfloat162 h01 = __floats2bfloat162_rn(o.x, o.y), h23 = __floats2bfloat162_rn(o.z, o.w);
+      const __nv_bfloat162 l01 = __floats2bfloat162_rn(o.x - __low2float(h01), o.y - __high2float(h01));
+      const __nv_bfloat162 l23 = __floats2bfloat162_rn(o.z - __low2float(h23), o.w - __high2float(h23));
+      uint2 ph, pl;
+      ph.x = *reinterpret_cast<const uint32_t *>(&h01); ph.y = *reinterpret_cast<const uint32_t *>(&h23);
+      pl.x = *reinterpret_cast<const uint32_t *>(&l01); pl.y = *reinterpret_cast<const uint32_t *>(&l23);
+      *reinterpret_cast<uint2 *>(apb + (long long)f * ncols + c) = ph;
+      *reinterpret_cast<uint2 *>(apb + apb_plane + (long long)f * ncols + c) = pl;
+    }
   }
 }
 
-int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap, cudaStream_t st) {
+int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap,
+                __nv_bfloat16 *apb, long long apb_plane, cudaStream_t st) {
   if (ncols % 4) { set_error("pool_finish: ncols must be a multiple of 4"); return PLR2_E_SHAPE; }
   dim3 grid((ncols / 4 + 63) / 64, frames);
-  pool_finish_kernel<<<grid, 256, 0, st>>>(pool, rows_per_frame, M, ncols, ap);
+  pool_finish_kernel<<<grid, 256, 0, st>>>(pool, rows_per_frame, M, ncols, ap, apb, apb_plane);
   return check_launch("pool_finish");
 }
 
@@ -794,7 +807,14 @@ int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
   if ((g.out_mode == TC_OUT_POOL || g.out_mode == TC_OUT_HEAD || g.frame_bias) && g.rows_per_frame < TC_BM) { set_error("gemm_bf16x2: per-frame epilogues need rows_per_frame >= %d", TC_BM); return PLR2_E_UNSUPPORTED; }
   const bool hi_only = g.a_hi_only != 0;
   if (tc_cta_group() == 2) {
-    if (g.N >= 256) return hi_only ? launch_tc<256, 2, 2>(g, st) : launch_tc<256, 3, 2>(g, st);
+    // few 256-wide tiles (M = frames problems): halve the tile so twice as many CTA pairs share the work
+    static int pairs = 0;
+    if (!pairs) { const int n = plr2_device_sm_count(); pairs = (n > 0 ? n : 148) / 2; }
+    const long long tiles256 = (long long)((g.M + 2 * TC_BM - 1) / (2 * TC_BM)) * ((g.N + 255) / 256) * g.batch;
+    static int allow_narrow = -1;
+    if (allow_narrow < 0) { const char *e = getenv("PLR2_TC_NARROW"); allow_narrow = (e && e[0] == '0') ? 0 : 1; }
+    const bool narrow = g.N < 256 || (allow_narrow && 2 * tiles256 <= pairs && g.out_mode != TC_OUT_POOL);
+    if (!narrow) return hi_only ? launch_tc<256, 2, 2>(g, st) : launch_tc<256, 3, 2>(g, st);
     return hi_only ? launch_tc<128, 2, 2>(g, st) : launch_tc<128, 3, 2>(g, st);
   }
   if (g.N >= 256) return hi_only ? launch_tc<256, 2, 1>(g, st) : launch_tc<256, 3, 1>(g, st);

@@ -29,8 +29,10 @@ struct TcGemm {
 };
 
 int gemm_bf16x2(const TcGemm &g, cudaStream_t st);
-// ap[f][c] = (1/rows_per_frame) * sum of the pooling partials belonging to frame f
-int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap, cudaStream_t st);
+// ap[f][c] = (1/rows_per_frame) * sum of the pooling partials belonging to frame f; apb (optional): the same
+// values as split-bf16 planes [2][frames][ncols], plane stride apb_plane elements
+int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap,
+                __nv_bfloat16 *apb, long long apb_plane, cudaStream_t st);
 // dst planes <- split(src): hi = bf16(v), lo = bf16(v - hi)
 int split_bf16x2(const float *src, long long ld, long long rows, int cols, __nv_bfloat16 *dst, long long ldd,
                  long long plane, cudaStream_t st);

@@ -7,9 +7,9 @@
 
 namespace plr2 {
 
-constexpr int PM_THREADS = 256;
-constexpr int PM_SLICES = 8;      // CTAs per frame, each owning a contiguous range of query points
-constexpr int PM_QPT = 2;         // queries per thread and pass
+constexpr int PM_THREADS = 128;
+constexpr int PM_SLICES = 8;      // at most this many CTAs per frame, each owning a contiguous range of query points
+constexpr int PM_QPT = 4;         // queries per thread and pass (as kernel (4))
 
 // fixed-order block sum: warp shuffles, then warp 0 adds the per-warp values in warp order
 template <typename T>
@@ -52,7 +52,7 @@ pose_metric_kernel(const float *__restrict__ model, long long model_stride, cons
     }
     __syncthreads();
   }
-  const int per = (M + PM_SLICES - 1) / PM_SLICES;
+  const int per = (M + gridDim.x - 1) / gridDim.x;
   const int j0 = s * per, j1 = min(M, j0 + per);
   float acc_add = 0.f, acc_adds = 0.f;
   for (int base = j0; base < j1; base += PM_THREADS * PM_QPT) {
@@ -91,12 +91,12 @@ pose_metric_kernel(const float *__restrict__ model, long long model_stride, cons
   }
 }
 
-__global__ void pose_metric_finish_kernel(const float *__restrict__ partial, int frames, int M,
+__global__ void pose_metric_finish_kernel(const float *__restrict__ partial, int frames, int M, int slices,
                                           float *__restrict__ add, float *__restrict__ adds) {
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= frames) return;
   float a = 0.f, b = 0.f;
-  for (int s = 0; s < PM_SLICES; ++s) {          // slice order: deterministic
+  for (int s = 0; s < slices; ++s) {             // slice order: deterministic
     a += partial[((size_t)f * PM_SLICES + s) * 2];
     b += partial[((size_t)f * PM_SLICES + s) * 2 + 1];
   }
@@ -201,7 +201,10 @@ extern "C" int plr2_pose_metric(const float *model_points, long long model_strid
   }
   cudaStream_t st = (cudaStream_t)stream;
   float *partial = (float *)workspace;
-  dim3 grid(PM_SLICES, frames);
+  // slices sized to one pass of a CTA (PM_THREADS * PM_QPT queries), so no thread idles through the scan
+  int slices = (n_mesh + PM_THREADS * PM_QPT - 1) / (PM_THREADS * PM_QPT);
+  slices = slices > PM_SLICES ? PM_SLICES : slices;
+  dim3 grid(slices, frames);
   if (adds) {
     const size_t smem = (size_t)knn_pad(n_mesh) * 3 * sizeof(float);
     static bool attr = false;
@@ -214,7 +217,7 @@ extern "C" int plr2_pose_metric(const float *model_points, long long model_strid
   } else {
     pose_metric_kernel<false><<<grid, PM_THREADS, 0, st>>>(model_points, model_stride, pose_a, pose_b, n_mesh, partial);
   }
-  pose_metric_finish_kernel<<<(frames + 127) / 128, 128, 0, st>>>(partial, frames, n_mesh, add, adds);
+  pose_metric_finish_kernel<<<(frames + 127) / 128, 128, 0, st>>>(partial, frames, n_mesh, slices, add, adds);
   return check_launch("plr2_pose_metric", 2);
 }
 

@@ -93,6 +93,7 @@ struct TcWorkspace {
   void *pf, *x5, *h1, *h2;                 // bf16 planes
   long long pf_plane, x5_plane, h1_plane, h2_plane;
   float *pool, *ap, *hb, *h3, *out;        // fp32; refiner: hb = l1 out, h3 = l2 out
+  void *apb; long long apb_plane;          // pooled features as split-bf16 planes [2][F][1024] (operand of the M = frames GEMMs)
   size_t bytes;
 };
 
@@ -108,6 +109,7 @@ inline TcWorkspace carve_tc_workspace(const NetLayout &L, void *base, int frames
   W.x5 = take(2 * R * 512 * 2); W.x5_plane = (long long)R * 512;
   W.pool = (float *)take(((R + 31) / 32) * 2 * 1024 * sizeof(float));
   W.ap = (float *)take(F * 1024 * sizeof(float));
+  W.apb = take(2 * F * 1024 * 2); W.apb_plane = (long long)F * 1024;
   if (pn) {
     W.hb = (float *)take(F * h1all * sizeof(float));
     W.h1 = take(2 * R * h1all * 2); W.h1_plane = (long long)R * h1all;

@@ -358,9 +358,9 @@ static int build_table(const NetLayout &L, const plr2_param_table *P, float *pac
   for (int h = 0; h < L.heads; ++h, ++li) {      // conv1_{r,t,c}
     if (pn) {
       blk(P->w[li], 1408, L.h1pf + (size_t)h * 640 * 384, 384, 640, 384, round);
-      blk(P->w[li] + 384, 1408, L.h1ap + (size_t)h * 640 * 1024, 1024, 640, 1024, 0);
+      blk(P->w[li] + 384, 1408, L.h1ap + (size_t)h * 640 * 1024, 1024, 640, 1024, round);
     } else {
-      blk(P->w[li], 1024, L.h1ap + (size_t)h * 512 * 1024, 1024, 512, 1024, 0);
+      blk(P->w[li], 1024, L.h1ap + (size_t)h * 512 * 1024, 1024, 512, 1024, round);
     }
     blk(P->b[li], L.h1n, L.h1b + (size_t)h * L.h1n, L.h1n, 1, L.h1n, 0);
   }

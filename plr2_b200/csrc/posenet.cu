@@ -107,7 +107,7 @@ static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspac
   g.out_mode = TC_OUT_POOL; g.pool = W.pool; g.rows_per_frame = N;
   g.a_hi_only = 1;
   RC(gemm_bf16x2(g, st));                                                            // conv6 + AvgPool partials
-  RC(pool_finish(W.pool, F, N, R, 1024, W.ap, st));
+  RC(pool_finish(W.pool, F, N, R, 1024, W.ap, (__nv_bfloat16 *)W.apb, W.apb_plane, st));
   return 0;
 }
 
@@ -119,9 +119,12 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   const long long wplane = (long long)L.total;
   __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *h1 = (__nv_bfloat16 *)W.h1, *h2 = (__nv_bfloat16 *)W.h2;
   RC(feat_forward_tc(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, st));
-  // per-frame bias of conv1_{r,t,c}: hb[F,1920] = ap W1[:,384:]^T + b1 (FP32)
-  RC(frame_linear(W.ap, 1024, pk + L.h1ap, 1024, pk + L.h1b, W.hb, 1920, F, 1920, 1024, 0, 1, 0, 0, 0, 0, st));
+  // per-frame bias of conv1_{r,t,c}: hb[F,1920] = ap W1[:,384:]^T + b1 (an M = frames GEMM, FP32 out)
   TcGemm g;
+  g.A = (const __nv_bfloat16 *)W.apb; g.lda = 1024; g.a_plane = W.apb_plane; g.W = wb + L.h1ap; g.ldw = 1024; g.w_plane = wplane;
+  g.M = F; g.N = 1920; g.K = 1024; g.bias = pk + L.h1b; g.out_mode = TC_OUT_F32; g.Cf = W.hb; g.ldc = 1920;
+  RC(gemm_bf16x2(g, st));
+  g = TcGemm();
   g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.h1pf; g.ldw = 384; g.w_plane = wplane;
   g.M = R; g.N = 1920; g.K = 384; g.frame_bias = W.hb; g.rows_per_frame = N; g.ldfb = 1920; g.relu = 1;
   g.out_mode = TC_OUT_BF16X2; g.Cb = h1; g.ldcb = 1920; g.c_plane = W.h1_plane;
@@ -149,8 +152,14 @@ static int refiner_forward_tc(const float *pk, const NetLayout &L, const TcWorks
                               const float *emb, const int64_t *obj, int F, int N, float *pred_r, float *pred_t,
                               cudaStream_t st) {
   RC(feat_forward_tc(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, st));
-  // Linear 1024->512 (x2 heads), 512->128 (x2), 128->7 for the frame's class: M = frames, FP32 SIMT
-  RC(frame_linear(W.ap, 1024, pk + L.h1ap, 1024, pk + L.h1b, W.hb, 1024, F, 1024, 1024, 1, 1, 0, 0, 0, 0, st));
+  // Linear 1024->512 (x2 heads) as one M = frames tensor-core GEMM; 512->128 (x2) and 128->7 for the frame's
+  // class in FP32 SIMT
+  const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);
+  TcGemm g;
+  g.A = (const __nv_bfloat16 *)W.apb; g.lda = 1024; g.a_plane = W.apb_plane; g.W = wb + L.h1ap; g.ldw = 1024;
+  g.w_plane = (long long)L.total;
+  g.M = F; g.N = 1024; g.K = 1024; g.bias = pk + L.h1b; g.relu = 1; g.out_mode = TC_OUT_F32; g.Cf = W.hb; g.ldc = 1024;
+  RC(gemm_bf16x2(g, st));
   RC(frame_linear(W.hb, 1024, pk + L.h2w, 512, pk + L.h2b, W.h3, 256, F, 128, 512, 1, 2, 512, 128 * 512, 128, 128, st));
   RC(head_out(W.h3, 256, pk + L.h4w, pk + L.h4b, obj, L.O, F, 1, pred_r, pred_t, nullptr, st));
   return 0;
