@@ -265,7 +265,13 @@ int plr2_posenet_backward(const float *packed, const int64_t *choose, const floa
                           void *stream);
 
 /* PoseRefineNet.forward (lib/network.py:187-206): x [F][N][3], emb [F][32][N], obj [F]
- *   -> pred_r [F][4], pred_t [F][3] */
+ *   -> pred_r [F][4], pred_t [F][3]
+ * training: 0 inference, 1 training (activations kept for plr2_refiner_backward), or
+ * PLR2_REFINER_NEXT_ITER: inference for refine iteration >= 2 (tools/train.py:141-145 feeds the SAME emb to
+ * every iteration): the caller guarantees that emb, the packed parameters, frames/n_points and the workspace
+ * are those of the immediately preceding plr2_refiner_forward call on this workspace, so the emb branch
+ * (e_conv1, e_conv2) still held there is reused instead of recomputed. Ignored (full forward) on the FP32 path. */
+#define PLR2_REFINER_NEXT_ITER 2
 int plr2_refiner_forward(const float *packed, const float *x, const float *emb, const int64_t *obj,
                          int frames, int n_points, int num_obj, void *workspace, size_t workspace_bytes,
                          float *pred_r, float *pred_t, int training, int precision, void *stream);

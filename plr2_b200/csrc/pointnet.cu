@@ -24,7 +24,7 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
                    const float *__restrict__ out_img, const int64_t *__restrict__ choose,
                    const float *__restrict__ emb_in, const float *__restrict__ x, int N, int hw,
                    float *__restrict__ pf, __nv_bfloat16 *__restrict__ pfb, long long pf_plane,
-                   float *__restrict__ emb_out, float *__restrict__ embT) {
+                   float *__restrict__ emb_out, float *__restrict__ embT, int skip_e) {
   __shared__ __align__(16) float sw1[64 * 4];
   __shared__ __align__(16) float swe[64 * 32];
   __shared__ float sb1[64], sbe[64];
@@ -55,7 +55,10 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
   const int n = live ? n_raw : N - 1;               // dead lanes shadow the last point (no stores)
   const size_t row = (size_t)f * N + n;
   float e[32];
-  if (choose != nullptr) {
+  if (skip_e) {                                     // emb branch reused from the previous refine iteration
+#pragma unroll
+    for (int ch = 0; ch < 32; ++ch) e[ch] = 0.f;
+  } else if (choose != nullptr) {
     long long c = choose[row];
     c = c < 0 ? 0 : (c >= hw ? hw - 1 : c);       // torch.gather would raise; we clamp
     const float *src = out_img + (size_t)f * 32 * hw + c;
@@ -78,8 +81,9 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
   }
   const float px = x[row * 3], py = x[row * 3 + 1], pz = x[row * 3 + 2];
   // 8 outputs at a time: conv1 (o < 64) then e_conv1 (o >= 64)
+  const int o8_end = skip_e ? 8 : 16;
 #pragma unroll 1
-  for (int o8 = 0; o8 < 16; ++o8) {
+  for (int o8 = 0; o8 < o8_end; ++o8) {
     float v[8];
     if (o8 < 8) {
 #pragma unroll
@@ -147,18 +151,18 @@ int first_layer(const float *packed, const NetLayout &L, const float *out_img, c
                 float *embT, cudaStream_t st) {
   dim3 grid((N + FL_THREADS - 1) / FL_THREADS, frames);
   first_layer_kernel<false><<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
-                                                         out_img, choose, emb_in, x, N, hw, pf, nullptr, 0, emb_out, embT);
+                                                         out_img, choose, emb_in, x, N, hw, pf, nullptr, 0, emb_out, embT, 0);
   return check_launch("first_layer");
 }
 
 // same, writing the split-bf16 planes consumed by the tensor-core layers
 int first_layer_bf16(const float *packed, const NetLayout &L, const float *out_img, const int64_t *choose,
                      const float *emb_in, const float *x, int frames, int N, int hw, __nv_bfloat16 *pfb,
-                     long long pf_plane, float *emb_out, cudaStream_t st) {
+                     long long pf_plane, float *emb_out, int skip_e, cudaStream_t st) {
   dim3 grid((N + FL_THREADS - 1) / FL_THREADS, frames);
   first_layer_kernel<true><<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
                                                         out_img, choose, emb_in, x, N, hw, nullptr, pfb, pf_plane, emb_out,
-                                                        nullptr);
+                                                        nullptr, skip_e);
   return check_launch("first_layer_bf16");
 }
 

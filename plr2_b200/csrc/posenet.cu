@@ -72,13 +72,13 @@ static int check_tc_ws(const NetLayout &L, void *ws, size_t bytes, int frames, i
 // first layer, conv2/e_conv2, conv5, conv6 + fused per-frame average pooling -> W.ap [F,1024]
 static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspace &W, const float *out_img,
                            const int64_t *choose, const float *emb_in, const float *x, int F, int N, int hw,
-                           float *emb_out, cudaStream_t st) {
+                           float *emb_out, bool reuse_emb, cudaStream_t st) {
   const int R = F * N;
   const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);   // split-bf16 weights
   const long long wplane = (long long)L.total;
   __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *x5 = (__nv_bfloat16 *)W.x5;
   // the refiner's trunk is consumed through the pool only (hi-only readers below): no lo plane needed
-  RC(first_layer_bf16(pk, L, out_img, choose, emb_in, x, F, N, hw, pf, L.net == PLR2_NET_REFINER ? 0 : W.pf_plane, emb_out, st));
+  RC(first_layer_bf16(pk, L, out_img, choose, emb_in, x, F, N, hw, pf, L.net == PLR2_NET_REFINER ? 0 : W.pf_plane, emb_out, reuse_emb ? 1 : 0, st));
   TcGemm g;
   g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.c2w; g.ldw = 64; g.w_plane = wplane;
   g.M = R; g.N = 128; g.K = 64; g.bias = pk + L.c2b; g.relu = 1;
@@ -86,6 +86,7 @@ static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspac
   // conv2 and e_conv2 in one launch (batch = branch): x1 -> pf[:,128:256), e1 -> pf[:,256:384)
   g.batch = 2; g.a_col_z = 64; g.b_row_z = (int)((L.e2w - L.c2w) / 64); g.c_col_z = 128;
   g.bias_z = (long long)(L.e2b - L.c2b);
+  if (reuse_emb) g.batch = 1;        // pf[:,64:128) and pf[:,256:384) still hold e_conv1 / e_conv2 of the same emb
   // Layers whose output is consumed ONLY through the per-frame average pool (conv5, conv6; in the refiner
   // also conv2/e_conv2) read just the hi plane of their activations (2 MMAs per MAC instead of 3): the
   // bf16 rounding of an activation is unbiased and independent from point to point, so it averages out
@@ -118,7 +119,7 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);
   const long long wplane = (long long)L.total;
   __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *h1 = (__nv_bfloat16 *)W.h1, *h2 = (__nv_bfloat16 *)W.h2;
-  RC(feat_forward_tc(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, st));
+  RC(feat_forward_tc(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, false, st));
   // per-frame bias of conv1_{r,t,c}: hb[F,1920] = ap W1[:,384:]^T + b1 (an M = frames GEMM, FP32 out)
   TcGemm g;
   g.A = (const __nv_bfloat16 *)W.apb; g.lda = 1024; g.a_plane = W.apb_plane; g.W = wb + L.h1ap; g.ldw = 1024; g.w_plane = wplane;
@@ -150,8 +151,8 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
 
 static int refiner_forward_tc(const float *pk, const NetLayout &L, const TcWorkspace &W, const float *x,
                               const float *emb, const int64_t *obj, int F, int N, float *pred_r, float *pred_t,
-                              cudaStream_t st) {
-  RC(feat_forward_tc(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, st));
+                              bool reuse_emb, cudaStream_t st) {
+  RC(feat_forward_tc(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, reuse_emb, st));
   // Linear 1024->512 (x2 heads) as one M = frames tensor-core GEMM; 512->128 (x2) and 128->7 for the frame's
   // class in FP32 SIMT
   const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);
@@ -311,10 +312,12 @@ extern "C" int plr2_refiner_forward(const float *packed, const float *x, const f
   if ((long long)frames * n_points > 0x7fffffffLL / 2048) { set_error("plr2_refiner_forward: too many rows per call"); return PLR2_E_SHAPE; }
   const NetLayout L = make_layout(PLR2_NET_REFINER, num_obj);
   cudaStream_t st = (cudaStream_t)stream;
+  const bool next_iter = training == PLR2_REFINER_NEXT_ITER;    // inference, emb branch already in the workspace
+  if (next_iter) training = 0;
   if (use_tc(precision, training, n_points)) {
     TcWorkspace T;
     RC(check_tc_ws(L, workspace, workspace_bytes, frames, n_points, T));
-    return refiner_forward_tc(packed, L, T, x, emb, obj, frames, n_points, pred_r, pred_t, st);
+    return refiner_forward_tc(packed, L, T, x, emb, obj, frames, n_points, pred_r, pred_t, next_iter, st);
   }
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));

@@ -128,3 +128,14 @@ class PoseRefineNet(nn.Module):
             raise ValueError(f"PoseRefineNet built for {self.num_points} points got {x.shape[1]}")
         return ops.RefinerFn.apply(self._state, self.precision, torch.is_grad_enabled(), x, emb, obj,
                                    *self.hot_path_parameters())
+
+    @torch.no_grad()
+    def forward_next_iteration(self, x, emb, obj):
+        """Extension (inference only): refine iteration >= 2 of the loop in tools/train.py:141-145, which passes
+        the SAME `emb` to every iteration. The emb branch (e_conv1, e_conv2) computed by the previous `forward`
+        call is reused from the workspace; if this call does not continue that one (different emb tensor,
+        parameters or shape) it silently runs the full forward. Same results as `forward`."""
+        if x.shape[1] != self.num_points:
+            raise ValueError(f"PoseRefineNet built for {self.num_points} points got {x.shape[1]}")
+        return ops.RefinerFn.apply(self._state, self.precision, ops.REFINER_NEXT_ITER, x, emb, obj,
+                                   *self.hot_path_parameters())

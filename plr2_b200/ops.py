@@ -268,6 +268,9 @@ class PoseNetFn(torch.autograd.Function):
         return (None, None, None, g_img, None, None, None) + tuple(grads)
 
 
+REFINER_NEXT_ITER = 2      # PLR2_REFINER_NEXT_ITER (include/plr2_b200.h)
+
+
 class RefinerFn(torch.autograd.Function):
     """PoseRefineNet.forward (lib/network.py:187-206) for F frames: x (F,N,3), emb (F,32,N), obj
     -> pred_r (F,4), pred_t (F,3)."""
@@ -279,15 +282,21 @@ class RefinerFn(torch.autograd.Function):
         F, N = x.shape[0], x.shape[1]
         xs, em = _f32c(x), _f32c(emb)
         ob = obj.detach().reshape(F).to(torch.int64).contiguous()
-        training = bool(grad_mode) and any(ctx.needs_input_grad)
+        next_iter = grad_mode == REFINER_NEXT_ITER and grad_mode is not True
+        training = (not next_iter) and bool(grad_mode) and any(ctx.needs_input_grad)
         packed = state.packed_for(params, precision)
         ws, nbytes = state.workspace(F, N, training, dev)
         pred_r = torch.empty((F, 4), dtype=torch.float32, device=dev)
         pred_t = torch.empty((F, 3), dtype=torch.float32, device=dev)
+        # the emb branch may be reused only if this call continues the previous one: same workspace, same emb
+        # tensor (storage and version), same parameters and shape; anything else runs the full forward
+        sig = (ws.data_ptr(), em.data_ptr(), em._version, emb.data_ptr(), F, N, state.key, precision)
+        mode = 1 if training else (REFINER_NEXT_ITER if next_iter and getattr(state, "last_infer_sig", None) == sig else 0)
+        state.last_infer_sig = None if training else sig
         with torch.cuda.device(dev):
             rc = _cabi.lib().plr2_refiner_forward(
                 _cabi.ptr(packed), _cabi.ptr(xs), _cabi.ptr(em), _cabi.ptr(ob), F, N, state.num_obj,
-                _cabi.ptr(ws), nbytes, _cabi.ptr(pred_r), _cabi.ptr(pred_t), int(training), precision,
+                _cabi.ptr(ws), nbytes, _cabi.ptr(pred_r), _cabi.ptr(pred_t), mode, precision,
                 _cabi.stream_ptr(dev))
         _cabi.check(rc, "plr2_refiner_forward")
         if training:

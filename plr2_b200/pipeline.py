@@ -56,8 +56,9 @@ class DenseFusionPipeline:
         if dis.dim() == 0:
             dis = dis.reshape(1)
         pose = self.criterion.last_pose.clone()          # (F,12) camera-frame pose after the best vote
-        for _ in range(self.refine_iters):
-            rr, rt = self.refiner(new_points, emb, obj)
+        for it in range(self.refine_iters):
+            # every iteration sees the same emb: from the second one on its branch is reused from the workspace
+            rr, rt = self.refiner(new_points, emb, obj) if it == 0 else self.refiner.forward_next_iteration(new_points, emb, obj)
             dis, new_points, new_target = self.criterion_refine(rr, rt, new_target, model_points, obj, new_points)
             ops.pose_compose_(pose, self.criterion_refine.last_pose)    # stays on the device (kernel (5))
         return dis, pose

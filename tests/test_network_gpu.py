@@ -301,3 +301,34 @@ def test_pipeline_refined_pose_matches_oracle_composition():
         pred = m @ R.T + t
         if obj not in shp.sym_list:
             assert abs(float((pred - tt(fr["target"]).double()).norm(dim=1).mean()) - float(d)) < 1e-4
+
+
+def test_refiner_next_iteration_reuses_the_emb_branch_bit_identically():
+    """forward_next_iteration (refine iteration >= 2, same emb) must give exactly what a full forward gives, and
+    must fall back to the full forward when the call does not continue the previous one."""
+    g = load_golden("refiner_ycb_sym")
+    shp = shape_of(g)
+    net = build_refiner(shp, int(g["seed"]), ops.PREC_BF16X2)
+    frames = 3
+    gen = torch.Generator().manual_seed(77)
+    emb = torch.randn(frames, 32, shp.num_points, generator=gen).cuda()
+    emb_other = torch.randn(frames, 32, shp.num_points, generator=gen).cuda()
+    x1 = (torch.randn(frames, shp.num_points, 3, generator=gen) * 0.05).cuda()
+    x2 = (torch.randn(frames, shp.num_points, 3, generator=gen) * 0.05).cuda()
+    idx = torch.tensor([[3], [12], [20]], device="cuda")
+    with torch.no_grad():
+        full2 = [t.clone() for t in net(x2, emb, idx)]
+        full2_other = [t.clone() for t in net(x2, emb_other, idx)]
+        net(x1, emb, idx)                                           # iteration 1
+        (r, t), _, n_tc, _ = ops.tensor_core_profile(lambda: net.forward_next_iteration(x2, emb, idx))
+        assert n_tc == 4
+        assert torch.equal(r, full2[0]) and torch.equal(t, full2[1])
+        # different emb tensor: not a continuation -> full forward, still right
+        r, t = net.forward_next_iteration(x2, emb_other, idx)
+        assert torch.equal(r, full2_other[0]) and torch.equal(t, full2_other[1])
+        # emb modified in place between the calls: version counter differs -> full forward
+        net(x1, emb, idx)
+        emb.mul_(0.5)
+        r, t = net.forward_next_iteration(x2, emb, idx)
+        ref = net(x2, emb, idx)
+        assert torch.equal(r, ref[0]) and torch.equal(t, ref[1])
