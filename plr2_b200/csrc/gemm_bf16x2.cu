@@ -103,6 +103,12 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
   const int num_kb = g.K / TC_BK;
   const int tiles_per_z = g.m_tiles * g.n_tiles;
   const int num_tiles = tiles_per_z * g.batch;
+  // Tile of round `it` for this unit.  The slot rotates by one per round so that every unit sees every
+  // n-tile index equally often (with a fixed slot, unit u would only ever meet n = (u + it*n_units) % n_tiles,
+  // and a half-width last n-tile would unbalance the units); each round still covers a contiguous tile range.
+  auto tile_of = [&](int it) { return it * n_units + (unit + it) % n_units; };
+  // Width of the MMA for n-tile `nt`: a last tile with at most BN/2 valid columns runs at N = BN/2
+  auto tile_nw = [&](int nt) { return (g.N - nt * BN <= BN / 2) ? BN / 2 : BN; };
 
   if (threadIdx.x == 0) {
     prefetch_tensormap(&tmA_hi); prefetch_tensormap(&tmA_lo);
@@ -124,9 +130,12 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     // ===================== TMA producer (both CTAs of a pair) =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int t = unit; t < num_tiles; t += n_units) {
+      for (int it = 0, t; (t = tile_of(it)) < num_tiles; ++it) {
         const int z = t / tiles_per_z, r = t % tiles_per_z;
-        const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = (r % g.n_tiles) * BN + rank * Cfg::B_ROWS;
+        const int nt = r % g.n_tiles;
+        // CG == 2: each CTA supplies half of the MMA's N columns, i.e. W rows [n_tile + rank*nw/2, +nw/2)
+        // (the box still loads B_ROWS rows; a half-width MMA reads the first nw/2 of them)
+        const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = nt * BN + (CG == 2 ? rank * (tile_nw(nt) / 2) : 0);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty_bar + stage, phase ^ 1);
           uint8_t *sA = smem + stage * Cfg::STAGE_BYTES;
@@ -153,10 +162,11 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
     if (lane == 0 && rank == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(TC_BM * CG, BN);
+      constexpr uint32_t idesc_full = make_idesc_bf16(TC_BM * CG, BN), idesc_half = make_idesc_bf16(TC_BM * CG, BN / 2);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
-      for (int t = unit; t < num_tiles; t += n_units) {
+      for (int it = 0, t; (t = tile_of(it)) < num_tiles; ++it) {
+        const uint32_t idesc = tile_nw((t % tiles_per_z) % g.n_tiles) == BN ? idesc_full : idesc_half;
         mbar_wait(tempty_bar + as, aphase ^ 1);          // epilogues (of both CTAs) have drained this accumulator
         fence_after_sync();
         const uint32_t tmem_d = tmem_base + as * BN;
@@ -245,13 +255,14 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
       }
     };
     float bnext[2] = {0.f, 0.f}, wnext[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-    if (unit < num_tiles) {
-      load_bias(unit, bnext);
-      if (BN == 128 && g.out_mode == TC_OUT_HEAD) load_headw(unit, wnext);
+    if (tile_of(0) < num_tiles) {
+      load_bias(tile_of(0), bnext);
+      if (BN == 128 && g.out_mode == TC_OUT_HEAD) load_headw(tile_of(0), wnext);
     }
-    for (int t = unit; t < num_tiles; t += n_units) {
+    for (int it = 0, t; (t = tile_of(it)) < num_tiles; ++it) {
       const int z = t / tiles_per_z, r = t % tiles_per_z;
       const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = (r % g.n_tiles) * BN;
+      const int nw_half = tile_nw(r % g.n_tiles) / 2;    // columns per warpgroup half in this tile
       // Stage bias[n] (+ frame_bias[frame][n]) of this tile's <= 2 frames: sB[sel][c], sel = row >= split_row.
       // The values were fetched while the previous tile was processed; the next tile's are requested now.
       const int fa = m0 / g.rows_per_frame;
@@ -267,9 +278,9 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         for (int u = 0; u < 4; ++u) sW[te + u * 32 * TC_EPI_WARPS] = wnext[u];
         if (te < 8) sW[2 * 4 * 128 + te] = wnext[4];
       }
-      if (t + n_units < num_tiles) {
-        load_bias(t + n_units, bnext);
-        if (BN == 128 && g.out_mode == TC_OUT_HEAD) load_headw(t + n_units, wnext);
+      if (tile_of(it + 1) < num_tiles) {
+        load_bias(tile_of(it + 1), bnext);
+        if (BN == 128 && g.out_mode == TC_OUT_HEAD) load_headw(tile_of(it + 1), wnext);
       }
       named_bar_sync(1, 32 * TC_EPI_WARPS);
       mbar_wait(tfull_bar + as, aphase);
@@ -280,7 +291,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         // of chunk i+1 is in flight while chunk i is processed; tile outputs leave through per-warp
         // shared-memory slabs and TMA stores (no LSU traffic), pooled sums through a halving butterfly.
         constexpr int NCH = BN / 2 / TC_EPI_COLS;
-        const int cbase = half * (BN / 2);
+        const int cbase = half * nw_half;
         const uint32_t tbase = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + as * BN + cbase;
         const int row = rbase + lane;
         const bool second = row >= split_row;
@@ -291,9 +302,9 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
 #pragma unroll
         for (int ci = 0; ci < NCH; ++ci) {
           const int c0 = ci * TC_EPI_COLS;
-          if (n0 + cbase + c0 >= g.N || g.debug == 2) break;          // warp-uniform
+          if (c0 >= nw_half || n0 + cbase + c0 >= g.N || g.debug == 2) break;          // warp-uniform
           tmem_ld_wait();
-          if (ci + 1 < NCH && n0 + cbase + c0 + TC_EPI_COLS < g.N) tmem_ld_32x16(tbase + c0 + TC_EPI_COLS, raw[(ci + 1) & 1]);
+          if (ci + 1 < NCH && c0 + TC_EPI_COLS < nw_half && n0 + cbase + c0 + TC_EPI_COLS < g.N) tmem_ld_32x16(tbase + c0 + TC_EPI_COLS, raw[(ci + 1) & 1]);
           float a[16];
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -522,6 +533,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         __syncwarp();
       }
       }
+      tmem_ld_wait();                                     // a prefetched chunk that was never consumed (no valid columns)
       fence_before_sync();
       __syncwarp();
       if (lane == 0) {                                    // one arrival per epilogue warp (CG * 8 in total)
