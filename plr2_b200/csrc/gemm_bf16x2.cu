@@ -209,7 +209,8 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     int as = 0; uint32_t aphase = 0;
     unsigned slab_i = 0;                                  // ring position, runs across tiles
     // bias (+ per-frame bias) of a tile for this thread's staging slots i = te, te + 256 (< 2*BN)
-    auto load_bias = [&](int t, float (&bv)[2]) {
+    // (the two addends stay in separate registers until they are staged, so nothing waits on the loads here)
+    auto load_bias = [&](int t, float (&bv)[2], float (&fv)[2]) {
       const int z = t / tiles_per_z, r = t % tiles_per_z;
       const int m0 = (r / g.n_tiles) * (TC_BM * CG) + rank * TC_BM, n0 = (r % g.n_tiles) * BN;
       const float *bias = g.bias ? g.bias + z * g.bias_z : nullptr;
@@ -218,15 +219,14 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
       for (int u = 0; u < 2; ++u) {
         const int i = te + u * 32 * TC_EPI_WARPS;
         const int sel = i / BN, c = i - sel * BN, n = n0 + c;
-        float v = 0.f;
+        bv[u] = 0.f; fv[u] = 0.f;
         if (i < 2 * BN && n < g.N) {
-          if (bias) v = __ldg(bias + n);
+          if (bias) bv[u] = __ldg(bias + n);
           if (g.frame_bias) {
             const long long fr = fa + sel;
-            if (fr * g.rows_per_frame < g.M) v += __ldg(g.frame_bias + fr * g.ldfb + n);
+            if (fr * g.rows_per_frame < g.M) fv[u] = __ldg(g.frame_bias + fr * g.ldfb + n);
           }
         }
-        bv[u] = v;
       }
     };
     // TC_OUT_HEAD: last-layer weights of head z for the classes of the tile's <= 2 frames, slots
@@ -254,9 +254,9 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         wv[u] = v;
       }
     };
-    float bnext[2] = {0.f, 0.f}, wnext[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    float bnext[2] = {0.f, 0.f}, fnext[2] = {0.f, 0.f}, wnext[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
     if (tile_of(0) < num_tiles) {
-      load_bias(tile_of(0), bnext);
+      load_bias(tile_of(0), bnext, fnext);
       if (BN == 128 && g.out_mode == TC_OUT_HEAD) load_headw(tile_of(0), wnext);
     }
     for (int it = 0, t; (t = tile_of(it)) < num_tiles; ++it) {
@@ -271,7 +271,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         const int i = te + u * 32 * TC_EPI_WARPS;
-        if (i < 2 * BN) sB[i] = bnext[u];
+        if (i < 2 * BN) sB[i] = bnext[u] + fnext[u];
       }
       if (BN == 128 && g.out_mode == TC_OUT_HEAD) {
 #pragma unroll
@@ -279,7 +279,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
         if (te < 8) sW[2 * 4 * 128 + te] = wnext[4];
       }
       if (tile_of(it + 1) < num_tiles) {
-        load_bias(tile_of(it + 1), bnext);
+        load_bias(tile_of(it + 1), bnext, fnext);
         if (BN == 128 && g.out_mode == TC_OUT_HEAD) load_headw(tile_of(it + 1), wnext);
       }
       named_bar_sync(1, 32 * TC_EPI_WARPS);
