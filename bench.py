@@ -227,6 +227,61 @@ def run_reference(args, world, rank):
     print(json.dumps(line), flush=True)
 
 
+def time_with_backbone(pipe, devw, frames, dev, chunk=64):
+    """SURVEY 8d asks for the metric with and without the (out-of-scope) PSPNet/ResNet-18 backbone: the same
+    device-resident chain, but `out_img` is produced by the backbone (PyTorch, random-init weights) from synthetic
+    `img` = randn(3,H,W) (lib/network.py:96, lib/pspnet.py:40-77).  `value` is the parity-preserving fp32 figure
+    (TF32 off): the best of the fp32 variants of the batched runner of SURVEY 8f-1 (plr2_b200/backbone.py); the
+    reduced-precision modes are listed beside it."""
+    from plr2_b200.backbone import BatchedBackbone
+    from plr2_b200.lib.network import ModifiedResnet
+    h, w = devw["out_img"].shape[-2:]
+    gen = torch.Generator(device=dev).manual_seed(5)
+    img = torch.randn(frames, 3, h, w, device=dev, generator=gen)
+    keys = [k for k in ("points", "choose", "obj", "target", "model_points")]
+
+    def measure(make_out_img, reps=3):
+        @torch.no_grad()
+        def step():
+            out = None
+            for a in range(0, frames, chunk):
+                b = min(frames, a + chunk)
+                out = pipe.infer(make_out_img(img[a:b]), *(devw[k][a:b] for k in keys))
+            return out
+        for _ in range(2):
+            res = step()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            res = step()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1) / reps
+        return {"poses_per_s": frames / (ms / 1e3), "ms_per_step": ms, "results_finite": bool(torch.isfinite(res).all())}
+
+    variants = {}
+    for name, kw in (("eager_fp32_nchw", dict(precision="fp32", channels_last=False, cuda_graph=False)),
+                     ("graph_fp32_nchw", dict(precision="fp32", channels_last=False, cuda_graph=True)),
+                     ("graph_fp32_channels_last", dict(precision="fp32", channels_last=True, cuda_graph=True)),
+                     ("graph_tf32_channels_last", dict(precision="tf32", channels_last=True, cuda_graph=True)),
+                     ("graph_bf16_channels_last", dict(precision="bf16", channels_last=True, cuda_graph=True))):
+        torch.manual_seed(0)
+        bb = BatchedBackbone(ModifiedResnet().to(dev), batch=chunk, **kw)
+        try:
+            variants[name] = measure(bb)
+        except Exception as exc:                      # a variant that cannot run here is reported, not hidden
+            variants[name] = {"error": f"{type(exc).__name__}: {exc}"[:200]}
+        del bb
+        torch.cuda.empty_cache()
+    fp32 = [v for k, v in variants.items() if "fp32" in k and "poses_per_s" in v]
+    best = max(fp32, key=lambda v: v["poses_per_s"]) if fp32 else {}
+    return {"value": best.get("poses_per_s"), "unit": "poses/s", "frames_per_step": frames,
+            "backbone": f"PSPNet/ResNet-18 in PyTorch, fp32 (TF32 off), batches of {chunk} frames, random-init weights; "
+                        "tf32/bf16 variants are reduced precision (not parity modes)",
+            "variants": variants}
+
+
 def run_ours(args, world, rank, local):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (this path has no CPU fallback; use --impl reference)")
@@ -341,6 +396,9 @@ def run_ours(args, world, rank, local):
         ref = cpu_reference_step(work, pnt, rft, 2)
         got = [float(x) for x in res_host[:2]]
         cpu["check_first2_rel_err"] = [abs(a - b) / max(abs(b), 1e-12) for a, b in zip(got, ref)]
+    with_bb = None
+    if world == 1 and args.backbone_frames > 0:
+        with_bb = time_with_backbone(pipe, devw, min(args.backbone_frames, frames), dev)
     eager = None
     if world == 1 and args.eager_frames > 0:
         eager = time_gpu_eager(work, pn, rf, args.eager_frames, dev)
@@ -364,6 +422,7 @@ def run_ours(args, world, rank, local):
         "knn_gpairs_per_s": {k: v["Gpairs_s"] for k, v in knn.items()},
         "cpu_baseline": cpu,
         "gpu_eager_baseline": eager,
+        "with_backbone": with_bb,
     }
     print(json.dumps(line), flush=True)
 
@@ -381,6 +440,8 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=8, help="frames of the CPU baseline sample (0 = skip)")
     ap.add_argument("--profile-step", action="store_true",
                     help="run ONE step between cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)")
+    ap.add_argument("--backbone-frames", type=int, default=256,
+                    help="frames of the extra with-backbone measurement (N=1 only; 0 disables)")
     ap.add_argument("--eager-frames", type=int, default=16,
                     help="frames of the same-box eager-PyTorch GPU baseline (reference algorithm, fp32, bs=1 loop; 0 = skip)")
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the reference arm")
