@@ -172,7 +172,14 @@ int plr2_auc_f32(const float *dist, int n, double max_distance, double below, do
  *   depth is uint16 (depth_is_u16 != 0, the PNG's type) or float32. cam [F][5] float32 = (cx, cy, fx, fy, scale).
  *
  * plr2_transform_target: target[f][j] = model_points[f][j] . R[f]^T + t[f] (+ add_t[f]) in float64, rounded
- *   to float32 (dataset.py:215-219,229); R [F][9] row-major, t [F][3], add_t [F][3] or NULL, all float64. */
+ *   to float32 (dataset.py:215-219,229); R [F][9] row-major, t [F][3], add_t [F][3] or NULL, all float64. *
+ * plr2_mask_bbox: mask[f] = (label[f] == obj_id[f]) & (depth[f] != 0) (dataset.py:143-145, uint8 0/1), count[f] its
+ *   number of set pixels (the `> minimum_num_pt` test of :146), bbox[f] = get_bbox(label[f] == obj_id[f])
+ *   (dataset.py:251-289): tight box of the label pixels, each side snapped up to the next multiple of 40
+ *   (border_list), centred, then shifted back inside the img_h x img_w image. No label pixel: bbox = 0,0,0,0
+ *   (the reference raises IndexError). label is uint8 (the -label.png class ids). */
+int plr2_mask_bbox(const void *depth, int depth_is_u16, const uint8_t *label, const int32_t *obj_id, int frames,
+                   int img_h, int img_w, uint8_t *mask, int32_t *bbox, int32_t *count, void *stream);
 size_t plr2_choose_workspace_bytes(int frames, int max_crop_pixels);
 int plr2_choose_from_mask(const uint8_t *mask, int img_h, int img_w, const int32_t *bbox, int frames,
                           int n_points, const uint8_t *keep, long long keep_stride, unsigned long long seed,

@@ -27,6 +27,7 @@ SIGNATURES = {
     "plr2_pose_compose": (_i, [_vp, _vp, _i, _vp]),
     "plr2_pose_metric_workspace_bytes": (_sz, [_i]),
     "plr2_pose_metric": (_i, [_vp, C.c_longlong, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    "plr2_mask_bbox": (_i, [_vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "plr2_choose_workspace_bytes": (_sz, [_i, _i]),
     "plr2_choose_from_mask": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, C.c_longlong, C.c_ulonglong, _vp, _vp, _vp, _sz, _vp]),
     "plr2_backproject": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),

@@ -258,3 +258,80 @@ extern "C" int plr2_transform_target(const float *model_points, const double *R,
   transform_target_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(model_points, R, t, add_t, n_mesh, target);
   return check_launch("plr2_transform_target");
 }
+
+// ---------------------------------------------------------------------------------------------
+// mask = (label == obj) & (depth != 0), bbox = get_bbox(label == obj)  (datasets/ycb/dataset.py:143-145, 251-289)
+namespace plr2 {
+
+// snap a side length up to the next entry of border_list = [-1, 40, 80, ..., 680] (dataset.py:247,258-267):
+// values strictly between two borders go to the upper one, values ON a border (or beyond the list) stay
+__device__ __forceinline__ int snap_border(int b) {
+  if (b <= -1 || b >= 680) return b;
+  if (b < 40) return 40;                                  // between -1 and 40
+  return (b % 40 == 0) ? b : (b / 40 + 1) * 40;
+}
+
+template <typename DT>
+__global__ void __launch_bounds__(1024)
+mask_bbox_kernel(const DT *__restrict__ depth, const uint8_t *__restrict__ label, const int32_t *__restrict__ obj_id,
+                 int img_h, int img_w, uint8_t *__restrict__ mask, int32_t *__restrict__ bbox, int32_t *__restrict__ count) {
+  __shared__ int s_rmin, s_rmax, s_cmin, s_cmax, s_cnt;
+  const int f = blockIdx.x, tid = threadIdx.x;
+  if (tid == 0) { s_rmin = img_h; s_rmax = -1; s_cmin = img_w; s_cmax = -1; s_cnt = 0; }
+  __syncthreads();
+  const int obj = obj_id[f];
+  const size_t base = (size_t)f * img_h * img_w;
+  const int P = img_h * img_w;
+  int rmin = img_h, rmax = -1, cmin = img_w, cmax = -1, cnt = 0;
+  for (int p = tid; p < P; p += 1024) {
+    const bool lab = (int)label[base + p] == obj;
+    const bool m = lab && depth[base + p] != (DT)0;
+    mask[base + p] = m ? 1 : 0;
+    cnt += m ? 1 : 0;
+    if (lab) {
+      const int r = p / img_w, c = p - r * img_w;
+      rmin = min(rmin, r); rmax = max(rmax, r); cmin = min(cmin, c); cmax = max(cmax, c);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    rmin = min(rmin, __shfl_xor_sync(0xffffffffu, rmin, o)); rmax = max(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+    cmin = min(cmin, __shfl_xor_sync(0xffffffffu, cmin, o)); cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, o));
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  }
+  if ((tid & 31) == 0) {
+    atomicMin(&s_rmin, rmin); atomicMax(&s_rmax, rmax); atomicMin(&s_cmin, cmin); atomicMax(&s_cmax, cmax);
+    atomicAdd(&s_cnt, cnt);
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  if (count) count[f] = s_cnt;
+  int r0 = s_rmin, r1 = s_rmax + 1, c0 = s_cmin, c1 = s_cmax + 1;       // rmax += 1; cmax += 1 (:256-257)
+  if (s_rmax < 0) { bbox[4 * f] = bbox[4 * f + 1] = bbox[4 * f + 2] = bbox[4 * f + 3] = 0; return; }
+  const int r_b = snap_border(r1 - r0), c_b = snap_border(c1 - c0);
+  const int cr = (r0 + r1) / 2, cc = (c0 + c1) / 2;                    // int((rmin + rmax) / 2): operands >= 0
+  r0 = cr - r_b / 2; r1 = cr + r_b / 2; c0 = cc - c_b / 2; c1 = cc + c_b / 2;
+  if (r0 < 0) { r1 += -r0; r0 = 0; }
+  if (c0 < 0) { c1 += -c0; c0 = 0; }
+  if (r1 > img_h) { r0 -= r1 - img_h; r1 = img_h; }
+  if (c1 > img_w) { c0 -= c1 - img_w; c1 = img_w; }
+  bbox[4 * f] = r0; bbox[4 * f + 1] = r1; bbox[4 * f + 2] = c0; bbox[4 * f + 3] = c1;
+}
+
+}  // namespace plr2
+
+extern "C" int plr2_mask_bbox(const void *depth, int depth_is_u16, const uint8_t *label, const int32_t *obj_id, int frames,
+                              int img_h, int img_w, uint8_t *mask, int32_t *bbox, int32_t *count, void *stream) {
+  if (frames < 0 || img_h <= 0 || img_w <= 0 || (long long)img_h * img_w > (1ll << 30)) {
+    plr2::set_error("plr2_mask_bbox: bad shape F=%d img=%dx%d", frames, img_h, img_w);
+    return PLR2_E_SHAPE;
+  }
+  if (frames == 0) return 0;
+  if (!depth || !label || !obj_id || !mask || !bbox) { plr2::set_error("plr2_mask_bbox: null pointer"); return PLR2_E_NULLPTR; }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (depth_is_u16)
+    plr2::mask_bbox_kernel<uint16_t><<<frames, 1024, 0, st>>>((const uint16_t *)depth, label, obj_id, img_h, img_w, mask, bbox, count);
+  else
+    plr2::mask_bbox_kernel<float><<<frames, 1024, 0, st>>>((const float *)depth, label, obj_id, img_h, img_w, mask, bbox, count);
+  return plr2::check_launch("plr2_mask_bbox");
+}

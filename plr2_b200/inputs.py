@@ -1,13 +1,14 @@
 """Input step before the hot path, on the device.
 
-Batched equivalents of what ``datasets/ycb/dataset.py:177-197,215-219`` (and ``src/loaders_v2/dataset_ycb.py:
+Batched equivalents of what ``datasets/ycb/dataset.py:143-146,177-197,215-219,251-289`` (and ``src/loaders_v2/dataset_ycb.py:
 91-119``: ``_compute_choose``, ``pointcloud``) do per frame with numpy on the host:
 
+    mask_and_bbox      depth + label + class id -> object mask, ``get_bbox`` crop, pixel count
     choose_from_mask   mask crop -> ``choose`` (F,1,N) int64   (nonzero, wrap pad / order-preserving subset)
     pointcloud         depth + choose + intrinsics -> ``cloud`` (F,N,3) float32
     transform_target   model_points . R^T + t (+ add_t) -> ``target`` (F,M,3) float32
 
-All three go through the C-ABI (``plr2_choose_from_mask``, ``plr2_backproject``, ``plr2_transform_target``);
+All go through the C-ABI (``plr2_mask_bbox``, ``plr2_choose_from_mask``, ``plr2_backproject``, ``plr2_transform_target``);
 CPU tensors raise ``Plr2Error`` - there is no host fallback.
 """
 import torch
@@ -116,3 +117,32 @@ def transform_target(model_points, target_r, target_t, add_t=None):
                                                _cabi.ptr(out), _cabi.stream_ptr(dev))
     _cabi.check(rc, "plr2_transform_target")
     return out
+
+
+def mask_and_bbox(depth, label, obj_id):
+    """depth (F,H,W) uint16 bits (int16/uint16) or float32, label (F,H,W) uint8, obj_id (F,) int ->
+    (mask (F,H,W) uint8 = (label == obj_id) & (depth != 0), bbox (F,4) int32 = get_bbox(label == obj_id),
+    count (F,) int32 = mask.sum()) - datasets/ycb/dataset.py:143-146 and get_bbox :251-289."""
+    depth = _cuda(depth, "mask_and_bbox")
+    label = _cuda(label, "mask_and_bbox")
+    if label.dtype != torch.uint8 or label.dim() != 3 or label.shape != depth.shape:
+        raise ValueError("inputs.mask_and_bbox: label must be (F,H,W) uint8 with depth's shape")
+    frames, h, w = depth.shape
+    dev = depth.device
+    if depth.dtype in (torch.int16, torch.uint16):
+        d, is_u16 = depth.contiguous(), 1
+    elif depth.dtype == torch.float32:
+        d, is_u16 = depth.contiguous(), 0
+    else:
+        d, is_u16 = depth.to(torch.float32).contiguous(), 0
+    oid = _cuda(obj_id, "mask_and_bbox").reshape(frames).to(torch.int32).contiguous()
+    mask = torch.empty(frames, h, w, device=dev, dtype=torch.uint8)
+    bbox = torch.empty(frames, 4, device=dev, dtype=torch.int32)
+    count = torch.empty(frames, device=dev, dtype=torch.int32)
+    if frames == 0:
+        return mask, bbox, count
+    with torch.cuda.device(dev):
+        rc = _cabi.lib().plr2_mask_bbox(_cabi.ptr(d), is_u16, _cabi.ptr(label.contiguous()), _cabi.ptr(oid), frames, h, w,
+                                        _cabi.ptr(mask), _cabi.ptr(bbox), _cabi.ptr(count), _cabi.stream_ptr(dev))
+    _cabi.check(rc, "plr2_mask_bbox")
+    return mask, bbox, count

@@ -151,3 +151,67 @@ def test_no_cpu_fallback():
         inputs.choose_from_mask(torch.zeros(1, 4, 4, dtype=torch.uint8), torch.zeros(1, 4, dtype=torch.int32), 4)
     with pytest.raises(_cabi.Plr2Error):
         inputs.pointcloud(torch.zeros(1, 4, 4), torch.zeros(1, 4), torch.zeros(1, 1, 4), torch.zeros(1, 5))
+
+
+def test_mask_and_bbox_bit_exact():
+    """mask = (label == obj) & (depth != 0) and get_bbox of the label mask against the numpy restatement of
+    dataset.py:143-145,251-289: blobs at the image borders, on exact multiples of 40, single pixels, absent object."""
+    rng = np.random.default_rng(21)
+    cases = [(0, 0, 37, 55), (470, 630, 10, 10), (100, 200, 40, 80), (100, 200, 41, 79), (0, 600, 480, 40), (200, 300, 1, 1),
+             (5, 5, 300, 500), (430, 0, 50, 640), (17, 333, 121, 161)]
+    frames = len(cases) + 1
+    label = rng.integers(0, 5, size=(frames, H, W)).astype(np.uint8) * 0            # background 0
+    depth = rng.integers(0, 3, size=(frames, H, W)).astype(np.uint16) * 4000        # a third of the pixels invalid
+    obj = np.arange(3, 3 + frames).astype(np.int32)
+    for f, (r0, c0, h, w) in enumerate(cases):
+        blob = rng.random((h, w)) < 0.8
+        blob[0, :] |= True; blob[-1, :] |= True; blob[:, 0] |= True; blob[:, -1] |= True     # tight extent known
+        label[f, r0:r0 + h, c0:c0 + w][blob] = obj[f]
+        label[f, (r0 + 200) % H, (c0 + 300) % W] = obj[f] + 1 if f % 2 else 0            # another class elsewhere
+    # last frame: object absent
+    mask, bbox, count = inputs.mask_and_bbox(torch.from_numpy(depth.view(np.int16)).cuda(), torch.from_numpy(label).cuda(),
+                                             torch.from_numpy(obj).cuda())
+    mask, bbox, count = mask.cpu().numpy(), bbox.cpu().numpy(), count.cpu().numpy()
+    for f in range(frames - 1):
+        m, ml = IO.object_mask(depth[f], label[f], obj[f])
+        np.testing.assert_array_equal(mask[f], m.astype(np.uint8))
+        assert count[f] == int(m.sum())
+        assert tuple(bbox[f]) == tuple(int(v) for v in IO.get_bbox(ml)), (f, bbox[f], IO.get_bbox(ml))
+        rmin, rmax, cmin, cmax = bbox[f]
+        assert 0 <= rmin < rmax <= H and 0 <= cmin < cmax <= W and (rmax - rmin) % 40 == 0 and (cmax - cmin) % 40 == 0
+    assert tuple(bbox[-1]) == (0, 0, 0, 0) and count[-1] == 0 and mask[-1].sum() == 0
+    # float32 depth gives the same
+    mask2, bbox2, _ = inputs.mask_and_bbox(torch.from_numpy(depth.astype(np.float32)).cuda(), torch.from_numpy(label).cuda(),
+                                           torch.from_numpy(obj).cuda())
+    assert np.array_equal(mask2.cpu().numpy(), mask) and np.array_equal(bbox2.cpu().numpy(), bbox)
+
+
+def test_input_chain_on_device():
+    """depth + label -> mask/bbox -> choose -> cloud, all on the device, equals the numpy chain frame by frame."""
+    rng = np.random.default_rng(31)
+    frames, num_pt = 4, 1000
+    label = np.zeros((frames, H, W), dtype=np.uint8)
+    depth = rng.integers(3000, 20000, size=(frames, H, W)).astype(np.uint16)
+    depth[rng.random((frames, H, W)) < 0.1] = 0
+    obj = np.array([7, 2, 15, 9], dtype=np.int32)
+    for f, (r0, c0, h, w) in enumerate([(50, 60, 130, 170), (300, 400, 60, 45), (0, 0, 25, 25), (200, 100, 200, 333)]):
+        label[f, r0:r0 + h, c0:c0 + w][rng.random((h, w)) < 0.85] = obj[f]
+    dd, dl, do = torch.from_numpy(depth.view(np.int16)).cuda(), torch.from_numpy(label).cuda(), torch.from_numpy(obj).cuda()
+    mask, bbox, count = inputs.mask_and_bbox(dd, dl, do)
+    keep = np.zeros((frames, H * W), dtype=np.uint8)
+    ref_choose, ref_cloud = [], []
+    for f in range(frames):
+        m, ml = IO.object_mask(depth[f], label[f], obj[f])
+        bb = IO.get_bbox(ml)
+        cnt = int(m[bb[0]:bb[1], bb[2]:bb[3]].sum())
+        c_mask = None
+        if cnt > num_pt:
+            c_mask = np.zeros(cnt, dtype=int); c_mask[:num_pt] = 1; rng.shuffle(c_mask); keep[f, :cnt] = c_mask
+        ch, _ = IO.compute_choose(m, bb, num_pt, c_mask)
+        ref_choose.append(ch)
+        ref_cloud.append(IO.pointcloud(depth[f], bb, ch, *CAM, np.uint16(10000)))
+    choose, cnt = inputs.choose_from_mask(mask, bbox, num_pt, keep=torch.from_numpy(keep).cuda())
+    cam = torch.tensor([[*CAM, 10000.0]] * frames, device="cuda")
+    cloud = inputs.pointcloud(dd, bbox, choose, cam)
+    np.testing.assert_array_equal(choose[:, 0].cpu().numpy(), np.stack(ref_choose))
+    np.testing.assert_array_equal(cloud.cpu().numpy().view(np.uint32), np.stack(ref_cloud).view(np.uint32))

@@ -34,3 +34,17 @@ def test_transform_target_is_rigid():
     out = IO.transform_target(pts, R, t)
     np.testing.assert_allclose(out, (R @ pts.T).T + t, rtol=1e-5, atol=1e-6)
     assert out.dtype == np.float32
+
+
+def test_get_bbox_snaps_to_multiples_of_40_and_stays_inside():
+    lab = np.zeros((480, 640), dtype=bool)
+    lab[100:141, 200:279] = True                       # 41 x 79 -> 80 x 80 around the centre
+    rmin, rmax, cmin, cmax = IO.get_bbox(lab)
+    assert (rmax - rmin, cmax - cmin) == (80, 80) and rmin <= 100 and rmax >= 141 and cmin <= 200 and cmax >= 279
+    lab[:] = False
+    lab[0:10, 630:640] = True                          # corner: shifted back inside the image
+    rmin, rmax, cmin, cmax = IO.get_bbox(lab)
+    assert (rmin, rmax, cmin, cmax) == (0, 40, 600, 640)
+    lab[:] = False
+    lab[100:140, 200:280] = True                       # already on the borders: unchanged
+    assert IO.get_bbox(lab) == (100, 140, 200, 280)
