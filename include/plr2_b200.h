@@ -133,6 +133,12 @@ int plr2_pose_compose(float *pose_acc, const float *pose_delta, int frames, void
  * add or adds may be NULL (not computed). FP32 arithmetic (the reference computes in float64).
  * workspace: plr2_pose_metric_workspace_bytes(frames) bytes, contents irrelevant. n_mesh <= 8192. */
 size_t plr2_pose_metric_workspace_bytes(int frames);
+/* Rotation and translation error between two poses per frame (src/estimation/errors.py:12-51):
+ *   rot_err[f]   = || Rodrigues(Ra Rb^T) || = rotation angle of Ra Rb^T in [0, pi]   (errors.py:29-32)
+ *   trans_err[f] = || ta - tb ||                                                     (errors.py:50)
+ * computed as atan2(|axis vector|, trace - 1) (well conditioned at both ends). Either output may be NULL. */
+int plr2_pose_errors(const float *pose_a, const float *pose_b, int frames, float *rot_err, float *trans_err,
+                     void *stream);
 int plr2_pose_metric(const float *model_points, long long model_stride, const float *pose_a,
                      const float *pose_b, int frames, int n_mesh, float *add, float *adds,
                      void *workspace, size_t workspace_bytes, void *stream);

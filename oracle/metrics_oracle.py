@@ -3,10 +3,12 @@
 numpy float64 restatement of the reference's evaluation metrics:
 
     add, adds   <- src/estimation/errors.py:53-67, 69-84 (points.apply_transform: src/estimation/state.py:235-247)
+    rotation_error, translation_error <- src/estimation/errors.py:12-51
     vocap, auc  <- replace_ycb_toolbox/plot_accuracy_keyframe.m:38-52 (sort, accuracy, "< 2 cm") and
                    VOCap :150-170
 
-Pinning: add/adds are checked against outputs of the reference's own ``estimation.errors.ADD/ADDS`` (imported
+Pinning: add/adds/rotation_error/translation_error are checked against outputs of the reference's own
+``estimation.errors`` functions (imported
 from /root/reference/src by tests/golden/make_metrics_golden.py, fixture tests/golden/metrics_add_adds.npz)
 and against its known-answer cases in src/estimation/main.py:117-131.  The AUC script is MATLAB and cannot be
 run here: PARITY UNPINNED for ``auc`` beyond hand-computed known answers (tests/test_metrics_oracle.py).
@@ -61,3 +63,15 @@ def auc(distances, max_distance=0.1, below=0.02):
     c = int(np.sum(d < below))
     accuracy = np.cumsum(np.ones(n)) / n
     return vocap(d, accuracy, max_distance), c / n
+
+
+def rotation_error(pose1, pose2):
+    """errors.py:12-32 on homogeneous matrices: norm of the Rodrigues vector of R1 R2^T = its rotation angle."""
+    R = np.asarray(pose1, dtype=np.float64)[:3, :3] @ np.asarray(pose2, dtype=np.float64)[:3, :3].T
+    v = np.array([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]])
+    return float(np.arctan2(np.linalg.norm(v), np.trace(R) - 1.0))
+
+
+def translation_error(pose1, pose2):
+    """errors.py:34-51."""
+    return float(np.linalg.norm(np.asarray(pose1, dtype=np.float64)[:3, 3] - np.asarray(pose2, dtype=np.float64)[:3, 3]))

@@ -32,6 +32,7 @@ SIGNATURES = {
     "plr2_choose_from_mask": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, C.c_longlong, C.c_ulonglong, _vp, _vp, _vp, _sz, _vp]),
     "plr2_backproject": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),
     "plr2_transform_target": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),
+    "plr2_pose_errors": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
     "plr2_auc_workspace_bytes": (_sz, [_i]),
     "plr2_auc_f32": (_i, [_vp, _i, C.c_double, C.c_double, _vp, _vp, _sz, _vp]),
     "plr2_refine_loss_workspace_bytes": (_sz, [_i, _i]),

@@ -104,6 +104,29 @@ __global__ void pose_metric_finish_kernel(const float *__restrict__ partial, int
   if (adds) adds[f] = b / (float)M;
 }
 
+__global__ void pose_errors_kernel(const float *__restrict__ pa, const float *__restrict__ pb, int frames,
+                                   float *__restrict__ rot_err, float *__restrict__ trans_err) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= frames) return;
+  const float *A = pa + (size_t)f * 12, *B = pb + (size_t)f * 12;
+  float D[9];                                              // D = Ra Rb^T
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      D[3 * i + j] = fmaf(A[3 * i], B[3 * j], fmaf(A[3 * i + 1], B[3 * j + 1], A[3 * i + 2] * B[3 * j + 2]));
+  if (rot_err) {
+    const float vx = D[7] - D[5], vy = D[2] - D[6], vz = D[3] - D[1];        // 2 sin(angle) * axis
+    const float s2 = sqrtf(fmaf(vz, vz, fmaf(vy, vy, vx * vx)));
+    const float c2 = D[0] + D[4] + D[8] - 1.0f;                               // 2 cos(angle)
+    rot_err[f] = atan2f(s2, c2);
+  }
+  if (trans_err) {
+    const float dx = A[9] - B[9], dy = A[10] - B[10], dz = A[11] - B[11];
+    trans_err[f] = sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
+  }
+}
+
 // ---- AUC -----------------------------------------------------------------------------------
 constexpr int AUC_THREADS = 256;
 struct AucPartial { double contrib; double dmax; long long below; long long nfin; };
@@ -219,6 +242,15 @@ extern "C" int plr2_pose_metric(const float *model_points, long long model_strid
   }
   pose_metric_finish_kernel<<<(frames + 127) / 128, 128, 0, st>>>(partial, frames, n_mesh, slices, add, adds);
   return check_launch("plr2_pose_metric", 2);
+}
+
+extern "C" int plr2_pose_errors(const float *pose_a, const float *pose_b, int frames, float *rot_err, float *trans_err,
+                                void *stream) {
+  if (frames < 0) { set_error("plr2_pose_errors: bad shape F=%d", frames); return PLR2_E_SHAPE; }
+  if (frames == 0) return 0;
+  if (!pose_a || !pose_b || (!rot_err && !trans_err)) { set_error("plr2_pose_errors: null pointer"); return PLR2_E_NULLPTR; }
+  pose_errors_kernel<<<(frames + 127) / 128, 128, 0, (cudaStream_t)stream>>>(pose_a, pose_b, frames, rot_err, trans_err);
+  return check_launch("plr2_pose_errors");
 }
 
 extern "C" size_t plr2_auc_workspace_bytes(int n) {

@@ -3,6 +3,7 @@
 Mirrors the reference's evaluation helpers:
   * ``ADD`` / ``ADDS``  - ``src/estimation/errors.py:53-67`` / ``:69-84`` (model points under two poses;
     ADD-S = mean distance of every ``pose2`` point to its nearest ``pose1`` point);
+  * ``pose_errors``     - ``src/estimation/errors.py:12-51`` (rotation angle and translation distance between poses);
   * ``auc``             - ``replace_ycb_toolbox/plot_accuracy_keyframe.m:38-52`` with ``VOCap`` ``:150-170``
     (AUC of the accuracy-threshold curve up to 0.1 m and the "< 2 cm" rate).
 
@@ -70,6 +71,24 @@ def ADD(model_points, pose1, pose2):
 def ADDS(model_points, pose1, pose2):
     """``src/estimation/errors.py:69-84`` for F frames at once."""
     return pose_metrics(model_points, pose1, pose2, False, True)[1]
+
+
+def pose_errors(pose1, pose2):
+    """``(rotation_error, translation_error)`` per frame, each ``(F,)`` float32: ``src/estimation/errors.py:12-32``
+    (norm of the Rodrigues vector of ``R1 R2^T``, i.e. the rotation angle in radians) and ``:34-51``."""
+    a, b = _pose12(pose1), _pose12(pose2)
+    if a.shape != b.shape:
+        raise ValueError("metrics: pose1/pose2 shapes differ: %s vs %s" % (tuple(a.shape), tuple(b.shape)))
+    frames, dev = a.shape[0], a.device
+    rot = torch.empty(frames, device=dev, dtype=torch.float32)
+    tr = torch.empty(frames, device=dev, dtype=torch.float32)
+    if frames == 0:
+        return rot, tr
+    with torch.cuda.device(dev):
+        rc = _cabi.lib().plr2_pose_errors(_cabi.ptr(a), _cabi.ptr(b), frames, _cabi.ptr(rot), _cabi.ptr(tr),
+                                          _cabi.stream_ptr(dev))
+    _cabi.check(rc, "plr2_pose_errors")
+    return rot, tr
 
 
 def auc(distances, max_distance=0.1, below=0.02):

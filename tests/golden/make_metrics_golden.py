@@ -13,8 +13,8 @@ try:
 except Exception:                                   # pragma: no cover
     sys.modules["cv2"] = types.ModuleType("cv2")
 sys.path.insert(0, "/root/reference/src")
-from estimation.errors import ADD, ADDS              # noqa: E402
-from estimation.state import State_SE3, points       # noqa: E402
+from estimation.errors import ADD, ADDS, rotation_error, translation_error   # noqa: E402
+from estimation.state import State_R3xQuat, State_SE3, points       # noqa: E402
 from scipy.spatial.transform import Rotation         # noqa: E402
 
 
@@ -36,6 +36,21 @@ def main():
         adds = np.array([ADDS(points(model[f]), State_SE3(p1[f]), State_SE3(p2[f])) for f in range(frames)])
         out.update({f"{name}_model": model, f"{name}_pose1": p1, f"{name}_pose2": p2,
                     f"{name}_add": add, f"{name}_adds": adds})
+    # rotation / translation errors (errors.py:12-51) on State_R3xQuat poses, incl. identical, tiny and ~180 deg cases
+    n = 24
+    quats = rng.normal(size=(n, 4)); quats /= np.linalg.norm(quats, axis=1, keepdims=True)
+    quats2 = rng.normal(size=(n, 4)); quats2 /= np.linalg.norm(quats2, axis=1, keepdims=True)
+    quats2[0] = quats[0]                                                    # identical
+    quats2[1] = quats[1] + 1e-4 * rng.normal(size=4); quats2[1] /= np.linalg.norm(quats2[1])   # tiny angle
+    quats2[2] = np.array([quats[2][3], -quats[2][2], quats[2][1], -quats[2][0]])                # orthogonal quaternion: 180 deg
+    ts, ts2 = rng.normal(size=(n, 3)), rng.normal(size=(n, 3))
+    ts2[0] = ts[0]
+    pa = [State_R3xQuat(list(ts[i]) + list(quats[i])) for i in range(n)]
+    pb = [State_R3xQuat(list(ts2[i]) + list(quats2[i])) for i in range(n)]
+    out["err_pose1"] = np.stack([State_SE3(p).state for p in pa])
+    out["err_pose2"] = np.stack([State_SE3(p).state for p in pb])
+    out["err_rot"] = np.array([rotation_error(pa[i], pb[i]) for i in range(n)])
+    out["err_trans"] = np.array([translation_error(pa[i], pb[i]) for i in range(n)])
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "metrics_add_adds.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, {k: v.shape for k, v in out.items()})

@@ -104,3 +104,13 @@ def test_no_cpu_fallback():
         metrics.auc(torch.zeros(4))
     with pytest.raises(_cabi.Plr2Error):
         metrics.pose_metrics(torch.zeros(4, 3), torch.zeros(1, 12), torch.zeros(1, 12))
+
+
+def test_rotation_translation_errors_match_reference_golden():
+    g = load_golden("metrics_add_adds")
+    rot, tr = metrics.pose_errors(_cuda(g["err_pose1"]), _cuda(g["err_pose2"]))
+    # float32 rotation matrices: entries carry ~6e-8 error, so angles are good to ~3e-4 rad only where the two
+    # rotations coincide (sqrt of the rounding) and to ~1e-6 elsewhere; rtol 1e-3 as everywhere
+    np.testing.assert_allclose(rot.cpu().numpy(), g["err_rot"], rtol=RTOL, atol=5e-4)
+    np.testing.assert_allclose(tr.cpu().numpy(), g["err_trans"], rtol=RTOL, atol=1e-6)
+    assert abs(float(rot[2]) - np.pi) < 1e-3                    # the 180 degree case
