@@ -106,7 +106,7 @@ inline TcWorkspace carve_tc_workspace(const NetLayout &L, void *base, int frames
   auto take = [&](size_t nbytes) { void *r = p ? p + o : nullptr; o += (nbytes + 127) / 128 * 128; return r; };
   const size_t h1all = (size_t)L.heads * L.h1n, h2all = (size_t)L.heads * L.h2n, h3all = (size_t)L.heads * L.h3n;
   W.pf = take(2 * R * 384 * 2); W.pf_plane = (long long)R * 384;
-  W.x5 = take(2 * R * 512 * 2); W.x5_plane = (long long)R * 512;
+  W.x5 = take(R * 512 * 2); W.x5_plane = 0;          // hi plane only: conv6 reads it through the pool (hi-only operand)
   W.pool = (float *)take(((R + 31) / 32) * 2 * 1024 * sizeof(float));
   W.ap = (float *)take(F * 1024 * sizeof(float));
   W.apb = take(2 * F * 1024 * 2); W.apb_plane = (long long)F * 1024;
@@ -114,8 +114,8 @@ inline TcWorkspace carve_tc_workspace(const NetLayout &L, void *base, int frames
     W.hb = (float *)take(F * h1all * sizeof(float));
     W.h1 = take(2 * R * h1all * 2); W.h1_plane = (long long)R * h1all;
     W.h2 = take(2 * R * h2all * 2); W.h2_plane = (long long)R * h2all;
-    W.h3 = (float *)take(R * h3all * sizeof(float));
-    W.out = (float *)take(R * L.ldo * sizeof(float));
+    W.h3 = nullptr; W.out = nullptr;                  // conv3 output and the all-class head outputs are never materialised
+    (void)h3all;
   } else {
     W.hb = (float *)take(F * h1all * sizeof(float));
     W.h3 = (float *)take(F * h2all * sizeof(float));
