@@ -58,8 +58,11 @@ inline NetLayout make_layout(int net, int O) {
 // Workspace (floats) for R = frames*n_points rows.
 struct NetWorkspace {
   float *pf, *x5, *x6, *ap, *hb, *h1, *h2, *h3, *out, *embT, *dpf, *dap, *dhb;
+  float *red;              // training: [BGRAD_SLICES][BGRAD_MAX_COLS] partial column sums of the bias gradients
   size_t floats;
 };
+
+constexpr int BGRAD_SLICES = 64, BGRAD_MAX_COLS = 2048;
 
 inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, int n_points, int training) {
   NetWorkspace W{};
@@ -81,6 +84,7 @@ inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, 
   W.embT = take(R * 32);
   if (training) {
     W.dpf = take(R * 384); W.dap = take(F * 1024); W.dhb = take(pn ? F * h1all : 0);
+    W.red = take((size_t)BGRAD_SLICES * BGRAD_MAX_COLS);
   }
   W.floats = o;
   return W;

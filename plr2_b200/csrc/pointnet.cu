@@ -191,15 +191,26 @@ int scatter_emb_grad(const float *demb, const int64_t *choose, int frames, int N
 // out[seg][c] = scale * sum_{r in segment} X[r][c]   (segments of rows_per_seg consecutive rows).
 // Block: 32 columns x 8 row lanes; fixed summation order (deterministic).
 __global__ void __launch_bounds__(256)
-segment_colsum_kernel(const float *__restrict__ X, long long ld, int rows_per_seg, int ncols, float scale,
+segment_colsum_kernel(const float *__restrict__ X, long long ld, int rows_per_seg, size_t total_rows, int ncols, float scale,
                       float *__restrict__ out, long long ldo) {
   __shared__ float red[8][33];
   const int c = blockIdx.x * 32 + (threadIdx.x & 31);
   const int rl = threadIdx.x >> 5;
   const size_t r0 = (size_t)blockIdx.y * rows_per_seg;
+  const int nr = (int)min((size_t)rows_per_seg, total_rows > r0 ? total_rows - r0 : (size_t)0);   // last segment may be short
   float s = 0.f;
-  if (c < ncols)
-    for (int r = rl; r < rows_per_seg; r += 8) s += X[(r0 + r) * ld + c];
+  if (c < ncols) {
+    // 4 independent partial sums per thread (rows rl, rl+8, rl+16, rl+24, ...): loads in flight instead of a
+    // serial add chain; combined in a fixed order
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int r = rl;
+    for (; r + 24 < nr; r += 32) {
+      s0 += X[(r0 + r) * ld + c]; s1 += X[(r0 + r + 8) * ld + c];
+      s2 += X[(r0 + r + 16) * ld + c]; s3 += X[(r0 + r + 24) * ld + c];
+    }
+    for (; r < nr; r += 8) s0 += X[(r0 + r) * ld + c];
+    s = (s0 + s1) + (s2 + s3);
+  }
   red[rl][threadIdx.x & 31] = s;
   __syncthreads();
   if (rl == 0 && c < ncols) {
@@ -214,8 +225,17 @@ int segment_colsum(const float *X, long long ld, int nseg, int rows_per_seg, int
                    long long ldo, cudaStream_t st) {
   if (nseg <= 0 || ncols <= 0) return 0;
   dim3 grid((ncols + 31) / 32, nseg);
-  segment_colsum_kernel<<<grid, 256, 0, st>>>(X, ld, rows_per_seg, ncols, scale, out, ldo);
+  segment_colsum_kernel<<<grid, 256, 0, st>>>(X, ld, rows_per_seg, (size_t)nseg * rows_per_seg, ncols, scale, out, ldo);
   return check_launch("segment_colsum");
+}
+
+// same with a short last segment: segment s covers rows [s*rows_per_seg, min((s+1)*rows_per_seg, total_rows))
+int segment_colsum_ragged(const float *X, long long ld, int nseg, int rows_per_seg, size_t total_rows, int ncols, float *out,
+                          long long ldo, cudaStream_t st) {
+  if (nseg <= 0 || ncols <= 0) return 0;
+  dim3 grid((ncols + 31) / 32, nseg);
+  segment_colsum_kernel<<<grid, 256, 0, st>>>(X, ld, rows_per_seg, total_rows, ncols, 1.0f, out, ldo);
+  return check_launch("segment_colsum_ragged");
 }
 
 // dX[r][c] = (X[r][c] > 0) * dseg[r / rows_per_seg][c] * scale     (in place over X allowed)

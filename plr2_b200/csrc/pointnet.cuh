@@ -15,6 +15,8 @@ int scatter_emb_grad(const float *demb, const int64_t *choose, int frames, int N
                      cudaStream_t st);
 int segment_colsum(const float *X, long long ld, int nseg, int rows_per_seg, int ncols, float scale, float *out,
                    long long ldo, cudaStream_t st);
+int segment_colsum_ragged(const float *X, long long ld, int nseg, int rows_per_seg, size_t total_rows, int ncols, float *out,
+                          long long ldo, cudaStream_t st);
 int segment_bcast_mask(const float *dseg, const float *X, size_t rows, int rows_per_seg, int ncols, float scale,
                        float *dX, cudaStream_t st);
 int select_outputs(const float *raw, const NetLayout &L, const int64_t *obj, int rows_per_frame, size_t rows,

@@ -178,8 +178,16 @@ static int auto_split(int M, int N, int batch, int K) {
   return (int)(s < 1 ? 1 : s);
 }
 static int wgrad(GemmArgs g, cudaStream_t st) { return gemm_f32(g, auto_split(g.M, g.N, g.batch, g.K), st); }
-static int bgrad(const float *dY, long long ld, int rows, int ncols, float *db, cudaStream_t st) {
-  return segment_colsum(dY, ld, 1, rows, ncols, 1.0f, db, ncols, st);
+// db[c] = sum over rows of dY[r][c].  Tall matrices are summed in two fixed-order stages (row slices into `red`,
+// then the slices), so that the first stage fills the GPU instead of running ncols/32 blocks.
+static int bgrad(const float *dY, long long ld, int rows, int ncols, float *db, float *red, cudaStream_t st) {
+  const int per = 256;                                    // rows per slice (a multiple of the kernel's 8 row lanes)
+  int slices = (rows + per - 1) / per;
+  if (red == nullptr || slices < 4 || ncols > BGRAD_MAX_COLS) return segment_colsum(dY, ld, 1, rows, ncols, 1.0f, db, ncols, st);
+  int rows_per = per;
+  if (slices > BGRAD_SLICES) { slices = BGRAD_SLICES; rows_per = ((rows + slices - 1) / slices + 7) / 8 * 8; slices = (rows + rows_per - 1) / rows_per; }
+  RC(segment_colsum_ragged(dY, ld, slices, rows_per, rows, ncols, red, ncols, st));
+  return segment_colsum(red, ncols, 1, slices, ncols, 1.0f, db, ncols, st);
 }
 
 // From W.dap (d loss / d pooled feature) and W.dpf (head contributions to d pf, or undefined when
@@ -190,13 +198,13 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
   // AvgPool1d backward through conv6's ReLU: dx6 = (x6 > 0) * dap[frame] / N     (in place)
   RC(segment_bcast_mask(W.dap, W.x6, (size_t)R, N, 1024, 1.0f / (float)N, W.x6, st));
   RC(wgrad(gemm_tn(W.x6, 1024, W.x5, 512, gp + L.c6w, 512, 1024, 512, R), st));
-  RC(bgrad(W.x6, 1024, R, 1024, gp + L.c6b, st));
+  RC(bgrad(W.x6, 1024, R, 1024, gp + L.c6b, W.red, st));
   GemmArgs g = gemm_nn(W.x6, 1024, pk + L.c6w, 512, W.x5, 512, R, 512, 1024);     // dx5 (in place)
   g.relu_mask = W.x5; g.ldmask = 512;
   RC(gemm_f32(g, 1, st));
   const float *a5 = L.c5k == 256 ? W.pf + 128 : W.pf;
   RC(wgrad(gemm_tn(W.x5, 512, a5, 384, gp + L.c5w, L.c5k, 512, L.c5k, R), st));
-  RC(bgrad(W.x5, 512, R, 512, gp + L.c5b, st));
+  RC(bgrad(W.x5, 512, R, 512, gp + L.c5b, W.red, st));
   const int off2 = L.c5k == 256 ? 0 : 128;    // column of pointfeat_2 inside conv5's input
   if (L.c5k == 384) {                         // refiner: conv5 also reads pointfeat_1
     g = gemm_nn(W.x5, 512, pk + L.c5w, 384, W.dpf, 384, R, 128, 512);
@@ -212,16 +220,16 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
     const int cin = e * 64, cout = 128 + e * 128;
     const size_t wo = e ? L.e2w : L.c2w, bo = e ? L.e2b : L.c2b;
     RC(wgrad(gemm_tn(W.dpf + cout, 384, W.pf + cin, 384, gp + wo, 64, 128, 64, R), st));
-    RC(bgrad(W.dpf + cout, 384, R, 128, gp + bo, st));
+    RC(bgrad(W.dpf + cout, 384, R, 128, gp + bo, W.red, st));
     g = gemm_nn(W.dpf + cout, 384, pk + wo, 64, W.dpf + cin, 384, R, 64, 128);
     g.accumulate = 1; g.relu_mask = W.pf + cin; g.ldmask = 384;
     RC(gemm_f32(g, 1, st));
   }
   // conv1 (3 -> 64) and e_conv1 (32 -> 64)
   RC(wgrad(gemm_tn(W.dpf, 384, x, 3, gp + L.c1w, 4, 64, 3, R), st));
-  RC(bgrad(W.dpf, 384, R, 64, gp + L.c1b, st));
+  RC(bgrad(W.dpf, 384, R, 64, gp + L.c1b, W.red, st));
   RC(wgrad(gemm_tn(W.dpf + 64, 384, W.embT, 32, gp + L.e1w, 32, 64, 32, R), st));
-  RC(bgrad(W.dpf + 64, 384, R, 64, gp + L.e1b, st));
+  RC(bgrad(W.dpf + 64, 384, R, 64, gp + L.e1b, W.red, st));
   return 0;
 }
 
@@ -365,7 +373,7 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   size_t row = 0;
   for (int h = 0; h < 3; ++h) {               // conv4_*
     RC(wgrad(gemm_tn(W.out + L.oc[h], L.ldo, W.h3 + h * 128, 384, gp + L.h4w + row * 128, 128, L.on[h], 128, R), st));
-    RC(bgrad(W.out + L.oc[h], L.ldo, R, L.on[h], gp + L.h4b + row, st));
+    RC(bgrad(W.out + L.oc[h], L.ldo, R, L.on[h], gp + L.h4b + row, W.red, st));
     GemmArgs g = gemm_nn(W.out + L.oc[h], L.ldo, pk + L.h4w + row * 128, 128, W.h3 + h * 128, 384, R, 128, L.on[h]);
     g.relu_mask = W.h3 + h * 128; g.ldmask = 384;
     RC(gemm_f32(g, 1, st));
@@ -375,7 +383,7 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   GemmArgs g = gemm_tn(W.h3, 384, W.h2, 768, gp + L.h3w, 256, 128, 256, R);
   g.batch = 3; g.zA = 128; g.zB = 256; g.zC = 128 * 256;
   RC(wgrad(g, st));
-  RC(bgrad(W.h3, 384, R, 384, gp + L.h3b, st));
+  RC(bgrad(W.h3, 384, R, 384, gp + L.h3b, W.red, st));
   g = gemm_nn(W.h3, 384, pk + L.h3w, 256, W.h2, 768, R, 256, 128);
   g.batch = 3; g.zA = 128; g.zB = 128 * 256; g.zC = 256; g.relu_mask = W.h2; g.ldmask = 768; g.zmask = 256;
   RC(gemm_f32(g, 1, st));
@@ -383,14 +391,14 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   g = gemm_tn(W.h2, 768, W.h1, 1920, gp + L.h2w, 640, 256, 640, R);
   g.batch = 3; g.zA = 256; g.zB = 640; g.zC = 256 * 640;
   RC(wgrad(g, st));
-  RC(bgrad(W.h2, 768, R, 768, gp + L.h2b, st));
+  RC(bgrad(W.h2, 768, R, 768, gp + L.h2b, W.red, st));
   g = gemm_nn(W.h2, 768, pk + L.h2w, 640, W.h1, 1920, R, 640, 256);
   g.batch = 3; g.zA = 256; g.zB = 256 * 640; g.zC = 640; g.relu_mask = W.h1; g.ldmask = 1920; g.zmask = 640;
   RC(gemm_f32(g, 1, st));
   // conv1_*: per-point part, per-frame (pooled) part, bias
   RC(wgrad(gemm_tn(W.h1, 1920, W.pf, 384, gp + L.h1pf, 384, 1920, 384, R), st));
   RC(segment_colsum(W.h1, 1920, F, N, 1920, 1.0f, W.dhb, 1920, st));
-  RC(bgrad(W.dhb, 1920, F, 1920, gp + L.h1b, st));
+  RC(bgrad(W.dhb, 1920, F, 1920, gp + L.h1b, W.red, st));
   RC(gemm_f32(gemm_tn(W.dhb, 1920, W.ap, 1024, gp + L.h1ap, 1024, 1920, 1024, F), 1, st));
   RC(gemm_f32(gemm_nn(W.dhb, 1920, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1920), 1, st));
   RC(gemm_f32(gemm_nn(W.h1, 1920, pk + L.h1pf, 384, W.dpf, 384, R, 384, 1920), 1, st));
@@ -422,7 +430,7 @@ extern "C" int plr2_refiner_backward(const float *packed, const float *x, const 
   size_t row = 0;
   for (int h = 0; h < 2; ++h) {               // conv3_{r,t}
     RC(gemm_f32(gemm_tn(W.out + L.oc[h], L.ldo, W.h2 + h * 128, 256, gp + L.h4w + row * 128, 128, L.on[h], 128, F), 1, st));
-    RC(bgrad(W.out + L.oc[h], L.ldo, F, L.on[h], gp + L.h4b + row, st));
+    RC(bgrad(W.out + L.oc[h], L.ldo, F, L.on[h], gp + L.h4b + row, W.red, st));
     GemmArgs g = gemm_nn(W.out + L.oc[h], L.ldo, pk + L.h4w + row * 128, 128, W.h2 + h * 128, 256, F, 128, L.on[h]);
     g.relu_mask = W.h2 + h * 128; g.ldmask = 256;
     RC(gemm_f32(g, 1, st));
@@ -431,12 +439,12 @@ extern "C" int plr2_refiner_backward(const float *packed, const float *x, const 
   GemmArgs g = gemm_tn(W.h2, 256, W.h1, 1024, gp + L.h2w, 512, 128, 512, F);      // conv2_{r,t}
   g.batch = 2; g.zA = 128; g.zB = 512; g.zC = 128 * 512;
   RC(gemm_f32(g, 1, st));
-  RC(bgrad(W.h2, 256, F, 256, gp + L.h2b, st));
+  RC(bgrad(W.h2, 256, F, 256, gp + L.h2b, W.red, st));
   g = gemm_nn(W.h2, 256, pk + L.h2w, 512, W.h1, 1024, F, 512, 128);
   g.batch = 2; g.zA = 128; g.zB = 128 * 512; g.zC = 512; g.relu_mask = W.h1; g.ldmask = 1024; g.zmask = 512;
   RC(gemm_f32(g, 1, st));
   RC(gemm_f32(gemm_tn(W.h1, 1024, W.ap, 1024, gp + L.h1ap, 1024, 1024, 1024, F), 1, st));   // conv1_{r,t}
-  RC(bgrad(W.h1, 1024, F, 1024, gp + L.h1b, st));
+  RC(bgrad(W.h1, 1024, F, 1024, gp + L.h1b, W.red, st));
   RC(gemm_f32(gemm_nn(W.h1, 1024, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1024), 1, st));
   RC(feat_backward(pk, gp, L, W, x, F, N, false, st));
   return 0;
