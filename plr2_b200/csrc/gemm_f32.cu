@@ -78,11 +78,13 @@ gemm_f32_kernel(GemmArgs g) {
   const int kend = min(g.K, kbeg + g.k_per_split);
   const int tx = tid & 15, ty = tid >> 4;   // 16 x 16 threads, each 8 (m) x 8 (n) as 2x2 groups of 4x4
 
-  float acc[8][8];
+  // accumulators as packed FP32x2 pairs along n: one FFMA2 (a_i broadcast) updates two of them, i.e. half the
+  // issue slots of scalar FFMA for the same FMA-pipe work - each half is an IEEE fma, results are unchanged
+  f32x2 acc2[8][4];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < 4; ++j) acc2[i][j] = pack2(0.f, 0.f);
 
   float ra[4], rb[4];
   load_tile_regs<AMODE>(g.A, g.sam, g.sak, m0, g.M, kbeg, kend, ra, tid);
@@ -105,11 +107,13 @@ gemm_f32_kernel(GemmArgs g) {
       const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[buf][kk][tx * 4]);
       const float4 b1 = *reinterpret_cast<const float4 *>(&Bs[buf][kk][64 + tx * 4]);
       const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-      const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      const f32x2 b2[4] = {pack2(b0.x, b0.y), pack2(b0.z, b0.w), pack2(b1.x, b1.y), pack2(b1.z, b1.w)};
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < 8; ++i) {
+        const f32x2 ai = pack2(a[i], a[i]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < 4; ++j) acc2[i][j] = fma2(ai, b2[j], acc2[i][j]);
+      }
     }
     if (more) {
       store_tile_smem<AMODE>(As[buf ^ 1], ra, tid);
@@ -119,6 +123,11 @@ gemm_f32_kernel(GemmArgs g) {
     }
   }
 
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) unpack2(acc2[i][j], acc[i][2 * j], acc[i][2 * j + 1]);
   const bool split = g.splits > 1;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {

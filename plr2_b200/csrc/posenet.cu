@@ -400,7 +400,13 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   RC(segment_colsum(W.h1, 1920, F, N, 1920, 1.0f, W.dhb, 1920, st));
   RC(bgrad(W.dhb, 1920, F, 1920, gp + L.h1b, W.red, st));
   RC(gemm_f32(gemm_tn(W.dhb, 1920, W.ap, 1024, gp + L.h1ap, 1024, 1920, 1024, F), 1, st));
-  RC(gemm_f32(gemm_nn(W.dhb, 1920, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1920), 1, st));
+  {  // d ap = d hb . W1[:,384:]: M = frames rows only -> split K over CTAs (atomic accumulation onto zeros)
+    cudaError_t e = cudaMemsetAsync(W.dap, 0, (size_t)F * 1024 * sizeof(float), st);
+    if (e != cudaSuccess) { set_error("posenet_backward: memset: %s", cudaGetErrorString(e)); return (int)e; }
+    GemmArgs ga = gemm_nn(W.dhb, 1920, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1920);
+    ga.accumulate = 1;
+    RC(gemm_f32(ga, auto_split(F, 1024, 1, 1920), st));
+  }
   RC(gemm_f32(gemm_nn(W.h1, 1920, pk + L.h1pf, 384, W.dpf, 384, R, 384, 1920), 1, st));
   RC(feat_backward(pk, gp, L, W, x, F, N, true, st));
   if (g_out_img != nullptr) {                 // d emb = d e1 . We1, scattered back to the pixels
