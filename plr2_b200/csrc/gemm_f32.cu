@@ -15,40 +15,58 @@ constexpr int GB_M = 128, GB_N = 128, GB_K = 8, G_THREADS = 256;
 
 enum { LOAD_KVEC = 0, LOAD_MVEC = 1, LOAD_SCALAR = 2 };
 
-// Load a (GB_K x 128) operand tile into smem laid out [k][mn].  `mn0` is the first row/column of
-// the tile, s_mn / s_k the strides of that index in global memory.
+// Loads this thread's 4 elements of a (GB_K x 128) operand tile (smem layout [k][mn]).  `mn0` is the first
+// row/column of the tile, s_mn / s_k the strides of that index in global memory.  The thread's base pointer and
+// row validity are computed once; each k step only advances the pointer (no 64-bit multiplies in the main loop).
 template <int MODE>
-__device__ __forceinline__ void load_tile_regs(const float *__restrict__ P, long long s_mn, long long s_k,
-                                               int mn0, int MN, int k0, int kend, float (&r)[4], int tid) {
-  if (MODE == LOAD_KVEC) {            // k contiguous: one float4 along k for row tid/2
-    const int row = tid >> 1, kq = (tid & 1) * 4;
-    const int mn = mn0 + row, k = k0 + kq;
-    if (mn < MN && k + 3 < kend) {
-      const float4 v = *reinterpret_cast<const float4 *>(P + (long long)mn * s_mn + k);
-      r[0] = v.x; r[1] = v.y; r[2] = v.z; r[3] = v.w;
-    } else {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) r[i] = (mn < MN && k + i < kend) ? P[(long long)mn * s_mn + k + i] : 0.f;
-    }
-  } else if (MODE == LOAD_MVEC) {     // mn contiguous: one float4 along mn for k = tid/32
-    const int kk = tid >> 5, c = (tid & 31) * 4;
-    const int mn = mn0 + c, k = k0 + kk;
-    if (k < kend && mn + 3 < MN) {
-      const float4 v = *reinterpret_cast<const float4 *>(P + (long long)k * s_k + mn);
-      r[0] = v.x; r[1] = v.y; r[2] = v.z; r[3] = v.w;
-    } else {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) r[i] = (k < kend && mn + i < MN) ? P[(long long)k * s_k + mn + i] : 0.f;
-    }
-  } else {                            // arbitrary strides
-    const int kk = tid >> 5, c = (tid & 31) * 4;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int mn = mn0 + c + i, k = k0 + kk;
-      r[i] = (k < kend && mn < MN) ? P[(long long)mn * s_mn + (long long)k * s_k] : 0.f;
+struct TileLoader {
+  const float *p;        // address of this thread's first element for the current k tile
+  long long step;        // pointer advance per k tile
+  long long s_mn, s_k;
+  int kofs;              // this thread's k offset inside a tile
+  int mn, MN;            // first mn index of this thread, bound
+  bool full;             // all 4 mn indices (MVEC/SCALAR) or the row (KVEC) are in range
+
+  __device__ __forceinline__ void init(const float *P, long long s_mn_, long long s_k_, int mn0, int MN_, int kbeg, int tid) {
+    s_mn = s_mn_; s_k = s_k_; MN = MN_;
+    if (MODE == LOAD_KVEC) {          // k contiguous: one float4 along k for row tid/2
+      mn = mn0 + (tid >> 1); kofs = (tid & 1) * 4;
+      full = mn < MN;
+      p = P + (long long)(full ? mn : 0) * s_mn + kbeg + kofs;
+      step = GB_K;
+    } else {                          // MVEC: mn contiguous, one float4 along mn for k = tid/32; SCALAR: any strides
+      mn = mn0 + (tid & 31) * 4; kofs = tid >> 5;
+      full = mn + 3 < MN;
+      p = P + (long long)(kbeg + kofs) * s_k + (long long)(mn < MN ? mn : 0) * s_mn;
+      step = (long long)GB_K * s_k;
     }
   }
-}
+  // k0: first k of the tile being loaded
+  __device__ __forceinline__ void load(int k0, int kend, float (&r)[4]) {
+    const int k = k0 + kofs;
+    if (MODE == LOAD_KVEC) {
+      if (full && k + 3 < kend) {
+        const float4 v = *reinterpret_cast<const float4 *>(p);
+        r[0] = v.x; r[1] = v.y; r[2] = v.z; r[3] = v.w;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) r[i] = (full && k + i < kend) ? p[i] : 0.f;
+      }
+    } else if (MODE == LOAD_MVEC) {
+      if (full && k < kend) {
+        const float4 v = *reinterpret_cast<const float4 *>(p);
+        r[0] = v.x; r[1] = v.y; r[2] = v.z; r[3] = v.w;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) r[i] = (k < kend && mn + i < MN) ? p[i] : 0.f;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) r[i] = (k < kend && mn + i < MN) ? p[(long long)i * s_mn] : 0.f;
+    }
+    p += step;
+  }
+};
 
 template <int MODE>
 __device__ __forceinline__ void store_tile_smem(float (*S)[GB_M + 4], const float (&r)[4], int tid) {
@@ -87,8 +105,12 @@ gemm_f32_kernel(GemmArgs g) {
     for (int j = 0; j < 4; ++j) acc2[i][j] = pack2(0.f, 0.f);
 
   float ra[4], rb[4];
-  load_tile_regs<AMODE>(g.A, g.sam, g.sak, m0, g.M, kbeg, kend, ra, tid);
-  load_tile_regs<BMODE>(g.B, g.sbn, g.sbk, n0, g.N, kbeg, kend, rb, tid);
+  TileLoader<AMODE> la;
+  TileLoader<BMODE> lb;
+  la.init(g.A, g.sam, g.sak, m0, g.M, kbeg, tid);
+  lb.init(g.B, g.sbn, g.sbk, n0, g.N, kbeg, tid);
+  la.load(kbeg, kend, ra);
+  lb.load(kbeg, kend, rb);
   store_tile_smem<AMODE>(As[0], ra, tid);
   store_tile_smem<BMODE>(Bs[0], rb, tid);
   __syncthreads();
@@ -97,8 +119,8 @@ gemm_f32_kernel(GemmArgs g) {
   for (int k0 = kbeg; k0 < kend; k0 += GB_K) {
     const bool more = k0 + GB_K < kend;
     if (more) {
-      load_tile_regs<AMODE>(g.A, g.sam, g.sak, m0, g.M, k0 + GB_K, kend, ra, tid);
-      load_tile_regs<BMODE>(g.B, g.sbn, g.sbk, n0, g.N, k0 + GB_K, kend, rb, tid);
+      la.load(k0 + GB_K, kend, ra);
+      lb.load(k0 + GB_K, kend, rb);
     }
 #pragma unroll
     for (int kk = 0; kk < GB_K; ++kk) {
