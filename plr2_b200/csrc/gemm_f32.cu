@@ -1,12 +1,14 @@
 // FP32 SIMT GEMM with fused epilogues: the exact-precision path for every contraction of the
 // PointNet / head MLPs (lib/network.py:53-68,107-121,151-168,193-200) and of their backward
-// (dX = dY.W, dW = dY^T.X).  The large forward layers are served by the tcgen05 TF32 kernel
-// (gemm_tf32.cu); this kernel covers everything else and is the in-GPU reference for it.
+// (dX = dY.W, dW = dY^T.X).  Inference runs the large layers on the tcgen05 split-bf16 kernel
+// (gemm_bf16x2.cu); this kernel serves training (forward and backward), the FP32 precision mode and is the
+// in-GPU reference for the tensor-core path.
 //
 //   C(m,n) (+)= epilogue( sum_k A(m,k) * B(k,n) )        A(m,k)=A[m*sam+k*sak], B(k,n)=B[k*sbk+n*sbn]
 //   epilogue: + bias[n] + frame_bias[m / rows_per_frame][n], ReLU, * (relu_mask(m,n) > 0)
 //
-// 128x128x8 block tile, 256 threads, 8x8 register micro-tile, double-buffered shared memory.
+// 128x128x8 block tile, 256 threads, 8x8 register micro-tile held as packed FP32x2 pairs (FFMA2), register-staged
+// double-buffered shared memory.
 #include "gemm.cuh"
 
 namespace plr2 {
