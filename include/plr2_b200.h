@@ -277,6 +277,15 @@ int plr2_posenet_backward(const float *packed, const int64_t *choose, const floa
                           const float *g_pred_c, float *packed_grad, float *g_out_img, int precision,
                           void *stream);
 
+/* Overlap of the gradient all-reduce with the backward pass ("bucketed so head-layer buckets overlap the
+ * feature-layer backward"). plr2_net_grad_regions gives the packed-gradient range [early_begin, early_end) (floats)
+ * holding the head-layer weights - 83 % of PoseNet's 16 MB - which plr2_posenet_backward completes first.
+ * plr2_set_backward_stage_event arms a cudaEvent_t (one-shot, per calling thread) that the NEXT
+ * plr2_posenet_backward records on its stream once that range is final; a side stream that waits on it can
+ * all-reduce the range while the trunk backward still runs (plr2_b200/ops.py: PoseNetFn.backward). */
+int plr2_set_backward_stage_event(void *cuda_event);
+int plr2_net_grad_regions(int net, int num_obj, size_t *early_begin, size_t *early_end);
+
 /* PoseRefineNet.forward (lib/network.py:187-206): x [F][N][3], emb [F][32][N], obj [F]
  *   -> pred_r [F][4], pred_t [F][3]
  * training: 0 inference, 1 training (activations kept for plr2_refiner_backward), or

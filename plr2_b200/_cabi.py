@@ -25,6 +25,8 @@ SIGNATURES = {
     "plr2_pose_loss_bwd": (_i, [_vp] * 7 + [_i, _i, _f] + [_vp] * 4),
     "plr2_pose_select": (_i, [_vp] * 6 + [_i] * 3 + [_vp] * 6),
     "plr2_pose_compose": (_i, [_vp, _vp, _i, _vp]),
+    "plr2_set_backward_stage_event": (_i, [_vp]),
+    "plr2_net_grad_regions": (_i, [_i, _i, C.POINTER(_sz), C.POINTER(_sz)]),
     "plr2_pose_metric_workspace_bytes": (_sz, [_i]),
     "plr2_pose_metric": (_i, [_vp, C.c_longlong, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "plr2_mask_bbox": (_i, [_vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),

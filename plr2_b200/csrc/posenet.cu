@@ -237,6 +237,24 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
 
 using namespace plr2;
 
+static thread_local cudaEvent_t g_stage_event = nullptr;
+
+extern "C" int plr2_set_backward_stage_event(void *event) {
+  g_stage_event = (cudaEvent_t)event;
+  return 0;
+}
+
+extern "C" int plr2_net_grad_regions(int net, int num_obj, size_t *early_begin, size_t *early_end) {
+  if (!early_begin || !early_end || num_obj <= 0 || (net != PLR2_NET_POSENET && net != PLR2_NET_REFINER)) {
+    set_error("plr2_net_grad_regions: bad arguments");
+    return PLR2_E_SHAPE;
+  }
+  const NetLayout L = make_layout(net, num_obj);
+  *early_begin = L.h1pf;      // head weights: conv1_*..conv4_* (PoseNet), conv1_*..conv3_* (refiner)
+  *early_end = L.c1b;         // biases of all layers follow the weights
+  return 0;
+}
+
 extern "C" size_t plr2_net_packed_floats(int net, int num_obj) { return 2 * make_layout(net, num_obj).total; }
 
 extern "C" size_t plr2_net_workspace_bytes(int net, int frames, int n_points, int num_obj, int training) {
@@ -408,6 +426,13 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
     RC(gemm_f32(ga, auto_split(F, 1024, 1, 1920), st));
   }
   RC(gemm_f32(gemm_nn(W.h1, 1920, pk + L.h1pf, 384, W.dpf, 384, R, 384, 1920), 1, st));
+  // every head-weight gradient (packed region [h1pf, c1b)) is final here: a caller that overlaps its gradient
+  // all-reduce with the trunk backward waits on this event (plr2_set_backward_stage_event, one-shot)
+  if (g_stage_event != nullptr) {
+    cudaError_t e = cudaEventRecord(g_stage_event, st);
+    g_stage_event = nullptr;
+    if (e != cudaSuccess) { set_error("plr2_posenet_backward: stage event: %s", cudaGetErrorString(e)); return (int)e; }
+  }
   RC(feat_backward(pk, gp, L, W, x, F, N, true, st));
   if (g_out_img != nullptr) {                 // d emb = d e1 . We1, scattered back to the pixels
     RC(gemm_f32(gemm_nn(W.dpf + 64, 384, pk + L.e1w, 32, W.embT, 32, R, 32, 64), 1, st));

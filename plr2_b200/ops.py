@@ -257,15 +257,37 @@ class PoseNetFn(torch.autograd.Function):
         g_img = torch.zeros((F, 32, H, Wd), dtype=torch.float32, device=dev) if ctx.needs_input_grad[3] else None
         z = lambda g, shp: _f32c(g) if g is not None else torch.zeros(shp, dtype=torch.float32, device=dev)
         g_r, g_t, g_c = z(g_r, (F, N, 4)), z(g_t, (F, N, 3)), z(g_c, (F, N, 1))
+        sync = getattr(state, "grad_sync", None)
+        sync = sync if (sync is not None and sync.active()) else None
         with torch.cuda.device(dev):
+            if sync is not None:
+                _cabi.check(_cabi.lib().plr2_set_backward_stage_event(sync.arm(dev)), "plr2_set_backward_stage_event")
             rc = _cabi.lib().plr2_posenet_backward(
                 _cabi.ptr(packed), _cabi.ptr(ch), _cabi.ptr(xs), _cabi.ptr(ob), F, N, H * Wd, state.num_obj,
                 _cabi.ptr(ws), nbytes, _cabi.ptr(g_r), _cabi.ptr(g_t), _cabi.ptr(g_c), _cabi.ptr(gp),
                 _cabi.ptr(g_img), ctx.precision, _cabi.stream_ptr(dev))
         _cabi.check(rc, "plr2_posenet_backward")
+        if sync is not None:
+            # gradient all-reduce inside the op: the head weights (most of the bytes) go out on a side stream as soon
+            # as they are final, while the trunk backward launched above is still running on this stream
+            sync.reduce(gp, *grad_regions(NET_POSENET, state.num_obj))
         grads = _unpack_grads(NET_POSENET, state.num_obj, gp, ctx.params, dev)
         ctx.saved = None
         return (None, None, None, g_img, None, None, None) + tuple(grads)
+
+
+_REGIONS = {}
+
+
+def grad_regions(net, num_obj):
+    """(begin, end) in floats of the packed-gradient range that the backward completes first (head weights)."""
+    key = (net, num_obj)
+    if key not in _REGIONS:
+        import ctypes as C
+        a, b = C.c_size_t(0), C.c_size_t(0)
+        _cabi.check(_cabi.lib().plr2_net_grad_regions(net, num_obj, C.byref(a), C.byref(b)), "plr2_net_grad_regions")
+        _REGIONS[key] = (int(a.value), int(b.value))
+    return _REGIONS[key]
 
 
 REFINER_NEXT_ITER = 2      # PLR2_REFINER_NEXT_ITER (include/plr2_b200.h)

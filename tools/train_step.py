@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--knn", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--overlap", type=int, default=0,
+                    help="1: gradient all-reduce inside the backward op, head weights overlapped with the trunk backward")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -46,6 +48,7 @@ def main():
     crit = Loss(shp.num_mesh, list(shp.sym_list), ops.KNN_FAST if args.knn == "fast" else ops.KNN_EXACT)
     params = net.hot_path_parameters()
     bucket = parallel.GradBucket(params)
+    in_op = parallel.InOpGradSync(average=True).attach(net) if (args.overlap and world > 1) else None
     opt = torch.optim.Adam(params, lr=1e-4)
     frs = [synth.make_frame(shp, 5000 + 131 * rank + i) for i in range(args.frames)]
     st = lambda k: torch.from_numpy(np.stack([f[k] for f in frs])).to(dev)
@@ -60,7 +63,8 @@ def main():
         loss.mean().backward()                       # average over the rank's frames
         if timed:
             ar_ev[0].record()
-        bucket.all_reduce(average=True)              # then over the ranks
+        if in_op is None:
+            bucket.all_reduce(average=True)          # then over the ranks (in_op: already done inside the backward)
         if timed:
             ar_ev[1].record()
         opt.step()
@@ -98,6 +102,7 @@ def main():
             "n_gpus": world, "steps": args.steps, "ms_per_step": ms / args.steps,
             "frames_per_s": world * args.frames * args.steps / (ms / 1e3),
             "allreduce_ms_per_step": ar_ms / args.steps, "grad_bucket_mb": bucket.numel * 4 / 1e6,
+            "allreduce": "inside the backward op, head weights overlapped with the trunk backward" if in_op else "one flat bucket after the backward",
             "replicas_consistent": consistent, "loss_finite": bool(torch.isfinite(loss).all()),
             "sym_frames_rank0": int(sum(int(f["idx"]) in shp.sym_list for f in frs)),
         }), flush=True)
