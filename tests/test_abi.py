@@ -61,3 +61,17 @@ def test_cpu_tensors_are_rejected():
     from plr2_b200.lib.knn import knn_indices
     with pytest.raises(_cabi.Plr2Error):
         knn_indices(torch.zeros(1, 3, 4), torch.zeros(1, 3, 5))
+
+
+def test_grad_regions_describe_the_head_weights(lib):
+    """plr2_net_grad_regions (no GPU needed): the early range is inside the packed gradient, starts after the trunk
+    weights and covers most of PoseNet's parameters (what the overlapped all-reduce sends first)."""
+    import ctypes as C
+    for net, num_obj in ((0, 21), (1, 21), (0, 13)):
+        a, b = C.c_size_t(0), C.c_size_t(0)
+        assert lib.plr2_net_grad_regions(net, num_obj, C.byref(a), C.byref(b)) == 0
+        total = lib.plr2_net_packed_floats(net, num_obj) // 2
+        assert 0 < a.value < b.value <= total
+        if net == 0:
+            assert (b.value - a.value) / total > 0.8
+    assert lib.plr2_net_grad_regions(0, 21, None, None) != 0
