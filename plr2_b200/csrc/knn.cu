@@ -2,138 +2,196 @@
 // (reference lib/knn/src/cuda/knn.cu:36-101,113-176) without the ref_nb x query_nb scratch matrix.
 //
 // dim==3, k==1 (the only shape the losses use, lib/loss.py:43, lib/loss_refiner.py:43):
-//   * references are staged once per CTA in shared memory as SoA (x[], y[], z[]) so that one
-//     LDS.128 broadcast feeds 4 references to every lane;
-//   * each thread keeps KNN_QPT queries in registers and evaluates TWO references per instruction
-//     with the Blackwell packed FP32x2 ops (FADD2/FMUL2/FFMA2): per 2 pairs
+//   * references are staged once per CTA in shared memory as SoA (x[], y[], z[], |r|^2[]; dynamic
+//     smem sized to n_ref, tiles of KNN_TILE_MAX beyond that) so that one LDS.128 broadcast feeds
+//     4 references to every lane;
+//   * each lane keeps up to KNN_QPT queries in registers and evaluates TWO references per
+//     instruction with the Blackwell packed FP32x2 ops (FADD2/FMUL2/FFMA2): per 2 pairs
 //         EXACT: 3 FADD2 + FMUL2 + 2 FFMA2 + 1 FMNMX3      (bit-identical to knn.cu:88-91)
 //         FAST : 3 FFMA2 + 1 FMNMX3 on centred coordinates  (|r|^2 - 2 q.r)
 //   * only the running minimum is tracked in the hot loop; the winning 16-reference chunk is
-//     remembered (strict '<' => earliest chunk) and re-scanned once at the end to recover the
-//     lowest index attaining the minimum (knn.cu:158 semantics), written 1-based (knn.cu:171).
+//     remembered (strict '<' => earliest chunk) and re-read from smem once at the end to recover
+//     the lowest index attaining the minimum (knn.cu:158 semantics), written 1-based (knn.cu:171).
+//
+// Work split (knn3_plan): grid = (nsplit, batch), CTA x owns queries [x*part, (x+1)*part) of its
+// batch element and walks them in rounds of 128 lanes x QPT queries, QPT from {8,4,2,1} by binary
+// decomposition of the per-lane count, so a ragged tail costs its own size and not a full round.
+// Measured on B200 (tools/knn_split_sweep.py): the loop is bound by the dispatch port shared by the
+// FMA and ALU pipes and needs >= 4 resident warps per scheduler to stay there.  ONE wave of long
+// CTAs loses 12 % (the warp scheduler drains warps one after the other, the last ones run alone);
+// several waves of short CTAs (<= 9 queries per lane) keep every scheduler full until the end.
 #include "knn_core.cuh"
 
 namespace plr2 {
 
 constexpr int KNN_THREADS = 128;
-constexpr int KNN_QPT = 4;        // queries per thread
-constexpr int KNN_TILE_R = 2048;  // references staged per shared-memory tile (3-4 x 8 KB)
-constexpr int KNN_QPB = KNN_THREADS * KNN_QPT;
+constexpr int KNN_QPT = 8;          // queries per lane in a full round
+constexpr int KNN_TILE_MAX = 4096;  // references per smem tile (64 KB in FAST mode)
 
 template <bool FAST>
-__global__ void __launch_bounds__(KNN_THREADS)
-knn3_kernel(const float *__restrict__ ref, const float *__restrict__ query,
-            int64_t *__restrict__ idx, float *__restrict__ dist, int n_ref, int n_query) {
-  __shared__ __align__(16) float sx[KNN_TILE_R];
-  __shared__ __align__(16) float sy[KNN_TILE_R];
-  __shared__ __align__(16) float sz[KNN_TILE_R];
-  __shared__ __align__(16) float sw[FAST ? KNN_TILE_R : 4];
-
-  const int b = blockIdx.y;
-  const float *rb = ref + (size_t)b * 3 * n_ref;
-  const float *qb = query + (size_t)b * 3 * n_query;
-  const int tid = threadIdx.x;
-  const int q0 = blockIdx.x * KNN_QPB + tid;
-
-  // centre for FAST mode: the first reference point (any point near the cloud will do)
-  float cx = 0.f, cy = 0.f, cz = 0.f;
-  if (FAST) {
-    cx = __ldg(rb);
-    cy = __ldg(rb + n_ref);
-    cz = __ldg(rb + 2 * n_ref);
+__device__ __forceinline__ void knn3_stage(float *sx, float *sy, float *sz, float *sw,
+                                           const float *__restrict__ rb, int n_ref, int r0, int nt,
+                                           int nt_pad, float cx, float cy, float cz, int tid) {
+  for (int j = tid; j < nt_pad; j += KNN_THREADS) {
+    float x, y, z;
+    if (j < nt) {
+      x = __ldg(rb + r0 + j);
+      y = __ldg(rb + n_ref + r0 + j);
+      z = __ldg(rb + 2 * n_ref + r0 + j);
+      if (FAST) {
+        x -= cx; y -= cy; z -= cz;
+        sw[j] = fmaf(z, z, fmaf(y, y, x * x));
+      }
+    } else {
+      x = y = z = FAST ? 0.f : CUDART_INF_F;
+      if (FAST) sw[j] = CUDART_INF_F;
+    }
+    sx[j] = x; sy[j] = y; sz[j] = z;
   }
+}
 
-  float nqx[KNN_QPT], nqy[KNN_QPT], nqz[KNN_QPT];
-  float best[KNN_QPT];
-  int bchunk[KNN_QPT];
+template <bool FAST, bool PACKED, int QPT>
+__device__ __forceinline__ void knn3_round(float *sx, float *sy, float *sz, float *sw,
+                                           const float *__restrict__ rb, const float *__restrict__ qb,
+                                           int64_t *__restrict__ idx_b, float *__restrict__ dist_b,
+                                           int n_ref, int n_query, int tile_r, bool single, int q0,
+                                           int q_end, float cx, float cy, float cz, int tid) {
+  float nqx[QPT], nqy[QPT], nqz[QPT], best[QPT];
+  int bchunk[QPT];
 #pragma unroll
-  for (int i = 0; i < KNN_QPT; ++i) {
-    int q = q0 + i * KNN_THREADS;
+  for (int i = 0; i < QPT; ++i) {
+    const int q = q0 + i * KNN_THREADS + tid;
     float x = 0.f, y = 0.f, z = 0.f;
-    if (q < n_query) {
+    if (q < q_end) {
       x = __ldg(qb + q);
       y = __ldg(qb + n_query + q);
       z = __ldg(qb + 2 * n_query + q);
     }
     if (FAST) {
-      nqx[i] = -2.0f * (x - cx);
-      nqy[i] = -2.0f * (y - cy);
-      nqz[i] = -2.0f * (z - cz);
+      nqx[i] = -2.0f * (x - cx); nqy[i] = -2.0f * (y - cy); nqz[i] = -2.0f * (z - cz);
     } else {
-      nqx[i] = -x;
-      nqy[i] = -y;
-      nqz[i] = -z;
+      nqx[i] = -x; nqy[i] = -y; nqz[i] = -z;
     }
     best[i] = CUDART_INF_F;
     bchunk[i] = 0;
   }
-
-  for (int r0 = 0; r0 < n_ref; r0 += KNN_TILE_R) {
-    const int nt = min(KNN_TILE_R, n_ref - r0);
-    const int nt_pad = (nt + KNN_CHUNK - 1) / KNN_CHUNK * KNN_CHUNK;
-    __syncthreads();
-    for (int j = tid; j < nt_pad; j += KNN_THREADS) {
-      float x, y, z;
-      if (j < nt) {
-        x = __ldg(rb + r0 + j);
-        y = __ldg(rb + n_ref + r0 + j);
-        z = __ldg(rb + 2 * n_ref + r0 + j);
-        if (FAST) {
-          x -= cx; y -= cy; z -= cz;
-          sw[j] = fmaf(z, z, fmaf(y, y, x * x));
-        }
-      } else {
-        // padding never wins: EXACT -> distance +inf (or NaN, ignored); FAST -> w = +inf
-        x = y = z = FAST ? 0.f : CUDART_INF_F;
-        if (FAST) sw[j] = CUDART_INF_F;
-      }
-      sx[j] = x; sy[j] = y; sz[j] = z;
+  if (single) {
+    nn_scan<FAST, QPT, PACKED>(sx, sy, sz, sw, knn_pad(n_ref), 0, nqx, nqy, nqz, best, bchunk);
+  } else {
+    for (int r0 = 0; r0 < n_ref; r0 += tile_r) {
+      const int nt = min(tile_r, n_ref - r0);
+      __syncthreads();
+      knn3_stage<FAST>(sx, sy, sz, sw, rb, n_ref, r0, nt, knn_pad(nt), cx, cy, cz, tid);
+      __syncthreads();
+      nn_scan<FAST, QPT, PACKED>(sx, sy, sz, sw, knn_pad(nt), r0 / KNN_CHUNK, nqx, nqy, nqz, best, bchunk);
     }
-    __syncthreads();
-
-    nn_scan<FAST, KNN_QPT>(sx, sy, sz, sw, nt_pad, r0 / KNN_CHUNK, nqx, nqy, nqz, best, bchunk);
   }
-
-  // Recover the lowest reference index attaining best[i] by re-scanning the winning chunk from
-  // global/L1 (the smem tile may hold another range by now).  Lanes walk the chunk rotated by
-  // lane id, hence the min over matching indices.
   const int lane = tid & 31;
 #pragma unroll
-  for (int i = 0; i < KNN_QPT; ++i) {
-    const int q = q0 + i * KNN_THREADS;
-    if (q >= n_query) continue;
-    const int base = bchunk[i] * KNN_CHUNK;
-    int win = 0x7fffffff;
-    for (int s = 0; s < KNN_CHUNK; ++s) {
-      const int j = base + ((s + lane) & (KNN_CHUNK - 1));
-      if (j < n_ref) {
-        float rx = __ldg(rb + j), ry = __ldg(rb + n_ref + j), rz = __ldg(rb + 2 * n_ref + j);
-        float rw = 0.f;
-        if (FAST) {
-          rx -= cx; ry -= cy; rz -= cz;
-          rw = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
+  for (int i = 0; i < QPT; ++i) {
+    const int q = q0 + i * KNN_THREADS + tid;
+    if (q >= q_end) continue;
+    int win;
+    if (single) {
+      win = nn_resolve_smem4<FAST>(sx, sy, sz, sw, n_ref, bchunk[i], best[i], nqx[i], nqy[i], nqz[i]);
+    } else {
+      const int base = bchunk[i] * KNN_CHUNK;
+      win = 0x7fffffff;
+      for (int s = 0; s < KNN_CHUNK; ++s) {
+        const int j = base + ((s + lane) & (KNN_CHUNK - 1));
+        if (j < n_ref) {
+          float rx = __ldg(rb + j), ry = __ldg(rb + n_ref + j), rz = __ldg(rb + 2 * n_ref + j);
+          float rw = 0.f;
+          if (FAST) {
+            rx -= cx; ry -= cy; rz -= cz;
+            rw = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
+          }
+          const float d = pair_dist_scalar<FAST>(rx, ry, rz, rw, nqx[i], nqy[i], nqz[i]);
+          if (d == best[i]) win = min(win, j);
         }
-        const float d = pair_dist_scalar<FAST>(rx, ry, rz, rw, nqx[i], nqy[i], nqz[i]);
-        if (d == best[i]) win = min(win, j);
       }
+      if (win == 0x7fffffff) win = 0;
     }
-    // No reference compared '<' +inf (all distances NaN/inf): the reference kernel keeps its
-    // initial index 1 (knn.cu:127-128).
-    if (win == 0x7fffffff) win = 0;
     if (!FAST) {
       // knn.cu:127: max_dist starts as dist[0]; a NaN there makes every later '<' false.
       const float d0 = pair_dist_scalar<false>(__ldg(rb), __ldg(rb + n_ref), __ldg(rb + 2 * n_ref),
                                                0.f, nqx[i], nqy[i], nqz[i]);
       if (d0 != d0) win = 0;
     }
-    idx[(size_t)b * n_query + q] = (int64_t)win + 1;
-    if (dist != nullptr) {
-      // always report the direct-form squared distance on the original coordinates
+    idx_b[q] = (int64_t)win + 1;
+    if (dist_b != nullptr) {
       const float qx = -__ldg(qb + q), qy = -__ldg(qb + n_query + q), qz = -__ldg(qb + 2 * n_query + q);
-      dist[(size_t)b * n_query + q] = pair_dist_scalar<false>(
-          __ldg(rb + win), __ldg(rb + n_ref + win), __ldg(rb + 2 * n_ref + win), 0.f, qx, qy, qz);
+      dist_b[q] = pair_dist_scalar<false>(__ldg(rb + win), __ldg(rb + n_ref + win),
+                                          __ldg(rb + 2 * n_ref + win), 0.f, qx, qy, qz);
     }
   }
+}
+
+template <bool FAST>
+__global__ void __launch_bounds__(KNN_THREADS, 4)
+knn3_kernel(const float *__restrict__ ref, const float *__restrict__ query,
+                     int64_t *__restrict__ idx, float *__restrict__ dist, int n_ref, int n_query,
+                     int part, int tile_r) {
+  extern __shared__ __align__(16) float knn_smem[];
+  float *sx = knn_smem, *sy = sx + tile_r, *sz = sy + tile_r, *sw = sz + tile_r;
+  const int b = blockIdx.y, tid = threadIdx.x;
+  const float *rb = ref + (size_t)b * 3 * n_ref;
+  const float *qb = query + (size_t)b * 3 * n_query;
+  int64_t *idx_b = idx + (size_t)b * n_query;
+  float *dist_b = dist ? dist + (size_t)b * n_query : nullptr;
+  const int q_beg = blockIdx.x * part;
+  const int q_end = min(n_query, q_beg + part);
+  if (q_beg >= q_end) return;
+
+  float cx = 0.f, cy = 0.f, cz = 0.f;
+  if (FAST) { cx = __ldg(rb); cy = __ldg(rb + n_ref); cz = __ldg(rb + 2 * n_ref); }
+  const bool single = n_ref <= tile_r;
+  if (single) {
+    knn3_stage<FAST>(sx, sy, sz, sw, rb, n_ref, 0, n_ref, knn_pad(n_ref), cx, cy, cz, tid);
+    __syncthreads();
+  }
+  constexpr int QMAX = KNN_QPT;
+  int q = q_beg;
+  while (q < q_end) {
+    const int rem = (q_end - q + KNN_THREADS - 1) / KNN_THREADS;  // queries left per lane
+    if (rem >= QMAX) {
+      knn3_round<FAST, true, QMAX>(sx, sy, sz, sw, rb, qb, idx_b, dist_b, n_ref, n_query, tile_r, single, q, q_end, cx, cy, cz, tid);
+      q += QMAX * KNN_THREADS;
+    } else if (QMAX > 4 && rem >= 4) {
+      knn3_round<FAST, true, 4>(sx, sy, sz, sw, rb, qb, idx_b, dist_b, n_ref, n_query, tile_r, single, q, q_end, cx, cy, cz, tid);
+      q += 4 * KNN_THREADS;
+    } else if (rem >= 2) {
+      knn3_round<FAST, true, 2>(sx, sy, sz, sw, rb, qb, idx_b, dist_b, n_ref, n_query, tile_r, single, q, q_end, cx, cy, cz, tid);
+      q += 2 * KNN_THREADS;
+    } else {
+      knn3_round<FAST, true, 1>(sx, sy, sz, sw, rb, qb, idx_b, dist_b, n_ref, n_query, tile_r, single, q, q_end, cx, cy, cz, tid);
+      q += KNN_THREADS;
+    }
+  }
+}
+
+// Host-side plan: split each batch element's queries into equal parts of `per` queries per lane.
+// Cost model (relative units fitted to the sweep): a round of 8/4/2/1 queries per lane costs
+// 8/4.6/2.8/1.9, a CTA costs its rounds + 0.35 (staging, launch), the grid costs
+// ceil(CTAs / resident slots) CTA times.  Parts longer than 9 queries per lane are not considered
+// (see the header: long CTAs drain badly) unless the batch element has fewer queries anyway.
+struct Knn3Plan { int nsplit, part; };
+static Knn3Plan knn3_plan(int batch, int n_query, int slots) {
+  const int lanes_q = (n_query + KNN_THREADS - 1) / KNN_THREADS;
+  Knn3Plan best{1, lanes_q * KNN_THREADS};
+  double best_cost = 1e300;
+  for (int per = 1; per <= 9 && per <= lanes_q; ++per) {
+    const int nsplit = (lanes_q + per - 1) / per;
+    const int per_eff = (lanes_q + nsplit - 1) / nsplit;  // evened out
+    const double round_cost = 8.0 * (per_eff >> 3) + ((per_eff & 4) ? 4.6 : 0.0) +
+                              ((per_eff & 2) ? 2.8 : 0.0) + ((per_eff & 1) ? 1.9 : 0.0);
+    const long long ctas = (long long)nsplit * batch;
+    const long long waves = (ctas + slots - 1) / slots;
+    const double cost = (double)waves * (round_cost + 0.35);
+    if (cost < best_cost - 1e-9) { best_cost = cost; best = {nsplit, per_eff * KNN_THREADS}; }
+  }
+  best.nsplit = (n_query + best.part - 1) / best.part;
+  return best;
 }
 
 // Generic (any dim, k <= 64): one thread per query, stable top-k by strict '<'
@@ -193,11 +251,28 @@ extern "C" int plr2_knn_f32(const float *ref, const float *query, int64_t *idx, 
   if (batch > 65535) { set_error("plr2_knn_f32: batch > 65535"); return PLR2_E_SHAPE; }
   cudaStream_t st = (cudaStream_t)stream;
   if (dim == 3 && k == 1) {
-    dim3 grid((n_query + KNN_QPB - 1) / KNN_QPB, batch);
-    if (mode == PLR2_KNN_FAST)
-      knn3_kernel<true><<<grid, KNN_THREADS, 0, st>>>(ref, query, idx, dist, n_ref, n_query);
-    else
-      knn3_kernel<false><<<grid, KNN_THREADS, 0, st>>>(ref, query, idx, dist, n_ref, n_query);
+    const bool fast = mode == PLR2_KNN_FAST;
+    const int tile_r = min(knn_pad(n_ref), KNN_TILE_MAX);
+    const size_t smem = (size_t)tile_r * sizeof(float) * (fast ? 4 : 3);
+    auto kern = fast ? knn3_kernel<true> : knn3_kernel<false>;
+    static int slots[2] = {0, 0};  // resident CTAs on the device, per mode (smem: n_ref <= 1024)
+    static int sms = 0;
+    if (!sms) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      cudaFuncSetAttribute(knn3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, KNN_TILE_MAX * 16);
+      cudaFuncSetAttribute(knn3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KNN_TILE_MAX * 12);
+    }
+    int per_sm = slots[fast];
+    if (!per_sm || tile_r > 1024) {
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, KNN_THREADS, smem);
+      if (per_sm < 1) per_sm = 1;
+      if (tile_r <= 1024) slots[fast] = per_sm;
+    }
+    const Knn3Plan plan = knn3_plan(batch, n_query, sms * per_sm);
+    dim3 grid(plan.nsplit, batch);
+    kern<<<grid, KNN_THREADS, smem, st>>>(ref, query, idx, dist, n_ref, n_query, plan.part, tile_r);
   } else {
     if (k > KNN_KMAX) { set_error("plr2_knn_f32: k=%d > %d unsupported", k, KNN_KMAX); return PLR2_E_UNSUPPORTED; }
     dim3 grid((n_query + 127) / 128, batch);
