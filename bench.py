@@ -436,7 +436,8 @@ def main():
     ap.add_argument("--frames", type=int, default=512, help="frames per GPU per step (config C4)")
     ap.add_argument("--chunk", type=int, default=512, help="frames per launch chunk, device-resident path")
     ap.add_argument("--host-chunk", type=int, default=64, help="frames per chunk of the host (e2e) path: H2D of chunk i+1 overlaps chunk i")
-    ap.add_argument("--knn", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--knn", default="fast", choices=["exact", "fast"],
+                    help="ranking arithmetic of the 1-NN scan fused into the ADD-S losses (ops.KNN_LOSS_DEFAULT = fast)")
     ap.add_argument("--cpu-frames", type=int, default=8, help="frames of the CPU baseline sample (0 = skip)")
     ap.add_argument("--profile-step", action="store_true",
                     help="run ONE step between cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)")

@@ -306,47 +306,77 @@ __device__ __forceinline__ void stage_targets(const float *__restrict__ tb, int 
   }
 }
 
-// Per-thread ADD-S accumulation over the mesh points j in [j_beg, j_end) (QPT per thread and pass) of
-// one pose: transform, 1-NN over the staged targets, residual to the nearest target.
-constexpr int ADDS_QPT = 4;
+// ADD-S accumulation over the mesh points j in [j_beg, j_end) of one pose: transform, 1-NN over the
+// staged targets, residual to the nearest target.  The slice is walked in rounds of blockDim.x lanes x
+// QPT mesh points, QPT from {8,4,2,1} by binary decomposition of the per-lane count (M = 2300 on 128
+// lanes: 8 + 8 + 2), like kernel (4).  Only the negated queries survive the scan in registers; the mesh
+// point is re-read and re-transformed (same FMAs, same bits) for the residual.
+__device__ __forceinline__ void adds_transform(const Pose &P, const float *__restrict__ mb, int j, float &mx,
+                                               float &my, float &mz, float &px, float &py, float &pz) {
+  mx = __ldg(mb + 3 * j); my = __ldg(mb + 3 * j + 1); mz = __ldg(mb + 3 * j + 2);
+  px = fmaf(P.R[0], mx, fmaf(P.R[1], my, fmaf(P.R[2], mz, P.s[0])));
+  py = fmaf(P.R[3], mx, fmaf(P.R[4], my, fmaf(P.R[5], mz, P.s[1])));
+  pz = fmaf(P.R[6], mx, fmaf(P.R[7], my, fmaf(P.R[8], mz, P.s[2])));
+}
+
 template <bool FAST, bool JAC, int QPT>
+__device__ __forceinline__ void adds_round(const Pose &P, const float *__restrict__ mb,
+                                           const float *__restrict__ tb, int M, int Mp, int j0, int j_end,
+                                           const float *sx, const float *sy, const float *sz,
+                                           const float *sw, float cx, float cy, float cz, Acc &A) {
+  const int stride = blockDim.x;
+  // warps whose mesh points all lie beyond the slice skip the round (warp-uniform)
+  if (j0 + (int)(threadIdx.x & ~31u) >= j_end) return;
+  float nqx[QPT], nqy[QPT], nqz[QPT], best[QPT];
+  int bchunk[QPT];
+#pragma unroll
+  for (int i = 0; i < QPT; ++i) {
+    const int j = j0 + i * stride + threadIdx.x;
+    float mx, my, mz, px, py, pz;
+    adds_transform(P, mb, min(j, j_end - 1), mx, my, mz, px, py, pz);
+    if (FAST) {
+      nqx[i] = -2.f * (px - cx); nqy[i] = -2.f * (py - cy); nqz[i] = -2.f * (pz - cz);
+    } else {
+      nqx[i] = -px; nqy[i] = -py; nqz[i] = -pz;
+    }
+    best[i] = CUDART_INF_F;
+    bchunk[i] = 0;
+  }
+  nn_scan<FAST, QPT>(sx, sy, sz, sw, Mp, 0, nqx, nqy, nqz, best, bchunk);
+#pragma unroll
+  for (int i = 0; i < QPT; ++i) {
+    const int j = j0 + i * stride + threadIdx.x;
+    if (j < j_end) {
+      const int win = nn_resolve_smem4<FAST>(sx, sy, sz, sw, M, bchunk[i], best[i], nqx[i], nqy[i], nqz[i]);
+      float mx, my, mz, px, py, pz;
+      adds_transform(P, mb, j, mx, my, mz, px, py, pz);
+      const float tx = __ldg(tb + 3 * win), ty = __ldg(tb + 3 * win + 1), tz = __ldg(tb + 3 * win + 2);
+      acc_pair<JAC>(A, px, py, pz, tx, ty, tz, mx, my, mz);
+    }
+  }
+}
+
+template <bool FAST, bool JAC>
 __device__ __forceinline__ void adds_accumulate(const Pose &P, const float *__restrict__ mb,
                                                 const float *__restrict__ tb, int M, int Mp, int j_beg, int j_end,
                                                 const float *sx, const float *sy, const float *sz,
                                                 const float *sw, float cx, float cy, float cz, Acc &A) {
-  const int lane = threadIdx.x & 31;
   const int stride = blockDim.x;
-  for (int j0 = j_beg; j0 < j_end; j0 += stride * QPT) {
-    float mx[QPT], my[QPT], mz[QPT], px[QPT], py[QPT], pz[QPT];
-    float nqx[QPT], nqy[QPT], nqz[QPT], best[QPT];
-    int bchunk[QPT];
-#pragma unroll
-    for (int i = 0; i < QPT; ++i) {
-      const int j = j0 + i * stride + threadIdx.x;
-      mx[i] = my[i] = mz[i] = 0.f;
-      if (j < j_end) { mx[i] = __ldg(mb + 3 * j); my[i] = __ldg(mb + 3 * j + 1); mz[i] = __ldg(mb + 3 * j + 2); }
-      px[i] = fmaf(P.R[0], mx[i], fmaf(P.R[1], my[i], fmaf(P.R[2], mz[i], P.s[0])));
-      py[i] = fmaf(P.R[3], mx[i], fmaf(P.R[4], my[i], fmaf(P.R[5], mz[i], P.s[1])));
-      pz[i] = fmaf(P.R[6], mx[i], fmaf(P.R[7], my[i], fmaf(P.R[8], mz[i], P.s[2])));
-      if (FAST) {
-        nqx[i] = -2.f * (px[i] - cx); nqy[i] = -2.f * (py[i] - cy); nqz[i] = -2.f * (pz[i] - cz);
-      } else {
-        nqx[i] = -px[i]; nqy[i] = -py[i]; nqz[i] = -pz[i];
-      }
-      best[i] = CUDART_INF_F;
-      bchunk[i] = 0;
-    }
-    // warps whose queries all lie beyond the slice skip the scan (warp-uniform)
-    if (j0 + (int)(threadIdx.x & ~31u) >= j_end) continue;
-    nn_scan<FAST, QPT>(sx, sy, sz, sw, Mp, 0, nqx, nqy, nqz, best, bchunk);
-#pragma unroll
-    for (int i = 0; i < QPT; ++i) {
-      const int j = j0 + i * stride + threadIdx.x;
-      if (j < j_end) {
-        const int win = nn_resolve_smem<FAST>(sx, sy, sz, sw, M, bchunk[i], best[i], nqx[i], nqy[i], nqz[i], lane);
-        const float tx = __ldg(tb + 3 * win), ty = __ldg(tb + 3 * win + 1), tz = __ldg(tb + 3 * win + 2);
-        acc_pair<JAC>(A, px[i], py[i], pz[i], tx, ty, tz, mx[i], my[i], mz[i]);
-      }
+  int j = j_beg;
+  while (j < j_end) {
+    const int rem = (j_end - j + stride - 1) / stride;   // mesh points left per lane
+    if (rem >= 8) {
+      adds_round<FAST, JAC, 8>(P, mb, tb, M, Mp, j, j_end, sx, sy, sz, sw, cx, cy, cz, A);
+      j += 8 * stride;
+    } else if (rem >= 4) {
+      adds_round<FAST, JAC, 4>(P, mb, tb, M, Mp, j, j_end, sx, sy, sz, sw, cx, cy, cz, A);
+      j += 4 * stride;
+    } else if (rem >= 2) {
+      adds_round<FAST, JAC, 2>(P, mb, tb, M, Mp, j, j_end, sx, sy, sz, sw, cx, cy, cz, A);
+      j += 2 * stride;
+    } else {
+      adds_round<FAST, JAC, 1>(P, mb, tb, M, Mp, j, j_end, sx, sy, sz, sw, cx, cy, cz, A);
+      j += stride;
     }
   }
 }
@@ -354,7 +384,7 @@ __device__ __forceinline__ void adds_accumulate(const Pose &P, const float *__re
 // ADD-S for symmetric frames of Loss (lib/loss.py:39-46): one CTA per (hypothesis n, frame).
 constexpr int ADDS_THREADS = 128;
 template <bool FAST, bool JAC>
-__global__ void __launch_bounds__(ADDS_THREADS)
+__global__ void __launch_bounds__(ADDS_THREADS, 4)
 adds_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
                  const float *__restrict__ target, const float *__restrict__ model,
                  const float *__restrict__ points, const int64_t *__restrict__ obj,
@@ -380,7 +410,7 @@ adds_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pre
   __syncthreads();
   Acc A;
   acc_zero(A);
-  adds_accumulate<FAST, JAC, ADDS_QPT>(P, mb, tb, M, Mp, 0, M, sx, sy, sz, sw, cx, cy, cz, A);
+  adds_accumulate<FAST, JAC>(P, mb, tb, M, Mp, 0, M, sx, sy, sz, sw, cx, cy, cz, A);
   acc_block_reduce<JAC>(A, red);
   if (threadIdx.x == 0) {
     const float invM = 1.0f / (float)M;

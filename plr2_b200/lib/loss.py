@@ -11,7 +11,7 @@ from .. import ops
 
 
 def loss_calculation(pred_r, pred_t, pred_c, target, model_points, idx, points, w, refine, num_point_mesh,
-                     sym_list, knn_mode=ops.KNN_EXACT):
+                     sym_list, knn_mode=ops.KNN_LOSS_DEFAULT):
     F = pred_r.shape[0]
     assert model_points.shape[-2] == num_point_mesh, "model_points does not have num_points_mesh rows"
     lut = ops.sym_lut(sym_list, pred_r.device)
@@ -26,7 +26,7 @@ def loss_calculation(pred_r, pred_t, pred_c, target, model_points, idx, points, 
 
 class Loss(_Loss):
 
-    def __init__(self, num_points_mesh, sym_list, knn_mode=ops.KNN_EXACT):
+    def __init__(self, num_points_mesh, sym_list, knn_mode=ops.KNN_LOSS_DEFAULT):
         super(Loss, self).__init__(True)
         self.num_pt_mesh = num_points_mesh
         self.sym_list = sym_list

@@ -8,7 +8,7 @@ from .. import ops
 
 
 def loss_calculation(pred_r, pred_t, target, model_points, idx, points, num_point_mesh, sym_list,
-                     knn_mode=ops.KNN_EXACT):
+                     knn_mode=ops.KNN_LOSS_DEFAULT):
     F = target.shape[0] if target.dim() == 3 else 1
     lut = ops.sym_lut(sym_list, pred_r.device)
     dis, new_points, new_target, pose = ops.RefineLossFn.apply(
@@ -20,7 +20,7 @@ def loss_calculation(pred_r, pred_t, target, model_points, idx, points, num_poin
 
 class Loss_refine(_Loss):
 
-    def __init__(self, num_points_mesh, sym_list, knn_mode=ops.KNN_EXACT):
+    def __init__(self, num_points_mesh, sym_list, knn_mode=ops.KNN_LOSS_DEFAULT):
         super(Loss_refine, self).__init__(True)
         self.num_pt_mesh = num_points_mesh
         self.sym_list = sym_list

@@ -6,6 +6,13 @@ from . import _cabi
 
 KNN_EXACT = 0
 KNN_FAST = 1
+# Ranking arithmetic of the 1-NN scan FUSED into the loss kernels.  There the queries are points this
+# library transformed itself (fused FMAs; the reference builds them with bmm + add, lib/loss.py:37), so
+# bit-identity with knn.cu's distance arithmetic cannot carry over to the indices anyway: both modes pick
+# the reference's neighbour wherever best and second best differ by more than ~1e-6, and the index never
+# leaves the kernel.  FAST (3 FFMA2 per 2 pairs instead of 6 packed ops) is therefore the default for the
+# losses; the stand-alone KNearestNeighbor, whose indices ARE the result, stays on EXACT.
+KNN_LOSS_DEFAULT = KNN_FAST
 
 _sym_luts = {}
 

@@ -25,7 +25,7 @@ INPUT_KEYS = ("out_img", "points", "choose", "obj", "target", "model_points")
 
 class DenseFusionPipeline:
     def __init__(self, num_points, num_obj, num_mesh, sym_list, device="cuda", precision=ops.PREC_BF16X2,
-                 knn_mode=ops.KNN_EXACT, refine_iters=2, chunk_frames=512, w=0.015, refine_start=True,
+                 knn_mode=ops.KNN_LOSS_DEFAULT, refine_iters=2, chunk_frames=512, w=0.015, refine_start=True,
                  with_backbone=False, host_chunk_frames=64):
         self.device = torch.device(device)
         self.estimator = PoseNet(num_points, num_obj, precision=precision)

@@ -171,10 +171,17 @@ def test_inference_add_kernel_slice_variants(frames):
         assert_close(dis_i[i].cpu().numpy(), od.numpy(), "dis vs oracle", frac=1.0)
 
 
+@pytest.mark.parametrize("mode", [ops.KNN_EXACT, ops.KNN_FAST])
 @pytest.mark.parametrize("n_mesh", [1, 17, 96, 97, 500, 2600])
-def test_refine_loss_ragged_mesh_sizes(n_mesh):
+def test_refine_loss_ragged_mesh_sizes(n_mesh, mode):
     """Loss_refine splits the mesh over up to 32 CTAs per frame and the references over 3 warp groups:
-    ragged sizes, symmetric and not, against the oracle (dis, re-centred clouds, Jacobians)."""
+    ragged sizes, symmetric and not, against the oracle (dis, re-centred clouds, Jacobians).
+
+    The ADD-S gradient is discontinuous where two targets are equidistant from a mesh point.  FAST
+    ranking may pick the other one when the squared distances differ by less than ~1e-8 (allowed: the
+    parity rule asks for the same index only above a gap of 1e-6); `dis` is unaffected, but one such
+    flip among M points moves the 4-element quaternion gradient by up to ~1/M of its norm.  The FAST
+    runs therefore compare the gradients relative to the gradient's largest entry."""
     shp = synth.Shape(64, 21, n_mesh, 8, 8, tuple(synth.YCB_SYM))
     objs = [12, 3, 20]
     frs = [synth.make_frame(shp, 4000 + n_mesh + i, obj=o, with_image=False) for i, o in enumerate(objs)]
@@ -182,10 +189,11 @@ def test_refine_loss_ragged_mesh_sizes(n_mesh):
     pr = np.stack([f["gt_q"] + 0.05 * rng.standard_normal(4) for f in frs]).astype(np.float32)
     pt = np.stack([f["gt_t"] + 0.005 * rng.standard_normal(3) for f in frs]).astype(np.float32)
     st = lambda key: tt(np.stack([f[key] for f in frs]), "cuda")
-    crit = Loss_refine(shp.num_mesh, list(shp.sym_list))
+    crit = Loss_refine(shp.num_mesh, list(shp.sym_list), mode)
     a, b = tt(pr, "cuda", grad=True), tt(pt, "cuda", grad=True)
     dis, npts, ntgt = crit(a, b, st("target"), st("model_points"), tt(np.array(objs)[:, None], "cuda"), st("points"))
     dis.sum().backward()
+    gtol = (lambda g: None) if mode == ops.KNN_EXACT else (lambda g: 2e-3 * float(np.abs(g).max()))
     for i, f in enumerate(frs):
         oa, ob = tt(pr[i:i + 1], grad=True), tt(pt[i:i + 1], grad=True)
         od, onp, ont, _ = DO.refine_loss(oa, ob, tt(f["target"]), tt(f["model_points"]), objs[i], tt(f["points"]), shp.sym_list)
@@ -193,5 +201,6 @@ def test_refine_loss_ragged_mesh_sizes(n_mesh):
         assert_close(dis[i].detach().cpu().numpy(), od.detach().numpy(), f"dis[{i}]", frac=1.0)
         assert_close(npts[i].cpu().numpy(), onp.numpy(), "new_points")
         assert_close(ntgt[i].cpu().numpy(), ont.numpy(), "new_target")
-        assert_close(a.grad[i].cpu().numpy(), oa.grad[0].numpy(), "g_pred_r", rtol=2e-3, frac=1.0)
-        assert_close(b.grad[i].cpu().numpy(), ob.grad[0].numpy(), "g_pred_t", rtol=2e-3, frac=1.0)
+        gr, gt = oa.grad[0].numpy(), ob.grad[0].numpy()
+        assert_close(a.grad[i].cpu().numpy(), gr, "g_pred_r", rtol=2e-3, atol=gtol(gr), frac=1.0)
+        assert_close(b.grad[i].cpu().numpy(), gt, "g_pred_t", rtol=2e-3, atol=gtol(gt), frac=1.0)

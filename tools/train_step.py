@@ -29,7 +29,7 @@ def main():
     ap.add_argument("--frames", type=int, default=8)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--knn", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--knn", default="fast", choices=["exact", "fast"])
     ap.add_argument("--overlap", type=int, default=0,
                     help="1: gradient all-reduce inside the backward op, head weights overlapped with the trunk backward")
     args = ap.parse_args()
