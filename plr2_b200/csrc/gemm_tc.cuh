@@ -37,4 +37,12 @@ int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int nc
 int split_bf16x2(const float *src, long long ld, long long rows, int cols, __nv_bfloat16 *dst, long long ldd,
                  long long plane, cudaStream_t st);
 
+
+// Training path (gemm_tc_f32.cu): a GemmArgs problem (gemm.cuh) on FP32 operands run on the tcgen05 kernel
+// through split-bf16 scratch planes.  pa / pb: two planes of `elems` bf16 each; ct: `elems` floats.
+struct TcScratch { __nv_bfloat16 *pa = nullptr, *pb = nullptr; float *ct = nullptr; size_t elems = 0; };
+struct GemmArgs;
+bool gemm_tc_eligible(const GemmArgs &g);
+int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st);
+
 }  // namespace plr2

@@ -1,0 +1,138 @@
+// Training-path contractions on the tcgen05 GEMM (gemm_bf16x2.cu).
+//
+// The forward/backward orchestration (posenet.cu) states every Conv1d(k=1)/Linear contraction of
+// lib/network.py:54-63,107-121,152-163,193-200 and of its autograd as a GemmArgs problem on FP32
+// operands in one of three layouts:
+//     forward      Y  = X  W^T        A k-contiguous,  B k-contiguous      (gemm_nt)
+//     input grad   dX = dY W          A k-contiguous,  B n-contiguous      (gemm_nn)
+//     weight grad  dW = dY^T X        A m-contiguous,  B n-contiguous      (gemm_tn, k = points)
+// The tensor-core kernel wants both operands K-major as split-bf16 planes (hi = bf16(v),
+// lo = bf16(v - hi)), K a multiple of 64.  gemm_tc_f32 therefore packs A and B into scratch planes
+// (a straight or a transposing split, zero-padded in K), runs ONE gemm_bf16x2 launch (3 MMAs per
+// MAC, FP32 accumulation, FP32 output through TMA stores) and, where the problem accumulates onto C
+// or passes through a ReLU mask, finishes with an element-wise combine out of a scratch C.
+// The packs cost 8 bytes per operand element of HBM traffic; at the training shapes (8 frames =
+// 8000 rows) every problem is launch/latency bound either way.
+#include "gemm.cuh"
+#include "gemm_tc.cuh"
+
+namespace plr2 {
+
+constexpr int PACK_TILE = 32;
+
+// dst[plane p][r][k] (row pitch ldd) = split(src[r * s_row + k * s_col]) for k < cols, 0 for
+// cols <= k < cols_pad.  TRANS: src is contiguous along r (s_row == 1): 32x32 tiles go through
+// shared memory so that both the reads (along r) and the writes (along k) are coalesced.
+template <bool TRANS>
+__global__ void __launch_bounds__(PACK_TILE * 8)
+pack_split_kernel(const float *__restrict__ src, long long s_row, long long s_col, int rows, int cols,
+                  int cols_pad, __nv_bfloat16 *__restrict__ dst, long long ldd, long long plane) {
+  __shared__ float tile[PACK_TILE][PACK_TILE + 1];
+  const int k0 = blockIdx.x * PACK_TILE, r0 = blockIdx.y * PACK_TILE;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  if (TRANS) {
+#pragma unroll
+    for (int j = 0; j < PACK_TILE / 8; ++j) {
+      const int k = k0 + ty + 8 * j, r = r0 + tx;
+      tile[ty + 8 * j][tx] = (k < cols && r < rows) ? __ldg(src + (long long)r * s_row + (long long)k * s_col) : 0.f;
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int j = 0; j < PACK_TILE / 8; ++j) {
+    const int r = r0 + ty + 8 * j, k = k0 + tx;
+    if (r < rows && k < cols_pad) {
+      float v;
+      if (TRANS) v = tile[tx][ty + 8 * j];
+      else v = k < cols ? __ldg(src + (long long)r * s_row + (long long)k * s_col) : 0.f;
+      const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+      const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+      dst[(long long)r * ldd + k] = hi;
+      dst[plane + (long long)r * ldd + k] = lo;
+    }
+  }
+}
+
+static int pack_split(const float *src, long long s_row, long long s_col, int rows, int cols, int cols_pad,
+                      __nv_bfloat16 *dst, long long ldd, long long plane, cudaStream_t st) {
+  dim3 grid((cols_pad + PACK_TILE - 1) / PACK_TILE, (rows + PACK_TILE - 1) / PACK_TILE), block(PACK_TILE, 8);
+  if (grid.y > 65535) { set_error("pack_split: too many rows (%d)", rows); return PLR2_E_SHAPE; }
+  if (s_row == 1 && s_col != 1)
+    pack_split_kernel<true><<<grid, block, 0, st>>>(src, s_row, s_col, rows, cols, cols_pad, dst, ldd, plane);
+  else
+    pack_split_kernel<false><<<grid, block, 0, st>>>(src, s_row, s_col, rows, cols, cols_pad, dst, ldd, plane);
+  return check_launch("pack_split");
+}
+
+// C = ((accumulate ? C : 0) + Ct) * (mask > 0)      (the epilogue order of gemm_f32_kernel)
+__global__ void __launch_bounds__(256)
+combine_kernel(const float *__restrict__ ct, long long ldct, float *C, long long ldc, const float *mask,
+               long long ldmask, int M, int N, int accumulate) {
+  const long long total = (long long)M * N;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / N;
+    const int n = (int)(i - r * N);
+    float v = ct[r * ldct + n];
+    float *c = C + r * ldc + n;
+    if (accumulate) v += *c;
+    if (mask != nullptr && !(mask[r * ldmask + n] > 0.f)) v = 0.f;   // mask may alias C: same thread, same element
+    *c = v;
+  }
+}
+
+bool gemm_tc_eligible(const GemmArgs &g) {
+  // tiny N (conv1's 3 input channels as a weight-gradient N) and K stay on the SIMT kernel
+  return g.M > 0 && g.N >= 16 && g.K >= 8 && !(g.relu && g.accumulate);
+}
+
+int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
+  const int batch = g.batch < 1 ? 1 : g.batch;
+  const int Kp = (g.K + 63) / 64 * 64;
+  // One launch serves the whole batch when problem z differs by a COLUMN offset of C (the r/t/c heads of
+  // the forward and of the input gradient); stacked weight gradients (z advances whole matrices) are looped.
+  const bool one = batch == 1 || (g.frame_bias == nullptr && g.zC >= g.N && g.zC * (batch - 1) + g.N <= g.ldc && g.N % 16 == 0);
+  if (!one) {
+    for (int z = 0; z < batch; ++z) {
+      GemmArgs gz = g;
+      gz.batch = 1;
+      gz.A += z * g.zA; gz.B += z * g.zB; gz.C += z * g.zC;
+      if (gz.bias) gz.bias += z * g.zbias;
+      if (gz.frame_bias) gz.frame_bias += z * g.zfb;
+      if (gz.relu_mask) gz.relu_mask += z * g.zmask;
+      const int rc = gemm_tc_f32(gz, S, st);
+      if (rc) return rc;
+    }
+    return 0;
+  }
+  const bool need_ct = g.accumulate || g.relu_mask != nullptr;
+  const size_t a_elems = (size_t)g.M * batch * Kp, b_elems = (size_t)g.N * batch * Kp, c_elems = (size_t)g.M * batch * g.N;
+  if (a_elems > S.elems || b_elems > S.elems || (need_ct && c_elems > S.elems)) return gemm_f32(g, 1, st);
+  int rc;
+  for (int z = 0; z < batch; ++z) {
+    if ((rc = pack_split(g.A + z * g.zA, g.sam, g.sak, g.M, g.K, Kp, S.pa + (size_t)z * Kp, (long long)batch * Kp, (long long)S.elems, st))) return rc;
+    if ((rc = pack_split(g.B + z * g.zB, g.sbn, g.sbk, g.N, g.K, Kp, S.pb + (size_t)z * g.N * Kp, Kp, (long long)S.elems, st))) return rc;
+  }
+  TcGemm t;
+  t.A = S.pa; t.lda = (long long)batch * Kp; t.a_plane = (long long)S.elems;
+  t.W = S.pb; t.ldw = Kp; t.w_plane = (long long)S.elems;
+  t.M = g.M; t.N = g.N; t.K = Kp; t.batch = batch;
+  t.a_col_z = Kp; t.b_row_z = g.N;
+  t.bias = g.bias; t.bias_z = g.zbias;
+  t.frame_bias = g.frame_bias; t.rows_per_frame = g.rows_per_frame; t.ldfb = g.ldfb;
+  t.relu = g.relu; t.out_mode = TC_OUT_F32;
+  if (need_ct) { t.Cf = S.ct; t.ldc = (long long)batch * g.N; t.c_col_z = g.N; }
+  else { t.Cf = g.C; t.ldc = g.ldc; t.c_col_z = g.zC; }
+  if ((rc = gemm_bf16x2(t, st))) return rc;
+  if (need_ct) {
+    for (int z = 0; z < batch; ++z) {
+      const long long total = (long long)g.M * g.N;
+      const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+      combine_kernel<<<blocks, 256, 0, st>>>(S.ct + (size_t)z * g.N, (long long)batch * g.N, g.C + z * g.zC, g.ldc,
+                                            g.relu_mask ? g.relu_mask + z * g.zmask : nullptr, g.ldmask, g.M, g.N, g.accumulate);
+    }
+    if ((rc = check_launch("gemm_tc_f32: combine", batch))) return rc;
+  }
+  return 0;
+}
+
+}  // namespace plr2

@@ -59,6 +59,10 @@ inline NetLayout make_layout(int net, int O) {
 struct NetWorkspace {
   float *pf, *x5, *x6, *ap, *hb, *h1, *h2, *h3, *out, *embT, *dpf, *dap, *dhb;
   float *red;              // training: [BGRAD_SLICES][BGRAD_MAX_COLS] partial column sums of the bias gradients
+  // training: scratch of the tensor-core contractions (gemm_tc_f32.cu): split-bf16 planes of the two operands
+  // (tc_pa, tc_pb: 2 planes x tc_elems bf16 each) and an FP32 output staging area (tc_ct: tc_elems floats)
+  float *tc_pa, *tc_pb, *tc_ct;
+  size_t tc_elems;
   size_t floats;
 };
 
@@ -85,6 +89,11 @@ inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, 
   if (training) {
     W.dpf = take(R * 384); W.dap = take(F * 1024); W.dhb = take(pn ? F * h1all : 0);
     W.red = take((size_t)BGRAD_SLICES * BGRAD_MAX_COLS);
+    // largest operand / output of any contraction: 1920 columns (conv1_{r,t,c}) x rows padded to the K tile,
+    // or the 1920 x 1024 per-frame weight block
+    const size_t rp = (R + 63) / 64 * 64;
+    W.tc_elems = (size_t)1920 * (rp > 1024 ? rp : 1024);
+    W.tc_pa = take(W.tc_elems); W.tc_pb = take(W.tc_elems); W.tc_ct = take(W.tc_elems);   // 2 bf16 planes = tc_elems floats
   }
   W.floats = o;
   return W;

@@ -14,9 +14,25 @@
 
 namespace plr2 {
 
-static int gemm_any(const GemmArgs &g, int precision, cudaStream_t st) {
-  (void)precision;
-  return gemm_f32(g, 1, st);
+// Where a contraction of the FP32-activation path (training, or inference without the bf16 workspace) runs:
+// on the tcgen05 kernel through split-bf16 scratch planes when the caller asked for PLR2_PREC_BF16X2 and the
+// call keeps activations for backward (gemm_tc_f32.cu), else on the FP32 SIMT kernel.
+struct GemmCtx {
+  bool tc = false;
+  TcScratch S;
+};
+static GemmCtx make_ctx(const NetWorkspace &W, int precision, int training, int n_points) {
+  GemmCtx c;
+  c.tc = precision == PLR2_PREC_BF16X2 && training && n_points >= 128 && W.tc_elems > 0 && W.tc_pa != nullptr;
+  c.S.pa = reinterpret_cast<__nv_bfloat16 *>(W.tc_pa);
+  c.S.pb = reinterpret_cast<__nv_bfloat16 *>(W.tc_pb);
+  c.S.ct = W.tc_ct;
+  c.S.elems = W.tc_elems;
+  return c;
+}
+static int gemm_run(const GemmArgs &g, int split_k, const GemmCtx &c, cudaStream_t st) {
+  if (c.tc && gemm_tc_eligible(g)) return gemm_tc_f32(g, c.S, st);
+  return gemm_f32(g, split_k, st);
 }
 
 #define RC(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
@@ -35,22 +51,22 @@ static int check_ws(const NetLayout &L, void *ws, size_t bytes, int frames, int 
 // Shared PointNet feature trunk: first layer, conv2/e_conv2, conv5, conv6, per-frame mean.
 static int feat_forward(const float *pk, const NetLayout &L, const NetWorkspace &W, const float *out_img,
                         const int64_t *choose, const float *emb_in, const float *x, int F, int N, int hw,
-                        float *emb_out, int training, int precision, cudaStream_t st) {
+                        float *emb_out, int training, const GemmCtx &cx, cudaStream_t st) {
   const int R = F * N;
   RC(first_layer(pk, L, out_img, choose, emb_in, x, F, N, hw, W.pf, emb_out, training ? W.embT : nullptr, st));
   GemmArgs g = gemm_nt(W.pf, 384, pk + L.c2w, 64, W.pf + 128, 384, R, 128, 64);   // conv2
   g.bias = pk + L.c2b; g.relu = 1;
-  RC(gemm_any(g, precision, st));
+  RC(gemm_run(g, 1, cx, st));
   g = gemm_nt(W.pf + 64, 384, pk + L.e2w, 64, W.pf + 256, 384, R, 128, 64);       // e_conv2
   g.bias = pk + L.e2b; g.relu = 1;
-  RC(gemm_any(g, precision, st));
+  RC(gemm_run(g, 1, cx, st));
   const float *a5 = L.c5k == 256 ? W.pf + 128 : W.pf;                              // pointfeat_2 | pointfeat_3
   g = gemm_nt(a5, 384, pk + L.c5w, L.c5k, W.x5, 512, R, 512, L.c5k);              // conv5
   g.bias = pk + L.c5b; g.relu = 1;
-  RC(gemm_any(g, precision, st));
+  RC(gemm_run(g, 1, cx, st));
   g = gemm_nt(W.x5, 512, pk + L.c6w, 512, W.x6, 1024, R, 1024, 512);              // conv6
   g.bias = pk + L.c6b; g.relu = 1;
-  RC(gemm_any(g, precision, st));
+  RC(gemm_run(g, 1, cx, st));
   RC(segment_colsum(W.x6, 1024, F, N, 1024, 1.0f / (float)N, W.ap, 1024, st));    // AvgPool1d(num_points)
   return 0;
 }
@@ -177,7 +193,7 @@ static int auto_split(int M, int N, int batch, int K) {
   if (s > smax) s = smax;
   return (int)(s < 1 ? 1 : s);
 }
-static int wgrad(GemmArgs g, cudaStream_t st) { return gemm_f32(g, auto_split(g.M, g.N, g.batch, g.K), st); }
+static int wgrad(GemmArgs g, const GemmCtx &cx, cudaStream_t st) { return gemm_run(g, auto_split(g.M, g.N, g.batch, g.K), cx, st); }
 // db[c] = sum over rows of dY[r][c].  Tall matrices are summed in two fixed-order stages (row slices into `red`,
 // then the slices), so that the first stage fills the GPU instead of running ncols/32 blocks.
 static int bgrad(const float *dY, long long ld, int rows, int ncols, float *db, float *red, cudaStream_t st) {
@@ -193,42 +209,42 @@ static int bgrad(const float *dY, long long ld, int rows, int ncols, float *db, 
 // From W.dap (d loss / d pooled feature) and W.dpf (head contributions to d pf, or undefined when
 // !dpf_has_heads) down to the first layer.  Leaves d e1 in W.dpf[:,64:128] and d emb in W.embT.
 static int feat_backward(const float *pk, float *gp, const NetLayout &L, const NetWorkspace &W, const float *x,
-                         int F, int N, bool dpf_has_heads, cudaStream_t st) {
+                         int F, int N, bool dpf_has_heads, const GemmCtx &cx, cudaStream_t st) {
   const int R = F * N;
   // AvgPool1d backward through conv6's ReLU: dx6 = (x6 > 0) * dap[frame] / N     (in place)
   RC(segment_bcast_mask(W.dap, W.x6, (size_t)R, N, 1024, 1.0f / (float)N, W.x6, st));
-  RC(wgrad(gemm_tn(W.x6, 1024, W.x5, 512, gp + L.c6w, 512, 1024, 512, R), st));
+  RC(wgrad(gemm_tn(W.x6, 1024, W.x5, 512, gp + L.c6w, 512, 1024, 512, R), cx, st));
   RC(bgrad(W.x6, 1024, R, 1024, gp + L.c6b, W.red, st));
   GemmArgs g = gemm_nn(W.x6, 1024, pk + L.c6w, 512, W.x5, 512, R, 512, 1024);     // dx5 (in place)
   g.relu_mask = W.x5; g.ldmask = 512;
-  RC(gemm_f32(g, 1, st));
+  RC(gemm_run(g, 1, cx, st));
   const float *a5 = L.c5k == 256 ? W.pf + 128 : W.pf;
-  RC(wgrad(gemm_tn(W.x5, 512, a5, 384, gp + L.c5w, L.c5k, 512, L.c5k, R), st));
+  RC(wgrad(gemm_tn(W.x5, 512, a5, 384, gp + L.c5w, L.c5k, 512, L.c5k, R), cx, st));
   RC(bgrad(W.x5, 512, R, 512, gp + L.c5b, W.red, st));
   const int off2 = L.c5k == 256 ? 0 : 128;    // column of pointfeat_2 inside conv5's input
   if (L.c5k == 384) {                         // refiner: conv5 also reads pointfeat_1
     g = gemm_nn(W.x5, 512, pk + L.c5w, 384, W.dpf, 384, R, 128, 512);
     g.accumulate = dpf_has_heads ? 1 : 0;
-    RC(gemm_f32(g, 1, st));
+    RC(gemm_run(g, 1, cx, st));
   }
   g = gemm_nn(W.x5, 512, pk + L.c5w + off2, L.c5k, W.dpf + 128, 384, R, 256, 512);  // d pointfeat_2
   g.accumulate = dpf_has_heads ? 1 : 0;
   g.relu_mask = W.pf + 128; g.ldmask = 384;
-  RC(gemm_f32(g, 1, st));
+  RC(gemm_run(g, 1, cx, st));
   // conv2 / e_conv2
   for (int e = 0; e < 2; ++e) {
     const int cin = e * 64, cout = 128 + e * 128;
     const size_t wo = e ? L.e2w : L.c2w, bo = e ? L.e2b : L.c2b;
-    RC(wgrad(gemm_tn(W.dpf + cout, 384, W.pf + cin, 384, gp + wo, 64, 128, 64, R), st));
+    RC(wgrad(gemm_tn(W.dpf + cout, 384, W.pf + cin, 384, gp + wo, 64, 128, 64, R), cx, st));
     RC(bgrad(W.dpf + cout, 384, R, 128, gp + bo, W.red, st));
     g = gemm_nn(W.dpf + cout, 384, pk + wo, 64, W.dpf + cin, 384, R, 64, 128);
     g.accumulate = 1; g.relu_mask = W.pf + cin; g.ldmask = 384;
-    RC(gemm_f32(g, 1, st));
+    RC(gemm_run(g, 1, cx, st));
   }
   // conv1 (3 -> 64) and e_conv1 (32 -> 64)
-  RC(wgrad(gemm_tn(W.dpf, 384, x, 3, gp + L.c1w, 4, 64, 3, R), st));
+  RC(wgrad(gemm_tn(W.dpf, 384, x, 3, gp + L.c1w, 4, 64, 3, R), cx, st));
   RC(bgrad(W.dpf, 384, R, 64, gp + L.c1b, W.red, st));
-  RC(wgrad(gemm_tn(W.dpf + 64, 384, W.embT, 32, gp + L.e1w, 32, 64, 32, R), st));
+  RC(wgrad(gemm_tn(W.dpf + 64, 384, W.embT, 32, gp + L.e1w, 32, 64, 32, R), cx, st));
   RC(bgrad(W.dpf + 64, 384, R, 64, gp + L.e1b, W.red, st));
   return 0;
 }
@@ -297,31 +313,32 @@ extern "C" int plr2_posenet_forward(const float *packed, const float *out_img, c
   }
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));
+  const GemmCtx cx = make_ctx(W, precision, training, n_points);
   const int F = frames, N = n_points, R = F * N;
   const float *pk = packed;
-  RC(feat_forward(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, training, precision, st));
+  RC(feat_forward(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, training, cx, st));
   // per-frame bias of the three conv1 heads: hb[F,1920] = ap W1[:,384:]^T + b1   (FP32 always)
   GemmArgs g = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.hb, 1920, F, 1920, 1024);
   g.bias = pk + L.h1b;
-  RC(gemm_f32(g, 1, st));
+  RC(gemm_run(g, 1, cx, st));
   // conv1_{r,t,c} on the per-point 384 channels, all three heads in one launch
   g = gemm_nt(W.pf, 384, pk + L.h1pf, 384, W.h1, 1920, R, 1920, 384);
   g.frame_bias = W.hb; g.rows_per_frame = N; g.ldfb = 1920; g.relu = 1;
-  RC(gemm_any(g, precision, st));
+  RC(gemm_run(g, 1, cx, st));
   // conv2_* : block diagonal, batch = head
   g = gemm_nt(W.h1, 1920, pk + L.h2w, 640, W.h2, 768, R, 256, 640);
   g.bias = pk + L.h2b; g.relu = 1; g.batch = 3; g.zA = 640; g.zB = 256 * 640; g.zC = 256; g.zbias = 256;
-  RC(gemm_any(g, precision, st));
+  RC(gemm_run(g, 1, cx, st));
   // conv3_*
   g = gemm_nt(W.h2, 768, pk + L.h3w, 256, W.h3, 384, R, 128, 256);
   g.bias = pk + L.h3b; g.relu = 1; g.batch = 3; g.zA = 256; g.zB = 128 * 256; g.zC = 128; g.zbias = 128;
-  RC(gemm_any(g, precision, st));
+  RC(gemm_run(g, 1, cx, st));
   // conv4_* for every class (the class of each frame is selected afterwards)
   size_t row = 0;
   for (int h = 0; h < 3; ++h) {
     g = gemm_nt(W.h3 + h * 128, 384, pk + L.h4w + row * 128, 128, W.out + L.oc[h], L.ldo, R, L.on[h], 128);
     g.bias = pk + L.h4b + row;
-    RC(gemm_f32(g, 1, st));
+    RC(gemm_run(g, 1, cx, st));
     row += L.on[h];
   }
   RC(select_outputs(W.out, L, obj, N, (size_t)R, pred_r, pred_t, pred_c, st));
@@ -347,21 +364,22 @@ extern "C" int plr2_refiner_forward(const float *packed, const float *x, const f
   }
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));
+  const GemmCtx cx = make_ctx(W, precision, training, n_points);
   const int F = frames, N = n_points;
   const float *pk = packed;
-  RC(feat_forward(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, training, precision, st));
+  RC(feat_forward(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, training, cx, st));
   // Linear 1024 -> 512 (x2 heads), 512 -> 128, 128 -> num_obj*{4,3}: M = frames, FP32
   GemmArgs g = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.h1, 1024, F, 1024, 1024);
   g.bias = pk + L.h1b; g.relu = 1;
-  RC(gemm_f32(g, 1, st));
+  RC(gemm_run(g, 1, cx, st));
   g = gemm_nt(W.h1, 1024, pk + L.h2w, 512, W.h2, 256, F, 128, 512);
   g.bias = pk + L.h2b; g.relu = 1; g.batch = 2; g.zA = 512; g.zB = 128 * 512; g.zC = 128; g.zbias = 128;
-  RC(gemm_f32(g, 1, st));
+  RC(gemm_run(g, 1, cx, st));
   size_t row = 0;
   for (int h = 0; h < 2; ++h) {
     g = gemm_nt(W.h2 + h * 128, 256, pk + L.h4w + row * 128, 128, W.out + L.oc[h], L.ldo, F, L.on[h], 128);
     g.bias = pk + L.h4b + row;
-    RC(gemm_f32(g, 1, st));
+    RC(gemm_run(g, 1, cx, st));
     row += L.on[h];
   }
   RC(select_outputs(W.out, L, obj, 1, (size_t)F, pred_r, pred_t, nullptr, st));
@@ -373,7 +391,6 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
                                      void *workspace, size_t workspace_bytes, const float *g_pred_r,
                                      const float *g_pred_t, const float *g_pred_c, float *packed_grad,
                                      float *g_out_img, int precision, void *stream) {
-  (void)precision;   // backward contractions run in FP32 in this version
   if (frames <= 0 || n_points <= 0 || num_obj <= 0) { set_error("plr2_posenet_backward: bad shape"); return PLR2_E_SHAPE; }
   if (!packed || !x || !obj || !g_pred_r || !g_pred_t || !g_pred_c || !packed_grad || (g_out_img && !choose)) {
     set_error("plr2_posenet_backward: null pointer"); return PLR2_E_NULLPTR;
@@ -381,6 +398,7 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   const NetLayout L = make_layout(PLR2_NET_POSENET, num_obj);
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, 1, W));
+  const GemmCtx cx = make_ctx(W, precision, 1, n_points);
   cudaStream_t st = (cudaStream_t)stream;
   const int F = frames, N = n_points, R = F * N;
   const float *pk = packed;
@@ -390,42 +408,42 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   RC(select_outputs_bwd(W.out, L, obj, N, (size_t)R, g_pred_r, g_pred_t, g_pred_c, st));
   size_t row = 0;
   for (int h = 0; h < 3; ++h) {               // conv4_*
-    RC(wgrad(gemm_tn(W.out + L.oc[h], L.ldo, W.h3 + h * 128, 384, gp + L.h4w + row * 128, 128, L.on[h], 128, R), st));
+    RC(wgrad(gemm_tn(W.out + L.oc[h], L.ldo, W.h3 + h * 128, 384, gp + L.h4w + row * 128, 128, L.on[h], 128, R), cx, st));
     RC(bgrad(W.out + L.oc[h], L.ldo, R, L.on[h], gp + L.h4b + row, W.red, st));
     GemmArgs g = gemm_nn(W.out + L.oc[h], L.ldo, pk + L.h4w + row * 128, 128, W.h3 + h * 128, 384, R, 128, L.on[h]);
     g.relu_mask = W.h3 + h * 128; g.ldmask = 384;
-    RC(gemm_f32(g, 1, st));
+    RC(gemm_run(g, 1, cx, st));
     row += L.on[h];
   }
   // conv3_*
   GemmArgs g = gemm_tn(W.h3, 384, W.h2, 768, gp + L.h3w, 256, 128, 256, R);
   g.batch = 3; g.zA = 128; g.zB = 256; g.zC = 128 * 256;
-  RC(wgrad(g, st));
+  RC(wgrad(g, cx, st));
   RC(bgrad(W.h3, 384, R, 384, gp + L.h3b, W.red, st));
   g = gemm_nn(W.h3, 384, pk + L.h3w, 256, W.h2, 768, R, 256, 128);
   g.batch = 3; g.zA = 128; g.zB = 128 * 256; g.zC = 256; g.relu_mask = W.h2; g.ldmask = 768; g.zmask = 256;
-  RC(gemm_f32(g, 1, st));
+  RC(gemm_run(g, 1, cx, st));
   // conv2_*
   g = gemm_tn(W.h2, 768, W.h1, 1920, gp + L.h2w, 640, 256, 640, R);
   g.batch = 3; g.zA = 256; g.zB = 640; g.zC = 256 * 640;
-  RC(wgrad(g, st));
+  RC(wgrad(g, cx, st));
   RC(bgrad(W.h2, 768, R, 768, gp + L.h2b, W.red, st));
   g = gemm_nn(W.h2, 768, pk + L.h2w, 640, W.h1, 1920, R, 640, 256);
   g.batch = 3; g.zA = 256; g.zB = 256 * 640; g.zC = 640; g.relu_mask = W.h1; g.ldmask = 1920; g.zmask = 640;
-  RC(gemm_f32(g, 1, st));
+  RC(gemm_run(g, 1, cx, st));
   // conv1_*: per-point part, per-frame (pooled) part, bias
-  RC(wgrad(gemm_tn(W.h1, 1920, W.pf, 384, gp + L.h1pf, 384, 1920, 384, R), st));
+  RC(wgrad(gemm_tn(W.h1, 1920, W.pf, 384, gp + L.h1pf, 384, 1920, 384, R), cx, st));
   RC(segment_colsum(W.h1, 1920, F, N, 1920, 1.0f, W.dhb, 1920, st));
   RC(bgrad(W.dhb, 1920, F, 1920, gp + L.h1b, W.red, st));
-  RC(gemm_f32(gemm_tn(W.dhb, 1920, W.ap, 1024, gp + L.h1ap, 1024, 1920, 1024, F), 1, st));
+  RC(gemm_run(gemm_tn(W.dhb, 1920, W.ap, 1024, gp + L.h1ap, 1024, 1920, 1024, F), 1, cx, st));
   {  // d ap = d hb . W1[:,384:]: M = frames rows only -> split K over CTAs (atomic accumulation onto zeros)
     cudaError_t e = cudaMemsetAsync(W.dap, 0, (size_t)F * 1024 * sizeof(float), st);
     if (e != cudaSuccess) { set_error("posenet_backward: memset: %s", cudaGetErrorString(e)); return (int)e; }
     GemmArgs ga = gemm_nn(W.dhb, 1920, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1920);
     ga.accumulate = 1;
-    RC(gemm_f32(ga, auto_split(F, 1024, 1, 1920), st));
+    RC(gemm_run(ga, auto_split(F, 1024, 1, 1920), cx, st));
   }
-  RC(gemm_f32(gemm_nn(W.h1, 1920, pk + L.h1pf, 384, W.dpf, 384, R, 384, 1920), 1, st));
+  RC(gemm_run(gemm_nn(W.h1, 1920, pk + L.h1pf, 384, W.dpf, 384, R, 384, 1920), 1, cx, st));
   // every head-weight gradient (packed region [h1pf, c1b)) is final here: a caller that overlaps its gradient
   // all-reduce with the trunk backward waits on this event (plr2_set_backward_stage_event, one-shot)
   if (g_stage_event != nullptr) {
@@ -433,9 +451,9 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
     g_stage_event = nullptr;
     if (e != cudaSuccess) { set_error("plr2_posenet_backward: stage event: %s", cudaGetErrorString(e)); return (int)e; }
   }
-  RC(feat_backward(pk, gp, L, W, x, F, N, true, st));
+  RC(feat_backward(pk, gp, L, W, x, F, N, true, cx, st));
   if (g_out_img != nullptr) {                 // d emb = d e1 . We1, scattered back to the pixels
-    RC(gemm_f32(gemm_nn(W.dpf + 64, 384, pk + L.e1w, 32, W.embT, 32, R, 32, 64), 1, st));
+    RC(gemm_run(gemm_nn(W.dpf + 64, 384, pk + L.e1w, 32, W.embT, 32, R, 32, 64), 1, cx, st));
     RC(scatter_emb_grad(W.embT, choose, F, N, hw, g_out_img, st));
   }
   return 0;
@@ -445,12 +463,13 @@ extern "C" int plr2_refiner_backward(const float *packed, const float *x, const 
                                      int frames, int n_points, int num_obj, void *workspace,
                                      size_t workspace_bytes, const float *g_pred_r, const float *g_pred_t,
                                      float *packed_grad, int precision, void *stream) {
-  (void)precision; (void)emb;
+  (void)emb;
   if (frames <= 0 || n_points <= 0 || num_obj <= 0) { set_error("plr2_refiner_backward: bad shape"); return PLR2_E_SHAPE; }
   if (!packed || !x || !obj || !g_pred_r || !g_pred_t || !packed_grad) { set_error("plr2_refiner_backward: null pointer"); return PLR2_E_NULLPTR; }
   const NetLayout L = make_layout(PLR2_NET_REFINER, num_obj);
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, 1, W));
+  const GemmCtx cx = make_ctx(W, precision, 1, n_points);
   cudaStream_t st = (cudaStream_t)stream;
   const int F = frames, N = n_points;
   const float *pk = packed;
@@ -460,23 +479,23 @@ extern "C" int plr2_refiner_backward(const float *packed, const float *x, const 
   RC(select_outputs_bwd(W.out, L, obj, 1, (size_t)F, g_pred_r, g_pred_t, nullptr, st));
   size_t row = 0;
   for (int h = 0; h < 2; ++h) {               // conv3_{r,t}
-    RC(gemm_f32(gemm_tn(W.out + L.oc[h], L.ldo, W.h2 + h * 128, 256, gp + L.h4w + row * 128, 128, L.on[h], 128, F), 1, st));
+    RC(gemm_run(gemm_tn(W.out + L.oc[h], L.ldo, W.h2 + h * 128, 256, gp + L.h4w + row * 128, 128, L.on[h], 128, F), 1, cx, st));
     RC(bgrad(W.out + L.oc[h], L.ldo, F, L.on[h], gp + L.h4b + row, W.red, st));
     GemmArgs g = gemm_nn(W.out + L.oc[h], L.ldo, pk + L.h4w + row * 128, 128, W.h2 + h * 128, 256, F, 128, L.on[h]);
     g.relu_mask = W.h2 + h * 128; g.ldmask = 256;
-    RC(gemm_f32(g, 1, st));
+    RC(gemm_run(g, 1, cx, st));
     row += L.on[h];
   }
   GemmArgs g = gemm_tn(W.h2, 256, W.h1, 1024, gp + L.h2w, 512, 128, 512, F);      // conv2_{r,t}
   g.batch = 2; g.zA = 128; g.zB = 512; g.zC = 128 * 512;
-  RC(gemm_f32(g, 1, st));
+  RC(gemm_run(g, 1, cx, st));
   RC(bgrad(W.h2, 256, F, 256, gp + L.h2b, W.red, st));
   g = gemm_nn(W.h2, 256, pk + L.h2w, 512, W.h1, 1024, F, 512, 128);
   g.batch = 2; g.zA = 128; g.zB = 128 * 512; g.zC = 512; g.relu_mask = W.h1; g.ldmask = 1024; g.zmask = 512;
-  RC(gemm_f32(g, 1, st));
-  RC(gemm_f32(gemm_tn(W.h1, 1024, W.ap, 1024, gp + L.h1ap, 1024, 1024, 1024, F), 1, st));   // conv1_{r,t}
+  RC(gemm_run(g, 1, cx, st));
+  RC(gemm_run(gemm_tn(W.h1, 1024, W.ap, 1024, gp + L.h1ap, 1024, 1024, 1024, F), 1, cx, st));   // conv1_{r,t}
   RC(bgrad(W.h1, 1024, F, 1024, gp + L.h1b, W.red, st));
-  RC(gemm_f32(gemm_nn(W.h1, 1024, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1024), 1, st));
-  RC(feat_backward(pk, gp, L, W, x, F, N, false, st));
+  RC(gemm_run(gemm_nn(W.h1, 1024, pk + L.h1ap, 1024, W.dap, 1024, F, 1024, 1024), 1, cx, st));
+  RC(feat_backward(pk, gp, L, W, x, F, N, false, cx, st));
   return 0;
 }
