@@ -20,59 +20,66 @@ namespace plr2 {
 
 constexpr int PACK_TILE = 32;
 
-// dst[plane p][r][k] (row pitch ldd) = split(src[r * s_row + k * s_col]) for k < cols, 0 for
-// cols <= k < cols_pad.  TRANS: src is contiguous along r (s_row == 1): 32x32 tiles go through
-// shared memory so that both the reads (along r) and the writes (along k) are coalesced.
+// dst[plane p][z][r][kk] (row pitch ldd, chunk stride dst_z) = split(src[r * s_row + k * s_col]) with
+// k = z * cols_z + kk for k < cols, 0 beyond; z = blockIdx.z walks the K chunks of a split-K problem
+// (one chunk of cols_z = padded K columns otherwise).  TRANS: src is contiguous along r (s_row == 1):
+// 32x32 tiles go through shared memory so that both the reads (along r) and the writes (along k) are
+// coalesced.
 template <bool TRANS>
 __global__ void __launch_bounds__(PACK_TILE * 8)
 pack_split_kernel(const float *__restrict__ src, long long s_row, long long s_col, int rows, int cols,
-                  int cols_pad, __nv_bfloat16 *__restrict__ dst, long long ldd, long long plane) {
+                  int cols_z, __nv_bfloat16 *__restrict__ dst, long long ldd, long long plane, long long dst_z) {
   __shared__ float tile[PACK_TILE][PACK_TILE + 1];
   const int k0 = blockIdx.x * PACK_TILE, r0 = blockIdx.y * PACK_TILE;
+  const int kz = blockIdx.z * cols_z;                 // first source column of this chunk
   const int tx = threadIdx.x, ty = threadIdx.y;
+  dst += blockIdx.z * dst_z;
   if (TRANS) {
 #pragma unroll
     for (int j = 0; j < PACK_TILE / 8; ++j) {
-      const int k = k0 + ty + 8 * j, r = r0 + tx;
-      tile[ty + 8 * j][tx] = (k < cols && r < rows) ? __ldg(src + (long long)r * s_row + (long long)k * s_col) : 0.f;
+      const int kk = k0 + ty + 8 * j, r = r0 + tx;
+      tile[ty + 8 * j][tx] = (kk < cols_z && kz + kk < cols && r < rows)
+                                 ? __ldg(src + (long long)r * s_row + (long long)(kz + kk) * s_col) : 0.f;
     }
     __syncthreads();
   }
 #pragma unroll
   for (int j = 0; j < PACK_TILE / 8; ++j) {
-    const int r = r0 + ty + 8 * j, k = k0 + tx;
-    if (r < rows && k < cols_pad) {
+    const int r = r0 + ty + 8 * j, kk = k0 + tx;
+    if (r < rows && kk < cols_z) {
       float v;
       if (TRANS) v = tile[tx][ty + 8 * j];
-      else v = k < cols ? __ldg(src + (long long)r * s_row + (long long)k * s_col) : 0.f;
+      else v = kz + kk < cols ? __ldg(src + (long long)r * s_row + (long long)(kz + kk) * s_col) : 0.f;
       const __nv_bfloat16 hi = __float2bfloat16_rn(v);
       const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
-      dst[(long long)r * ldd + k] = hi;
-      dst[plane + (long long)r * ldd + k] = lo;
+      dst[(long long)r * ldd + kk] = hi;
+      dst[plane + (long long)r * ldd + kk] = lo;
     }
   }
 }
 
-static int pack_split(const float *src, long long s_row, long long s_col, int rows, int cols, int cols_pad,
-                      __nv_bfloat16 *dst, long long ldd, long long plane, cudaStream_t st) {
-  dim3 grid((cols_pad + PACK_TILE - 1) / PACK_TILE, (rows + PACK_TILE - 1) / PACK_TILE), block(PACK_TILE, 8);
-  if (grid.y > 65535) { set_error("pack_split: too many rows (%d)", rows); return PLR2_E_SHAPE; }
+static int pack_split(const float *src, long long s_row, long long s_col, int rows, int cols, int cols_z, int chunks,
+                      __nv_bfloat16 *dst, long long ldd, long long plane, long long dst_z, cudaStream_t st) {
+  dim3 grid((cols_z + PACK_TILE - 1) / PACK_TILE, (rows + PACK_TILE - 1) / PACK_TILE, chunks), block(PACK_TILE, 8);
+  if (grid.y > 65535 || chunks > 65535) { set_error("pack_split: too many rows (%d)", rows); return PLR2_E_SHAPE; }
   if (s_row == 1 && s_col != 1)
-    pack_split_kernel<true><<<grid, block, 0, st>>>(src, s_row, s_col, rows, cols, cols_pad, dst, ldd, plane);
+    pack_split_kernel<true><<<grid, block, 0, st>>>(src, s_row, s_col, rows, cols, cols_z, dst, ldd, plane, dst_z);
   else
-    pack_split_kernel<false><<<grid, block, 0, st>>>(src, s_row, s_col, rows, cols, cols_pad, dst, ldd, plane);
+    pack_split_kernel<false><<<grid, block, 0, st>>>(src, s_row, s_col, rows, cols, cols_z, dst, ldd, plane, dst_z);
   return check_launch("pack_split");
 }
 
-// C = ((accumulate ? C : 0) + Ct) * (mask > 0)      (the epilogue order of gemm_f32_kernel)
+// C = ((accumulate ? C : 0) + sum_z Ct[:, z*N + n]) * (mask > 0)   (the epilogue order of gemm_f32_kernel;
+// nsum > 1: partial products of a split-K problem, summed in chunk order)
 __global__ void __launch_bounds__(256)
-combine_kernel(const float *__restrict__ ct, long long ldct, float *C, long long ldc, const float *mask,
+combine_kernel(const float *__restrict__ ct, long long ldct, int nsum, float *C, long long ldc, const float *mask,
                long long ldmask, int M, int N, int accumulate) {
   const long long total = (long long)M * N;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const long long r = i / N;
     const int n = (int)(i - r * N);
     float v = ct[r * ldct + n];
+    for (int z = 1; z < nsum; ++z) v += ct[r * ldct + (long long)z * N + n];
     float *c = C + r * ldc + n;
     if (accumulate) v += *c;
     if (mask != nullptr && !(mask[r * ldmask + n] > 0.f)) v = 0.f;   // mask may alias C: same thread, same element
@@ -104,13 +111,46 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     }
     return 0;
   }
+  int rc;
+  // Split-K: a contraction over the points (weight gradients, K = frames * num_points) with a handful of
+  // output tiles would run on a handful of SMs.  Its K chunks become the batch dimension of the launch
+  // (chunk z = columns [z*Ks, +Ks) of the packed A, row block z of the packed B) and the partial products
+  // meet in the combine pass.
+  int splits = 1;
+  if (batch == 1 && !g.relu && g.bias == nullptr && g.frame_bias == nullptr && g.K >= 1024 && g.N % 16 == 0) {
+    const long long tiles = (long long)((g.M + 255) / 256) * ((g.N + 127) / 128);
+    long long want = (74 + tiles - 1) / tiles;
+    if (want > g.K / 512) want = g.K / 512;
+    if (want > 32) want = 32;
+    while (want > 1 && (size_t)g.M * want * g.N > S.elems) --want;
+    splits = (int)(want < 1 ? 1 : want);
+  }
+  if (splits > 1) {
+    const int Ks = ((g.K + splits - 1) / splits + 63) / 64 * 64;
+    splits = (g.K + Ks - 1) / Ks;
+    const size_t kp_all = (size_t)splits * Ks;
+    if ((size_t)g.M * kp_all > S.elems || (size_t)g.N * kp_all > S.elems) return gemm_f32(g, 1, st);
+    if ((rc = pack_split(g.A, g.sam, g.sak, g.M, g.K, (int)kp_all, 1, S.pa, (long long)kp_all, (long long)S.elems, 0, st))) return rc;
+    if ((rc = pack_split(g.B, g.sbn, g.sbk, g.N, g.K, Ks, splits, S.pb, Ks, (long long)S.elems, (long long)g.N * Ks, st))) return rc;
+    TcGemm t;
+    t.A = S.pa; t.lda = (long long)kp_all; t.a_plane = (long long)S.elems;
+    t.W = S.pb; t.ldw = Ks; t.w_plane = (long long)S.elems;
+    t.M = g.M; t.N = g.N; t.K = Ks; t.batch = splits;
+    t.a_col_z = Ks; t.b_row_z = g.N;
+    t.out_mode = TC_OUT_F32; t.Cf = S.ct; t.ldc = (long long)splits * g.N; t.c_col_z = g.N;
+    if ((rc = gemm_bf16x2(t, st))) return rc;
+    const long long total = (long long)g.M * g.N;
+    const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+    combine_kernel<<<blocks, 256, 0, st>>>(S.ct, (long long)splits * g.N, splits, g.C, g.ldc, g.relu_mask, g.ldmask,
+                                          g.M, g.N, g.accumulate);
+    return check_launch("gemm_tc_f32: combine");
+  }
   const bool need_ct = g.accumulate || g.relu_mask != nullptr;
   const size_t a_elems = (size_t)g.M * batch * Kp, b_elems = (size_t)g.N * batch * Kp, c_elems = (size_t)g.M * batch * g.N;
   if (a_elems > S.elems || b_elems > S.elems || (need_ct && c_elems > S.elems)) return gemm_f32(g, 1, st);
-  int rc;
   for (int z = 0; z < batch; ++z) {
-    if ((rc = pack_split(g.A + z * g.zA, g.sam, g.sak, g.M, g.K, Kp, S.pa + (size_t)z * Kp, (long long)batch * Kp, (long long)S.elems, st))) return rc;
-    if ((rc = pack_split(g.B + z * g.zB, g.sbn, g.sbk, g.N, g.K, Kp, S.pb + (size_t)z * g.N * Kp, Kp, (long long)S.elems, st))) return rc;
+    if ((rc = pack_split(g.A + z * g.zA, g.sam, g.sak, g.M, g.K, Kp, 1, S.pa + (size_t)z * Kp, (long long)batch * Kp, (long long)S.elems, 0, st))) return rc;
+    if ((rc = pack_split(g.B + z * g.zB, g.sbn, g.sbk, g.N, g.K, Kp, 1, S.pb + (size_t)z * g.N * Kp, Kp, (long long)S.elems, 0, st))) return rc;
   }
   TcGemm t;
   t.A = S.pa; t.lda = (long long)batch * Kp; t.a_plane = (long long)S.elems;
@@ -127,7 +167,7 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     for (int z = 0; z < batch; ++z) {
       const long long total = (long long)g.M * g.N;
       const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-      combine_kernel<<<blocks, 256, 0, st>>>(S.ct + (size_t)z * g.N, (long long)batch * g.N, g.C + z * g.zC, g.ldc,
+      combine_kernel<<<blocks, 256, 0, st>>>(S.ct + (size_t)z * g.N, (long long)batch * g.N, 1, g.C + z * g.zC, g.ldc,
                                             g.relu_mask ? g.relu_mask + z * g.zmask : nullptr, g.ldmask, g.M, g.N, g.accumulate);
     }
     if ((rc = check_launch("gemm_tc_f32: combine", batch))) return rc;

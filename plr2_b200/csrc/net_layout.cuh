@@ -92,7 +92,7 @@ inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, 
     // largest operand / output of any contraction: 1920 columns (conv1_{r,t,c}) x rows padded to the K tile,
     // or the 1920 x 1024 per-frame weight block
     const size_t rp = (R + 63) / 64 * 64;
-    W.tc_elems = (size_t)1920 * (rp > 1024 ? rp : 1024);
+    W.tc_elems = (size_t)1920 * ((rp > 1024 ? rp : 1024) + 2048);   // + K padding of up to 32 split-K chunks
     W.tc_pa = take(W.tc_elems); W.tc_pb = take(W.tc_elems); W.tc_ct = take(W.tc_elems);   // 2 bf16 planes = tc_elems floats
   }
   W.floats = o;
