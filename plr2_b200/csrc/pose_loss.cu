@@ -547,39 +547,39 @@ pose_select_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
 constexpr int REFINE_RS = 3;                       // reference ranges scanned concurrently per query
 constexpr int REFINE_QT = 96;                      // query threads per range (3 warps)
 constexpr int REFINE_THREADS = REFINE_RS * REFINE_QT;
-constexpr int REFINE_QPT = 1;                      // few pairs in total: maximise warps, not register reuse
-constexpr int REFINE_PASS = REFINE_QT * REFINE_QPT;   // 96 queries per CTA pass
+// Queries per thread: 1 when few frames are in flight (maximise warps: the whole launch is a handful of
+// CTAs per SM), 4 for large batches - with one query per thread the scan issues one LDS.128 per 1.5 FFMA2
+// and sits on the shared-memory pipe (ncu: L1 61 % busy, FMA 26 %), four queries share each load.
+constexpr int REFINE_QPT_MAX = 4;
+constexpr int REFINE_PASS1 = REFINE_QT;            // queries per CTA pass at one query per thread
 constexpr int REFINE_MAX_SPLIT = 32;               // CTAs per frame
 
 // ADD-S accumulation for the refiner: thread (r, qt) scans reference range r for REFINE_QPT queries;
 // the per-range candidates meet in shared memory and range-0 threads finish (lowest range wins ties,
 // so the lowest reference index still wins, knn.cu:158).
-template <bool FAST, bool JAC>
+template <bool FAST, bool JAC, int REFINE_QPT>
 __device__ __forceinline__ void adds_accumulate_split(const Pose &P, const float *__restrict__ mb,
                                                       const float *__restrict__ tb, int M, int Mp, int j_beg,
                                                       int j_end, const float *sx, const float *sy, const float *sz,
                                                       const float *sw, float cx, float cy, float cz,
-                                                      float (*cand_d)[REFINE_PASS], int (*cand_c)[REFINE_PASS], Acc &A) {
+                                                      float (*cand_d)[REFINE_QT * REFINE_QPT], int (*cand_c)[REFINE_QT * REFINE_QPT], Acc &A) {
+  constexpr int REFINE_PASS = REFINE_QT * REFINE_QPT;
   const int lane = threadIdx.x & 31;
   const int r = threadIdx.x / REFINE_QT, qt = threadIdx.x - r * REFINE_QT;
   const int nchunk = Mp / KNN_CHUNK;
   const int c_beg = (int)((long long)nchunk * r / REFINE_RS), c_end = (int)((long long)nchunk * (r + 1) / REFINE_RS);
   for (int j0 = j_beg; j0 < j_end; j0 += REFINE_PASS) {
-    float mx[REFINE_QPT], my[REFINE_QPT], mz[REFINE_QPT], px[REFINE_QPT], py[REFINE_QPT], pz[REFINE_QPT];
     float nqx[REFINE_QPT], nqy[REFINE_QPT], nqz[REFINE_QPT], best[REFINE_QPT];
     int bchunk[REFINE_QPT];
 #pragma unroll
     for (int i = 0; i < REFINE_QPT; ++i) {
       const int j = j0 + i * REFINE_QT + qt;
-      mx[i] = my[i] = mz[i] = 0.f;
-      if (j < j_end) { mx[i] = __ldg(mb + 3 * j); my[i] = __ldg(mb + 3 * j + 1); mz[i] = __ldg(mb + 3 * j + 2); }
-      px[i] = fmaf(P.R[0], mx[i], fmaf(P.R[1], my[i], fmaf(P.R[2], mz[i], P.s[0])));
-      py[i] = fmaf(P.R[3], mx[i], fmaf(P.R[4], my[i], fmaf(P.R[5], mz[i], P.s[1])));
-      pz[i] = fmaf(P.R[6], mx[i], fmaf(P.R[7], my[i], fmaf(P.R[8], mz[i], P.s[2])));
+      float mx, my, mz, px, py, pz;
+      adds_transform(P, mb, min(j, j_end - 1), mx, my, mz, px, py, pz);
       if (FAST) {
-        nqx[i] = -2.f * (px[i] - cx); nqy[i] = -2.f * (py[i] - cy); nqz[i] = -2.f * (pz[i] - cz);
+        nqx[i] = -2.f * (px - cx); nqy[i] = -2.f * (py - cy); nqz[i] = -2.f * (pz - cz);
       } else {
-        nqx[i] = -px[i]; nqy[i] = -py[i]; nqz[i] = -pz[i];
+        nqx[i] = -px; nqy[i] = -py; nqz[i] = -pz;
       }
       best[i] = CUDART_INF_F;
       bchunk[i] = c_beg;
@@ -608,7 +608,9 @@ __device__ __forceinline__ void adds_accumulate_split(const Pose &P, const float
           }
           const int win = nn_resolve_smem<FAST>(sx, sy, sz, sw, M, bc, b, nqx[i], nqy[i], nqz[i], lane);
           const float tx = __ldg(tb + 3 * win), ty = __ldg(tb + 3 * win + 1), tz = __ldg(tb + 3 * win + 2);
-          acc_pair<JAC>(A, px[i], py[i], pz[i], tx, ty, tz, mx[i], my[i], mz[i]);
+          float mx, my, mz, px, py, pz;      // re-read and re-transform (same FMAs, same bits) instead of keeping them live
+          adds_transform(P, mb, j, mx, my, mz, px, py, pz);
+          acc_pair<JAC>(A, px, py, pz, tx, ty, tz, mx, my, mz);
         }
       }
     }
@@ -616,8 +618,8 @@ __device__ __forceinline__ void adds_accumulate_split(const Pose &P, const float
   }
 }
 
-template <bool FAST, bool JAC>
-__global__ void __launch_bounds__(REFINE_THREADS)
+template <bool FAST, bool JAC, int QPT>
+__global__ void __launch_bounds__(REFINE_THREADS, (QPT > 1 || (FAST && JAC)) ? 2 : 3)
 refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ pred_t,
                    const float *__restrict__ target, const float *__restrict__ model,
                    const float *__restrict__ points, const int64_t *__restrict__ obj,
@@ -629,8 +631,8 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
   extern __shared__ __align__(16) float dyn[];
   __shared__ float red[(REFINE_THREADS / 32) * 13];
   __shared__ int s_last;
-  __shared__ float cand_d[REFINE_RS][REFINE_PASS];
-  __shared__ int cand_c[REFINE_RS][REFINE_PASS];
+  __shared__ float cand_d[REFINE_RS][REFINE_QT * QPT];
+  __shared__ int cand_c[REFINE_RS][REFINE_QT * QPT];
   const int S = gridDim.x, s = blockIdx.x;
   const int f = blockIdx.y;
   const float *tb = target + (size_t)f * M * 3;
@@ -648,7 +650,7 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
     if (FAST) { cx = __ldg(tb); cy = __ldg(tb + 1); cz = __ldg(tb + 2); }
     stage_targets<FAST>(tb, M, Mp, sx, sy, sz, sw, cx, cy, cz);
     __syncthreads();
-    adds_accumulate_split<FAST, JAC>(P, mb, tb, M, Mp, j_beg, j_end, sx, sy, sz, sw, cx, cy, cz, cand_d, cand_c, A);
+    adds_accumulate_split<FAST, JAC, QPT>(P, mb, tb, M, Mp, j_beg, j_end, sx, sy, sz, sw, cx, cy, cz, cand_d, cand_c, A);
   } else {
     for (int j = j_beg + threadIdx.x; j < j_end; j += blockDim.x) {
       const float mx = __ldg(mb + 3 * j), my = __ldg(mb + 3 * j + 1), mz = __ldg(mb + 3 * j + 2);
@@ -756,6 +758,14 @@ using namespace plr2;
     kfn<<<GRID, BLOCK, SMEM, ST>>>(__VA_ARGS__);                                                 \
   } while (0)
 
+#define PLR2_LAUNCH_ADDS3(KERNEL, FASTV, JACV, QV, GRID, BLOCK, SMEM, ST, ...)                 \
+  do {                                                                                           \
+    auto kfn = KERNEL<FASTV, JACV, QV>;                                                          \
+    int rc_ = set_dyn_smem((const void *)kfn, SMEM);                                             \
+    if (rc_) return rc_;                                                                         \
+    kfn<<<GRID, BLOCK, SMEM, ST>>>(__VA_ARGS__);                                                 \
+  } while (0)
+
 extern "C" int plr2_pose_loss_fwd(const float *pred_r, const float *pred_t, const float *pred_c,
                                   const float *target, const float *model_points, const float *points,
                                   const int64_t *obj, const uint8_t *sym_lut, int num_obj, int frames,
@@ -831,8 +841,9 @@ extern "C" int plr2_pose_select(const float *pred_r, const float *pred_t, const 
   return check_launch("plr2_pose_select");
 }
 
-static int refine_split(int n_mesh) {
-  int S = (n_mesh + REFINE_PASS - 1) / REFINE_PASS;
+static int refine_split(int n_mesh, int qpt = 1) {
+  const int pass = REFINE_PASS1 * qpt;
+  int S = (n_mesh + pass - 1) / pass;
   return S > REFINE_MAX_SPLIT ? REFINE_MAX_SPLIT : (S < 1 ? 1 : S);
 }
 
@@ -863,7 +874,9 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
   const bool fast = knn_mode == PLR2_KNN_FAST, jac = jac_r != nullptr;
   const bool may_sym = sym_lut != nullptr && obj != nullptr;
   const size_t smem = may_sym ? (size_t)knn_pad(n_mesh) * sizeof(float) * (fast ? 4 : 3) : 0;
-  const int S = refine_split(n_mesh);
+  // four queries per thread once one-query CTAs alone would fill the GPU eight times over
+  const int qpt = (long long)frames * refine_split(n_mesh, 1) >= 8LL * 3 * plr2_device_sm_count() ? REFINE_QPT_MAX : 1;
+  const int S = refine_split(n_mesh, qpt);
   int slice = (n_mesh + S - 1) / S;
   slice = (slice + 31) / 32 * 32;               // warp granularity
   const size_t cnt_bytes = ((size_t)frames * sizeof(unsigned int) + 127) / 128 * 128;
@@ -873,10 +886,16 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
   if (e != cudaSuccess) { set_error("plr2_refine_loss_fwd: memset: %s", cudaGetErrorString(e)); return (int)e; }
   dim3 grid(S, frames);
 #define ARGS pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, slice, counters, partials, dis, new_points, new_target, jac_r, jac_t, pose_out
-  if (fast && jac) PLR2_LAUNCH_ADDS(refine_loss_kernel, true, true, grid, REFINE_THREADS, smem, st, ARGS);
-  else if (fast) PLR2_LAUNCH_ADDS(refine_loss_kernel, true, false, grid, REFINE_THREADS, smem, st, ARGS);
-  else if (jac) PLR2_LAUNCH_ADDS(refine_loss_kernel, false, true, grid, REFINE_THREADS, smem, st, ARGS);
-  else PLR2_LAUNCH_ADDS(refine_loss_kernel, false, false, grid, REFINE_THREADS, smem, st, ARGS);
+#define REFINE_LAUNCH(FASTV, JACV)                                                               \
+  do {                                                                                           \
+    if (qpt == 1) PLR2_LAUNCH_ADDS3(refine_loss_kernel, FASTV, JACV, 1, grid, REFINE_THREADS, smem, st, ARGS);                \
+    else PLR2_LAUNCH_ADDS3(refine_loss_kernel, FASTV, JACV, REFINE_QPT_MAX, grid, REFINE_THREADS, smem, st, ARGS);            \
+  } while (0)
+  if (fast && jac) REFINE_LAUNCH(true, true);
+  else if (fast) REFINE_LAUNCH(true, false);
+  else if (jac) REFINE_LAUNCH(false, true);
+  else REFINE_LAUNCH(false, false);
+#undef REFINE_LAUNCH
 #undef ARGS
   return check_launch("plr2_refine_loss_fwd");
 }
