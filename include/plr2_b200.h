@@ -62,6 +62,11 @@ size_t plr2_knn_workspace_bytes(int batch, int dim, int n_ref, int n_query, int 
 int plr2_knn_f32(const float *ref, const float *query, int64_t *idx, float *dist,
                  int batch, int dim, int n_ref, int n_query, int k, int mode,
                  void *workspace, size_t workspace_bytes, void *stream);
+/* Host-side work split of the dim==3,k==1 kernel (replaces the grid arithmetic of knn_device,
+ * lib/knn/src/cuda/knn.cu:217-263): every batch element's queries are cut into *nsplit equal parts of
+ * *part queries (a multiple of 128), one CTA each, chosen so that batch * nsplit CTAs of at most 9 queries
+ * per lane run in as few full waves of `resident_ctas` as possible.  Pure host arithmetic (no GPU). */
+int plr2_knn_plan(int batch, int n_query, int resident_ctas, int *nsplit, int *part);
 
 /* ---- (3) fused quaternion->R, mesh transform, ADD / ADD-S, confidence-weighted loss -------
  * One call handles `frames` independent frames (the reference only ever has frames==1).

@@ -21,6 +21,7 @@ SIGNATURES = {
     "plr2_profile_executed_flops": (C.c_double, []),
     "plr2_knn_workspace_bytes": (_sz, [_i] * 5),
     "plr2_knn_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "plr2_knn_plan": (_i, [_i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
     "plr2_pose_loss_fwd": (_i, [_vp] * 8 + [_i] * 4 + [_f, _i, _i] + [_vp] * 5),
     "plr2_pose_loss_bwd": (_i, [_vp] * 7 + [_i, _i, _f] + [_vp] * 4),
     "plr2_pose_select": (_i, [_vp] * 6 + [_i] * 3 + [_vp] * 6),

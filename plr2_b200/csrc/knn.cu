@@ -235,6 +235,17 @@ knn_generic_kernel(const float *__restrict__ ref, const float *__restrict__ quer
 
 }  // namespace plr2
 
+extern "C" int plr2_knn_plan(int batch, int n_query, int resident_ctas, int *nsplit, int *part) {
+  if (batch <= 0 || n_query <= 0 || resident_ctas <= 0 || !nsplit || !part) {
+    plr2::set_error("plr2_knn_plan: bad arguments");
+    return PLR2_E_SHAPE;
+  }
+  const plr2::Knn3Plan p = plr2::knn3_plan(batch, n_query, resident_ctas);
+  *nsplit = p.nsplit;
+  *part = p.part;
+  return 0;
+}
+
 extern "C" size_t plr2_knn_workspace_bytes(int, int, int, int, int) { return 0; }
 
 extern "C" int plr2_knn_f32(const float *ref, const float *query, int64_t *idx, float *dist,

@@ -75,3 +75,34 @@ def test_grad_regions_describe_the_head_weights(lib):
         if net == 0:
             assert (b.value - a.value) / total > 0.8
     assert lib.plr2_net_grad_regions(0, 21, None, None) != 0
+
+
+def _knn_plan(lib, batch, n_query, slots):
+    ns, part = ctypes.c_int(0), ctypes.c_int(0)
+    assert lib.plr2_knn_plan(batch, n_query, slots, ctypes.byref(ns), ctypes.byref(part)) == 0
+    return ns.value, part.value
+
+
+@pytest.mark.parametrize("batch,n_query", [(1, 1), (1, 127), (1, 129), (1, 2300), (512, 2300), (8, 500_000),
+                                           (1, 2_300_000), (3, 1025), (65535, 7)])
+def test_knn_plan_covers_every_query_once(lib, batch, n_query):
+    """Host-side split of kernel (4): parts are whole lane rows (multiples of 128 queries), at most 9 queries
+    per lane, they tile [0, n_query) exactly, and no split is empty."""
+    for slots in (1, 148 * 4, 148 * 5):
+        ns, part = _knn_plan(lib, batch, n_query, slots)
+        assert ns >= 1 and part >= 128 and part % 128 == 0
+        assert part // 128 <= 9
+        assert (ns - 1) * part < n_query <= ns * part
+
+
+def test_knn_plan_prefers_full_waves(lib):
+    """C2 x 8 (500 000 queries, 8 frames) on 592 resident CTAs: one 8-query round per CTA; 512 frames of
+    2300 queries: 9 queries per lane (8 + 1) in two parts, not three rounds of 6."""
+    ns, part = _knn_plan(lib, 8, 500_000, 592)
+    assert part == 8 * 128 and ns == 489
+    ns, part = _knn_plan(lib, 512, 2300, 592)
+    assert (ns, part) == (2, 9 * 128)
+    # a single small frame is spread over the SMs: one query per lane
+    ns, part = _knn_plan(lib, 1, 2300, 592)
+    assert (ns, part) == (18, 128)
+    assert lib.plr2_knn_plan(0, 10, 10, None, None) != 0
