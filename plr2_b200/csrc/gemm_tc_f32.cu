@@ -8,7 +8,7 @@
 //     weight grad  dW = dY^T X        A m-contiguous,  B n-contiguous      (gemm_tn, k = points)
 // The tensor-core kernel wants both operands K-major as split-bf16 planes (hi = bf16(v),
 // lo = bf16(v - hi)), K a multiple of 64.  gemm_tc_f32 therefore packs A and B into scratch planes
-// (a straight or a transposing split, zero-padded in K), runs ONE gemm_bf16x2 launch (3 MMAs per
+// (a straight or a transposing split, zero-padded in K; both operands in one launch), runs ONE gemm_bf16x2 launch (3 MMAs per
 // MAC, FP32 accumulation, FP32 output through TMA stores) and, where the problem accumulates onto C
 // or passes through a ReLU mask, finishes with an element-wise combine out of a scratch C.
 // The packs cost 8 bytes per operand element of HBM traffic; at the training shapes (8 frames =
@@ -20,52 +20,108 @@ namespace plr2 {
 
 constexpr int PACK_TILE = 32;
 
-// dst[plane p][z][r][kk] (row pitch ldd, chunk stride dst_z) = split(src[r * s_row + k * s_col]) with
-// k = z * cols_z + kk for k < cols, 0 beyond; z = blockIdx.z walks the K chunks of a split-K problem
-// (one chunk of cols_z = padded K columns otherwise).  TRANS: src is contiguous along r (s_row == 1):
-// 32x32 tiles go through shared memory so that both the reads (along r) and the writes (along k) are
-// coalesced.
-template <bool TRANS>
-__global__ void __launch_bounds__(PACK_TILE * 8)
-pack_split_kernel(const float *__restrict__ src, long long s_row, long long s_col, int rows, int cols,
-                  int cols_z, __nv_bfloat16 *__restrict__ dst, long long ldd, long long plane, long long dst_z) {
-  __shared__ float tile[PACK_TILE][PACK_TILE + 1];
-  const int k0 = blockIdx.x * PACK_TILE, r0 = blockIdx.y * PACK_TILE;
-  const int kz = blockIdx.z * cols_z;                 // first source column of this chunk
+// One operand of a pack launch:
+//   dst[plane p][z][r][kk] (row pitch ldd, chunk stride dst_z) = split(src[r * s_row + k * s_col]),
+//   k = z * cols_z + kk for k < cols, 0 beyond; z walks the K chunks of a split-K problem (one chunk of
+//   cols_z = padded K columns otherwise).
+// trans (src contiguous along r): 32 x 32 tiles go through shared memory so that both the reads (along r)
+// and the writes (along k) are coalesced.  Otherwise a tile is 32 rows x 128 columns, four consecutive k per
+// thread: one float4 load where the source allows it (vec), two 8-byte stores.
+struct PackDesc {
+  const float *src; long long s_row, s_col;
+  int rows, cols, cols_z, chunks;
+  __nv_bfloat16 *dst; long long ldd, plane, dst_z;
+  int trans, vec;
+  int tiles_x, tiles_y, blocks;
+};
+
+__device__ __forceinline__ void split_store4(__nv_bfloat16 *hi_p, __nv_bfloat16 *lo_p, const float (&v)[4]) {
+  __nv_bfloat16 h[4], l[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    h[e] = __float2bfloat16_rn(v[e]);
+    l[e] = __float2bfloat16_rn(v[e] - __bfloat162float(h[e]));
+  }
+  *reinterpret_cast<uint2 *>(hi_p) = *reinterpret_cast<const uint2 *>(h);
+  *reinterpret_cast<uint2 *>(lo_p) = *reinterpret_cast<const uint2 *>(l);
+}
+
+__device__ __forceinline__ void pack_tile(const PackDesc &d, int local, float (*tile)[PACK_TILE + 1]) {
+  const int per_z = d.tiles_x * d.tiles_y;
+  const int z = local / per_z, t = local - z * per_z;
+  const int bx = t % d.tiles_x, by = t / d.tiles_x;
+  const int kz = z * d.cols_z;                       // first source column of this chunk
   const int tx = threadIdx.x, ty = threadIdx.y;
-  dst += blockIdx.z * dst_z;
-  if (TRANS) {
+  __nv_bfloat16 *dst = d.dst + z * d.dst_z;
+  const int r0 = by * PACK_TILE;
+  if (d.trans) {
+    const int k0 = bx * PACK_TILE;
 #pragma unroll
     for (int j = 0; j < PACK_TILE / 8; ++j) {
       const int kk = k0 + ty + 8 * j, r = r0 + tx;
-      tile[ty + 8 * j][tx] = (kk < cols_z && kz + kk < cols && r < rows)
-                                 ? __ldg(src + (long long)r * s_row + (long long)(kz + kk) * s_col) : 0.f;
+      tile[ty + 8 * j][tx] = (kk < d.cols_z && kz + kk < d.cols && r < d.rows)
+                                 ? __ldg(d.src + (long long)r * d.s_row + (long long)(kz + kk) * d.s_col) : 0.f;
     }
     __syncthreads();
+#pragma unroll
+    for (int j = 0; j < PACK_TILE / 8; ++j) {
+      const int r = r0 + ty + 8 * j, kk = k0 + tx;
+      if (r < d.rows && kk < d.cols_z) {
+        const float v = tile[tx][ty + 8 * j];
+        const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+        dst[(long long)r * d.ldd + kk] = hi;
+        dst[d.plane + (long long)r * d.ldd + kk] = __float2bfloat16_rn(v - __bfloat162float(hi));
+      }
+    }
+    return;
   }
+  const int kk = bx * (4 * PACK_TILE) + 4 * tx;      // cols_z is a multiple of 64: kk < cols_z covers kk..kk+3
 #pragma unroll
   for (int j = 0; j < PACK_TILE / 8; ++j) {
-    const int r = r0 + ty + 8 * j, kk = k0 + tx;
-    if (r < rows && kk < cols_z) {
-      float v;
-      if (TRANS) v = tile[tx][ty + 8 * j];
-      else v = kz + kk < cols ? __ldg(src + (long long)r * s_row + (long long)(kz + kk) * s_col) : 0.f;
-      const __nv_bfloat16 hi = __float2bfloat16_rn(v);
-      const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
-      dst[(long long)r * ldd + kk] = hi;
-      dst[plane + (long long)r * ldd + kk] = lo;
+    const int r = r0 + ty + 8 * j;
+    if (r < d.rows && kk < d.cols_z) {
+      float v[4];
+      const float *sp = d.src + (long long)r * d.s_row + (long long)(kz + kk) * d.s_col;
+      if (d.vec && kz + kk + 3 < d.cols) {
+        const float4 q = __ldg(reinterpret_cast<const float4 *>(sp));
+        v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[e] = kz + kk + e < d.cols ? __ldg(sp + e * d.s_col) : 0.f;
+      }
+      __nv_bfloat16 *o = dst + (long long)r * d.ldd + kk;
+      split_store4(o, o + d.plane, v);
     }
   }
 }
 
-static int pack_split(const float *src, long long s_row, long long s_col, int rows, int cols, int cols_z, int chunks,
-                      __nv_bfloat16 *dst, long long ldd, long long plane, long long dst_z, cudaStream_t st) {
-  dim3 grid((cols_z + PACK_TILE - 1) / PACK_TILE, (rows + PACK_TILE - 1) / PACK_TILE, chunks), block(PACK_TILE, 8);
-  if (grid.y > 65535 || chunks > 65535) { set_error("pack_split: too many rows (%d)", rows); return PLR2_E_SHAPE; }
-  if (s_row == 1 && s_col != 1)
-    pack_split_kernel<true><<<grid, block, 0, st>>>(src, s_row, s_col, rows, cols, cols_z, dst, ldd, plane, dst_z);
-  else
-    pack_split_kernel<false><<<grid, block, 0, st>>>(src, s_row, s_col, rows, cols, cols_z, dst, ldd, plane, dst_z);
+// Both operands of a contraction in one launch: blocks [0, a.blocks) pack A, the rest pack B.
+__global__ void __launch_bounds__(PACK_TILE * 8)
+pack_split_kernel(PackDesc a, PackDesc b) {
+  __shared__ float tile[PACK_TILE][PACK_TILE + 1];
+  const int bid = blockIdx.x;
+  if (bid < a.blocks) pack_tile(a, bid, tile);
+  else pack_tile(b, bid - a.blocks, tile);
+}
+
+static PackDesc pack_desc(const float *src, long long s_row, long long s_col, int rows, int cols, int cols_z, int chunks,
+                          __nv_bfloat16 *dst, long long ldd, long long plane, long long dst_z) {
+  PackDesc d;
+  d.src = src; d.s_row = s_row; d.s_col = s_col; d.rows = rows; d.cols = cols; d.cols_z = cols_z; d.chunks = chunks;
+  d.dst = dst; d.ldd = ldd; d.plane = plane; d.dst_z = dst_z;
+  d.trans = (s_row == 1 && s_col != 1) ? 1 : 0;
+  // float4 loads: rows, chunks and columns must start on 16-byte boundaries of the source
+  d.vec = (!d.trans && s_col == 1 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 && s_row % 4 == 0 && cols_z % 4 == 0) ? 1 : 0;
+  d.tiles_x = d.trans ? (cols_z + PACK_TILE - 1) / PACK_TILE : (cols_z + 4 * PACK_TILE - 1) / (4 * PACK_TILE);
+  d.tiles_y = (rows + PACK_TILE - 1) / PACK_TILE;
+  d.blocks = d.tiles_x * d.tiles_y * chunks;
+  return d;
+}
+
+static int pack_pair(const PackDesc &a, const PackDesc &b, cudaStream_t st) {
+  const long long blocks = (long long)a.blocks + b.blocks;
+  if (blocks <= 0 || blocks > 0x7fffffffLL) { set_error("pack_split: bad block count"); return PLR2_E_SHAPE; }
+  pack_split_kernel<<<(unsigned)blocks, dim3(PACK_TILE, 8), 0, st>>>(a, b);
   return check_launch("pack_split");
 }
 
@@ -130,8 +186,8 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     splits = (g.K + Ks - 1) / Ks;
     const size_t kp_all = (size_t)splits * Ks;
     if ((size_t)g.M * kp_all > S.elems || (size_t)g.N * kp_all > S.elems) return gemm_f32(g, 1, st);
-    if ((rc = pack_split(g.A, g.sam, g.sak, g.M, g.K, (int)kp_all, 1, S.pa, (long long)kp_all, (long long)S.elems, 0, st))) return rc;
-    if ((rc = pack_split(g.B, g.sbn, g.sbk, g.N, g.K, Ks, splits, S.pb, Ks, (long long)S.elems, (long long)g.N * Ks, st))) return rc;
+    if ((rc = pack_pair(pack_desc(g.A, g.sam, g.sak, g.M, g.K, (int)kp_all, 1, S.pa, (long long)kp_all, (long long)S.elems, 0),
+                        pack_desc(g.B, g.sbn, g.sbk, g.N, g.K, Ks, splits, S.pb, Ks, (long long)S.elems, (long long)g.N * Ks), st))) return rc;
     TcGemm t;
     t.A = S.pa; t.lda = (long long)kp_all; t.a_plane = (long long)S.elems;
     t.W = S.pb; t.ldw = Ks; t.w_plane = (long long)S.elems;
@@ -149,8 +205,8 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
   const size_t a_elems = (size_t)g.M * batch * Kp, b_elems = (size_t)g.N * batch * Kp, c_elems = (size_t)g.M * batch * g.N;
   if (a_elems > S.elems || b_elems > S.elems || (need_ct && c_elems > S.elems)) return gemm_f32(g, 1, st);
   for (int z = 0; z < batch; ++z) {
-    if ((rc = pack_split(g.A + z * g.zA, g.sam, g.sak, g.M, g.K, Kp, 1, S.pa + (size_t)z * Kp, (long long)batch * Kp, (long long)S.elems, 0, st))) return rc;
-    if ((rc = pack_split(g.B + z * g.zB, g.sbn, g.sbk, g.N, g.K, Kp, 1, S.pb + (size_t)z * g.N * Kp, Kp, (long long)S.elems, 0, st))) return rc;
+    if ((rc = pack_pair(pack_desc(g.A + z * g.zA, g.sam, g.sak, g.M, g.K, Kp, 1, S.pa + (size_t)z * Kp, (long long)batch * Kp, (long long)S.elems, 0),
+                        pack_desc(g.B + z * g.zB, g.sbn, g.sbk, g.N, g.K, Kp, 1, S.pb + (size_t)z * g.N * Kp, Kp, (long long)S.elems, 0), st))) return rc;
   }
   TcGemm t;
   t.A = S.pa; t.lda = (long long)batch * Kp; t.a_plane = (long long)S.elems;
