@@ -252,7 +252,10 @@ typedef struct plr2_param_table {
 #define PLR2_NET_REFINER 1
 /* precision of the large contractions */
 #define PLR2_PREC_FP32 0      /* FP32 SIMT everywhere (bit-for-bit reproducible) */
-#define PLR2_PREC_BF16X2 1    /* tcgen05 kind::f16 on split-bf16 operands (hi+lo, 3 MMAs), FP32 accumulate in TMEM */
+#define PLR2_PREC_BF16X2 1    /* tcgen05 kind::f16 on split-bf16 operands (hi+lo, 3 MMAs), FP32 accumulate in TMEM.
+                               * Inference keeps activations as bf16 planes; with training != 0 activations stay FP32
+                               * and the operands of every forward / input-gradient / weight-gradient contraction are
+                               * packed into scratch planes of the workspace (n_points >= 128, else FP32 SIMT). */
 
 /* Packed weight buffer (floats) and workspace (bytes) sizes. */
 size_t plr2_net_packed_floats(int net, int num_obj);
@@ -268,7 +271,8 @@ int plr2_net_unpack_grads(int net, const float *packed_grad, const plr2_param_ta
 /* PoseNet.forward without the backbone (lib/network.py:98-132) for `frames` frames:
  *   out_img [F][32][hw] f32 backbone output; choose [F][N] i64; x [F][N][3]; obj [F] i64
  *   -> pred_r [F][N][4], pred_t [F][N][3], pred_c [F][N][1], emb [F][32][N]
- * training != 0 keeps every activation in the workspace for plr2_posenet_backward. */
+ * training != 0 keeps every activation in the workspace for plr2_posenet_backward (pass the same
+ * `precision` to both: the backward runs its contractions the way the forward did). */
 int plr2_posenet_forward(const float *packed, const float *out_img, const int64_t *choose, const float *x,
                          const int64_t *obj, int frames, int n_points, int hw, int num_obj,
                          void *workspace, size_t workspace_bytes, float *pred_r, float *pred_t,
