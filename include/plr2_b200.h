@@ -253,9 +253,12 @@ typedef struct plr2_param_table {
 /* precision of the large contractions */
 #define PLR2_PREC_FP32 0      /* FP32 SIMT everywhere (bit-for-bit reproducible) */
 #define PLR2_PREC_BF16X2 1    /* tcgen05 kind::f16 on split-bf16 operands (hi+lo, 3 MMAs), FP32 accumulate in TMEM.
-                               * Inference keeps activations as bf16 planes; with training != 0 activations stay FP32
-                               * and the operands of every forward / input-gradient / weight-gradient contraction are
-                               * packed into scratch planes of the workspace (n_points >= 128, else FP32 SIMT). */
+                               * Inference keeps activations as bf16 planes.  With training != 0 activations stay FP32:
+                               * the forward runs on the FP32 kernel (its ReLU signs are the masks of the backward),
+                               * the operands of every input-gradient / weight-gradient contraction are packed into
+                               * scratch planes of the workspace (n_points >= 128, else FP32 SIMT). */
+#define PLR2_PREC_BF16X2_ALL 2 /* as above, and the training forward on the tensor cores too: ~1 ReLU sign in 10^5
+                               * differs from an FP32 evaluation, gradients of small batches scatter at the 1e-3 level */
 
 /* Packed weight buffer (floats) and workspace (bytes) sizes. */
 size_t plr2_net_packed_floats(int net, int num_obj);

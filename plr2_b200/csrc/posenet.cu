@@ -21,9 +21,16 @@ struct GemmCtx {
   bool tc = false;
   TcScratch S;
 };
-static GemmCtx make_ctx(const NetWorkspace &W, int precision, int training, int n_points) {
+static bool prec_is_tc(int precision) { return precision == PLR2_PREC_BF16X2 || precision == PLR2_PREC_BF16X2_ALL; }
+// forward = the call is a training FORWARD.  Its ReLU outputs are the masks of the backward: an operand error
+// of 2^-17 flips the sign of about one pre-activation in 10^5 against an FP32 evaluation, and every flip moves the
+// gradients of that point by O(1) (measured: parameter gradients of a 500-point frame only 92-98 % within rtol
+// 1e-3 instead of 100 %).  PLR2_PREC_BF16X2 therefore keeps the training forward on the FP32 kernel and runs the
+// backward (no discontinuity: errors stay ~1e-5) on the tensor cores; PLR2_PREC_BF16X2_ALL opts the forward in too.
+static GemmCtx make_ctx(const NetWorkspace &W, int precision, int training, int n_points, bool forward) {
   GemmCtx c;
-  c.tc = precision == PLR2_PREC_BF16X2 && training && n_points >= 128 && W.tc_elems > 0 && W.tc_pa != nullptr;
+  c.tc = prec_is_tc(precision) && training && n_points >= 128 && W.tc_elems > 0 && W.tc_pa != nullptr &&
+         (!forward || precision == PLR2_PREC_BF16X2_ALL);
   c.S.pa = reinterpret_cast<__nv_bfloat16 *>(W.tc_pa);
   c.S.pb = reinterpret_cast<__nv_bfloat16 *>(W.tc_pb);
   c.S.ct = W.tc_ct;
@@ -74,7 +81,7 @@ static int feat_forward(const float *pk, const NetLayout &L, const NetWorkspace 
 // ---------------------------------------------------------------------------------------------
 // Tensor-core inference path (PLR2_PREC_BF16X2, no activations kept for backward).
 static bool use_tc(int precision, int training, int n_points) {
-  return precision == PLR2_PREC_BF16X2 && !training && n_points >= 128;   // per-frame epilogues: <= 2 frames per 128-row tile
+  return prec_is_tc(precision) && !training && n_points >= 128;   // per-frame epilogues: <= 2 frames per 128-row tile
 }
 
 static int check_tc_ws(const NetLayout &L, void *ws, size_t bytes, int frames, int n, TcWorkspace &W) {
@@ -313,7 +320,7 @@ extern "C" int plr2_posenet_forward(const float *packed, const float *out_img, c
   }
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));
-  const GemmCtx cx = make_ctx(W, precision, training, n_points);
+  const GemmCtx cx = make_ctx(W, precision, training, n_points, true);
   const int F = frames, N = n_points, R = F * N;
   const float *pk = packed;
   RC(feat_forward(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, training, cx, st));
@@ -364,7 +371,7 @@ extern "C" int plr2_refiner_forward(const float *packed, const float *x, const f
   }
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, training, W));
-  const GemmCtx cx = make_ctx(W, precision, training, n_points);
+  const GemmCtx cx = make_ctx(W, precision, training, n_points, true);
   const int F = frames, N = n_points;
   const float *pk = packed;
   RC(feat_forward(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, training, cx, st));
@@ -398,7 +405,7 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   const NetLayout L = make_layout(PLR2_NET_POSENET, num_obj);
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, 1, W));
-  const GemmCtx cx = make_ctx(W, precision, 1, n_points);
+  const GemmCtx cx = make_ctx(W, precision, 1, n_points, false);
   cudaStream_t st = (cudaStream_t)stream;
   const int F = frames, N = n_points, R = F * N;
   const float *pk = packed;
@@ -469,7 +476,7 @@ extern "C" int plr2_refiner_backward(const float *packed, const float *x, const 
   const NetLayout L = make_layout(PLR2_NET_REFINER, num_obj);
   NetWorkspace W;
   RC(check_ws(L, workspace, workspace_bytes, frames, n_points, 1, W));
-  const GemmCtx cx = make_ctx(W, precision, 1, n_points);
+  const GemmCtx cx = make_ctx(W, precision, 1, n_points, false);
   cudaStream_t st = (cudaStream_t)stream;
   const int F = frames, N = n_points;
   const float *pk = packed;

@@ -148,7 +148,7 @@ class RefineLossFn(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 # PoseNet / PoseRefineNet hot path
 NET_POSENET, NET_REFINER = 0, 1
-PREC_FP32, PREC_BF16X2 = 0, 1
+PREC_FP32, PREC_BF16X2, PREC_BF16X2_ALL = 0, 1, 2   # include/plr2_b200.h: PLR2_PREC_*
 
 POSENET_LAYER_NAMES = (["feat.conv1", "feat.e_conv1", "feat.conv2", "feat.e_conv2", "feat.conv5", "feat.conv6"]
                        + [f"conv{i}_{h}" for i in (1, 2, 3, 4) for h in "rtc"])
@@ -188,7 +188,7 @@ class NetState:
             pairs = [(w.contiguous(), b.contiguous()) for w, b in pairs]
             with torch.cuda.device(dev):
                 rc = L.plr2_net_pack(self.net, _param_table(pairs), self.num_obj, _cabi.ptr(self.packed),
-                                     1 if precision == PREC_BF16X2 else 0, _cabi.stream_ptr(dev))
+                                     0 if precision == PREC_FP32 else 1, _cabi.stream_ptr(dev))
             _cabi.check(rc, "plr2_net_pack")
             self.key = key
         return self.packed

@@ -38,7 +38,8 @@ def test_golden_reference_indices(name):
 
 
 @pytest.mark.parametrize("n_ref,n_query", [(1, 1), (1, 700), (15, 33), (16, 512), (17, 513), (500, 5000),
-                                           (2047, 100), (2048, 1031), (2049, 777), (5000, 300)])
+                                           (2047, 100), (2048, 1031), (2049, 777), (5000, 300),
+                                           (4096, 1100), (4097, 3000), (9000, 2500)])
 def test_exact_mode_bit_exact_vs_fma_oracle(n_ref, n_query):
     rng = np.random.default_rng(n_ref * 7 + n_query)
     ref = (rng.standard_normal((3, n_ref)) * 0.1 + 0.7).astype(np.float32)
@@ -54,6 +55,16 @@ def test_ties_on_lattice_lowest_index_wins():
     ref = rng.integers(-3, 4, (3, 777)).astype(np.float32)
     query = rng.integers(-3, 4, (3, 4099)).astype(np.float32)
     for mode in (KNN_EXACT, KNN_FAST):   # integers: both forms are exact -> identical indices
+        assert np.array_equal(run(ref, query, 1, mode), KO.knn_oracle(ref, query, 1)[0])
+
+
+def test_ties_on_lattice_multi_tile():
+    """More references than one shared-memory tile holds (4096): rounds of 8/4/2/1 queries per lane re-stage
+    the tiles, the winning chunk is re-read from global memory; lowest index still wins in both modes."""
+    rng = np.random.default_rng(5)
+    ref = rng.integers(-6, 7, (3, 9001)).astype(np.float32)
+    query = rng.integers(-6, 7, (3, 2300)).astype(np.float32)
+    for mode in (KNN_EXACT, KNN_FAST):
         assert np.array_equal(run(ref, query, 1, mode), KO.knn_oracle(ref, query, 1)[0])
 
 

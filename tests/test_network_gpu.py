@@ -76,7 +76,7 @@ def test_gemm_f32_layouts_and_epilogues(M, N, K, layout):
 
 # ---------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["posenet_linemod_nonsym", "posenet_ycb_sym", "posenet_ycb_refine"])
-@pytest.mark.parametrize("precision", [ops.PREC_FP32, ops.PREC_BF16X2])
+@pytest.mark.parametrize("precision", [ops.PREC_FP32, ops.PREC_BF16X2, ops.PREC_BF16X2_ALL])
 def test_posenet_forward_backward_matches_reference_golden(name, precision):
     g = load_golden(name)
     shp = shape_of(g)
@@ -136,10 +136,12 @@ def test_refiner_chain_matches_reference_golden(name, precision):
         assert_close(p.grad.norm().item(), g["gnorm." + k], "gnorm." + k, rtol=5e-3, frac=1.0)
 
 
+@pytest.mark.parametrize("precision", [ops.PREC_FP32, ops.PREC_BF16X2])
 @pytest.mark.parametrize("shape,obj", [(synth.LINEMOD, 3), (synth.YCB, 12)])
-def test_posenet_full_size_vs_oracle(shape, obj):
-    """BASELINE configs C1 / C2 at full size (N = 500 / 1000): forward + loss + all gradients."""
-    net = build_posenet(shape, 31, ops.PREC_FP32)
+def test_posenet_full_size_vs_oracle(shape, obj, precision):
+    """BASELINE configs C1 / C2 at full size (N = 500 / 1000): forward + loss + all gradients, with the
+    contractions on the FP32 SIMT kernel and on the tensor cores (packed split-bf16 operands)."""
+    net = build_posenet(shape, 31, precision)
     fr = synth.make_frame(shape, 32, obj=obj)
     img = tt(fr["out_img"], "cuda", grad=True)
     points, choose = tt(fr["points"], "cuda")[None], tt(fr["choose"], "cuda")[None, None]
@@ -176,6 +178,30 @@ def test_batched_frames_equal_single_frame_calls():
             a = net(st("out_img")[i:i + 1], st("points")[i:i + 1], st("choose")[i:i + 1, None], st("idx")[i:i + 1, None])
             for x, y in zip(a, (pr, pt, pc, emb)):
                 assert torch.equal(x[0], y[i])
+
+
+def test_batched_training_tensor_core_equals_fp32_path():
+    """Six frames of 200 points (1200 rows: K tail of the weight gradients, split-K, r/t/c head batches) through
+    forward + Loss + backward: gradients of the tensor-core training path against the FP32 SIMT path."""
+    shp = synth.Shape(200, 21, 100, 24, 24, tuple(synth.YCB_SYM))
+    frs = [synth.make_frame(shp, 90 + i, obj=o) for i, o in enumerate([3, 12, 0, 20, 7, 15])]
+    st = lambda key: tt(np.stack([f[key] for f in frs]), "cuda")
+    grads = {}
+    for prec in (ops.PREC_FP32, ops.PREC_BF16X2):
+        net = build_posenet(shp, 9, prec)
+        img = st("out_img").requires_grad_(True)
+        pr, pt, pc, _ = net(img, st("points"), st("choose")[:, None], st("idx")[:, None])
+        crit = Loss(shp.num_mesh, list(shp.sym_list))
+        loss, _, _, _ = crit(pr, pt, pc, st("target"), st("model_points"), st("idx")[:, None], st("points"), 0.015, False)
+        loss.mean().backward()
+        grads[prec] = ({k: v.grad.detach().cpu().numpy() for k, v in net.named_parameters() if v.grad is not None},
+                       img.grad.detach().cpu().numpy(), pr.detach().cpu().numpy())
+    ga, gb = grads[ops.PREC_FP32], grads[ops.PREC_BF16X2]
+    assert_close(gb[2], ga[2], "pred_r")
+    assert_close(gb[1], ga[1], "g_out_img", frac=0.99)
+    assert set(ga[0]) == set(gb[0]) and len(ga[0]) >= 30
+    for k in ga[0]:
+        assert_close(gb[0][k], ga[0][k], "grad " + k)
 
 
 def test_weight_update_is_picked_up():

@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--knn", default="fast", choices=["exact", "fast"])
+    ap.add_argument("--fwd-tc", type=int, default=0,
+                    help="1: training forward on the tensor cores too (PLR2_PREC_BF16X2_ALL; ReLU masks may differ from FP32 at ~1e-5 of the activations)")
     ap.add_argument("--overlap", type=int, default=0,
                     help="1: gradient all-reduce inside the backward op, head weights overlapped with the trunk backward")
     args = ap.parse_args()
@@ -41,7 +43,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl")
     shp = synth.YCB_REFINE
-    net = PoseNet(shp.num_points, shp.num_obj, precision=ops.PREC_BF16X2)
+    net = PoseNet(shp.num_points, shp.num_obj, precision=ops.PREC_BF16X2_ALL if args.fwd_tc else ops.PREC_BF16X2)
     net.cnn = torch.nn.Identity()
     net.load_state_dict({k: torch.from_numpy(v) for k, v in synth.make_params("posenet", shp.num_obj, 1).items()}, strict=False)
     net = net.to(dev)
@@ -99,6 +101,7 @@ def main():
             "config": "C5: PoseNet fwd+bwd + Loss (ADD-S, M=2300), %d frames/GPU, grad all-reduce + Adam" % args.frames,
             "n_gpus": world, "steps": args.steps, "ms_per_step": ms / args.steps,
             "frames_per_s": world * args.frames * args.steps / (ms / 1e3),
+            "train_forward": "tensor cores (PLR2_PREC_BF16X2_ALL)" if args.fwd_tc else "fp32 kernel, backward on tensor cores (PLR2_PREC_BF16X2)",
             "allreduce_ms_per_step": ar_ms / args.steps, "grad_bucket_mb": bucket.numel * 4 / 1e6,
             "allreduce": "inside the backward op, head weights overlapped with the trunk backward" if in_op else "one flat bucket after the backward",
             "replicas_consistent": consistent, "loss_finite": bool(torch.isfinite(loss).all()),
