@@ -1,3 +1,6 @@
+"""Per-parameter gradient accuracy of the three precision modes against the CPU oracle (config C1 at full size):
+fraction of elements within rtol 1e-3 (+1e-4 of the tensor's largest entry) and the largest deviation relative to
+the largest entry.  GPU only.  Usage: python tools/gradcheck_tc.py"""
 import sys, numpy as np, torch
 sys.path.insert(0, '.')
 from oracle import densefusion_oracle as DO
@@ -13,7 +16,7 @@ opr, opt_, opc, oemb = DO.posenet_forward(p, oimg, tt(fr["points"]), tt(fr["choo
 ol, od, _, _, _ = DO.pose_loss(opr, opt_, opc, tt(fr["target"]), tt(fr["model_points"]), obj, tt(fr["points"]), 0.015, False, shape.sym_list)
 ol.backward()
 res = {}
-for prec in (ops.PREC_FP32, ops.PREC_BF16X2):
+for prec in (ops.PREC_FP32, ops.PREC_BF16X2, ops.PREC_BF16X2_ALL):
     net = build_posenet(shape, 31, prec)
     img = tt(fr["out_img"], "cuda", grad=True)
     points, choose = tt(fr["points"], "cuda")[None], tt(fr["choose"], "cuda")[None, None]
@@ -27,5 +30,5 @@ for prec in (ops.PREC_FP32, ops.PREC_BF16X2):
         atol = 1e-4 * float(np.abs(o).max())
         res.setdefault(k, []).append((frac_close(g, o, 1e-3, atol), float(np.abs(g - o).max() / (np.abs(o).max() + 1e-30))))
 for k, v in res.items():
-    flag = "  <--" if v[1][0] < 0.95 else ""
-    print("%-18s fp32 frac %.3f maxrel %.1e | tc frac %.3f maxrel %.1e%s" % (k, v[0][0], v[0][1], v[1][0], v[1][1], flag))
+    flag = "  <--" if min(x[0] for x in v) < 0.95 else ""
+    print("%-18s fp32 %.3f %.1e | bwd-tc %.3f %.1e | all-tc %.3f %.1e%s" % (k, v[0][0], v[0][1], v[1][0], v[1][1], v[2][0], v[2][1], flag))
