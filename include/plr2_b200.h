@@ -257,8 +257,9 @@ typedef struct plr2_param_table {
                                * the forward runs on the FP32 kernel (its ReLU signs are the masks of the backward),
                                * the operands of every input-gradient / weight-gradient contraction are packed into
                                * scratch planes of the workspace (n_points >= 128, else FP32 SIMT). */
-#define PLR2_PREC_BF16X2_ALL 2 /* as above, and the training forward on the tensor cores too: ~1 ReLU sign in 10^5
-                               * differs from an FP32 evaluation, gradients of small batches scatter at the 1e-3 level */
+#define PLR2_PREC_BF16X2_ALL 2 /* as above, and the training forward on the tensor cores too; pre-activations inside the
+                               * operand-error bound (2^-14 |x||w|, ~1e-3 of them) are recomputed in FP32 before the ReLU
+                               * so that the masks of the backward agree with an FP32 forward */
 
 /* Packed weight buffer (floats) and workspace (bytes) sizes. */
 size_t plr2_net_packed_floats(int net, int num_obj);

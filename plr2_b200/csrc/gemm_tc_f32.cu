@@ -143,6 +143,55 @@ combine_kernel(const float *__restrict__ ct, long long ldct, int nsum, float *C,
   }
 }
 
+// ---- sign-safe ReLU of a training forward --------------------------------------------------
+// The ReLU output of a training forward is the mask of its backward, and the split-bf16 product carries a
+// relative error of up to 2^-16 per operand and 2^-16 for the dropped lo*lo term: a pre-activation closer to
+// zero than SIGN_TAU * ||x_r|| * ||w_n|| (Cauchy-Schwarz over the K terms; SIGN_TAU = 2^-14 > 3 * 2^-16 plus the
+// FP32 accumulation) may have the wrong sign.  Those elements - about one in a thousand - are recomputed as a
+// sequential FP32 dot product before the ReLU; everywhere else the tensor-core sign is provably the true one.
+constexpr float SIGN_TAU = 6.103515625e-05f;   // 2^-14
+
+// out[z][r] = || src_z[r, 0:cols] ||_2, one warp per row (rows contiguous along k for both operands of a forward)
+__global__ void __launch_bounds__(256)
+row_norm_kernel(const float *__restrict__ src, long long s_row, long long s_col, long long z_stride, int rows,
+                int cols, float *__restrict__ out) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const float *p = src + blockIdx.y * z_stride + (long long)warp * s_row;
+  float a = 0.f;
+  for (int k = lane; k < cols; k += 32) { const float v = __ldg(p + (long long)k * s_col); a = fmaf(v, v, a); }
+  a = warp_sum(a);
+  if (lane == 0) out[(size_t)blockIdx.y * rows + warp] = sqrtf(a);
+}
+
+// C (pre-activation, written by the tensor-core launch without ReLU) -> relu(C), with the elements inside the
+// error bound recomputed from the FP32 operands.  blockIdx.y = problem z of a batched launch.
+__global__ void __launch_bounds__(256)
+relu_signsafe_kernel(GemmArgs g, const float *__restrict__ nx, const float *__restrict__ nw) {
+  const int z = blockIdx.y;
+  const float *A = g.A + z * g.zA, *B = g.B + z * g.zB;
+  float *C = g.C + z * g.zC;
+  const float *bias = g.bias ? g.bias + z * g.zbias : nullptr;
+  const float *fb = g.frame_bias ? g.frame_bias + z * g.zfb : nullptr;
+  nx += (size_t)z * g.M;
+  nw += (size_t)z * g.N;
+  const long long total = (long long)g.M * g.N;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / g.N;
+    const int n = (int)(i - r * g.N);
+    float y = C[r * g.ldc + n];
+    if (fabsf(y) < SIGN_TAU * nx[r] * nw[n]) {
+      const float *a = A + r * g.sam, *b = B + (long long)n * g.sbn;
+      float acc = 0.f;
+      for (int k = 0; k < g.K; ++k) acc = fmaf(__ldg(a + (long long)k * g.sak), __ldg(b + (long long)k * g.sbk), acc);
+      if (bias) acc += bias[n];
+      if (fb) acc += fb[(r / g.rows_per_frame) * g.ldfb + n];
+      y = acc;
+    }
+    C[r * g.ldc + n] = fmaxf(y, 0.f);
+  }
+}
+
 bool gemm_tc_eligible(const GemmArgs &g) {
   // tiny N (conv1's 3 input channels as a weight-gradient N) and K stay on the SIMT kernel
   return g.M > 0 && g.N >= 16 && g.K >= 8 && !(g.relu && g.accumulate);
@@ -215,10 +264,24 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
   t.a_col_z = Kp; t.b_row_z = g.N;
   t.bias = g.bias; t.bias_z = g.zbias;
   t.frame_bias = g.frame_bias; t.rows_per_frame = g.rows_per_frame; t.ldfb = g.ldfb;
-  t.relu = g.relu; t.out_mode = TC_OUT_F32;
+  // ReLU layers (training forwards) go through the sign-safe pass; it borrows the unused C staging area for the
+  // row norms of both operands
+  const bool sign_safe = g.relu && !need_ct && (size_t)batch * ((size_t)g.M + g.N) <= S.elems;
+  t.relu = sign_safe ? 0 : g.relu; t.out_mode = TC_OUT_F32;
   if (need_ct) { t.Cf = S.ct; t.ldc = (long long)batch * g.N; t.c_col_z = g.N; }
   else { t.Cf = g.C; t.ldc = g.ldc; t.c_col_z = g.zC; }
   if ((rc = gemm_bf16x2(t, st))) return rc;
+  if (sign_safe) {
+    float *nx = S.ct, *nw = S.ct + (size_t)batch * g.M;
+    row_norm_kernel<<<dim3((g.M + 7) / 8, batch), 256, 0, st>>>(g.A, g.sam, g.sak, g.zA, g.M, g.K, nx);
+    row_norm_kernel<<<dim3((g.N + 7) / 8, batch), 256, 0, st>>>(g.B, g.sbn, g.sbk, g.zB, g.N, g.K, nw);
+    const long long total = (long long)g.M * g.N;
+    const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    GemmArgs gs = g;
+    gs.batch = batch;
+    relu_signsafe_kernel<<<dim3(blocks, batch), 256, 0, st>>>(gs, nx, nw);
+    if ((rc = check_launch("gemm_tc_f32: sign-safe relu", 3))) return rc;
+  }
   if (need_ct) {
     for (int z = 0; z < batch; ++z) {
       const long long total = (long long)g.M * g.N;

@@ -26,7 +26,8 @@ static bool prec_is_tc(int precision) { return precision == PLR2_PREC_BF16X2 || 
 // of 2^-17 flips the sign of about one pre-activation in 10^5 against an FP32 evaluation, and every flip moves the
 // gradients of that point by O(1) (measured: parameter gradients of a 500-point frame only 92-98 % within rtol
 // 1e-3 instead of 100 %).  PLR2_PREC_BF16X2 therefore keeps the training forward on the FP32 kernel and runs the
-// backward (no discontinuity: errors stay ~1e-5) on the tensor cores; PLR2_PREC_BF16X2_ALL opts the forward in too.
+// backward (no discontinuity: errors stay ~1e-5) on the tensor cores; PLR2_PREC_BF16X2_ALL opts the forward in too,
+// with the sign-safe ReLU pass of gemm_tc_f32.cu behind every ReLU layer.
 static GemmCtx make_ctx(const NetWorkspace &W, int precision, int training, int n_points, bool forward) {
   GemmCtx c;
   c.tc = prec_is_tc(precision) && training && n_points >= 128 && W.tc_elems > 0 && W.tc_pa != nullptr &&
