@@ -176,19 +176,33 @@ relu_signsafe_kernel(GemmArgs g, const float *__restrict__ nx, const float *__re
   nx += (size_t)z * g.M;
   nw += (size_t)z * g.N;
   const long long total = (long long)g.M * g.N;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / g.N;
-    const int n = (int)(i - r * g.N);
-    float y = C[r * g.ldc + n];
-    if (fabsf(y) < SIGN_TAU * nx[r] * nw[n]) {
-      const float *a = A + r * g.sam, *b = B + (long long)n * g.sbn;
+  const int lane = threadIdx.x & 31;
+  // warp-uniform trip count: every lane stays in the loop so that flagged elements can be recomputed by the
+  // whole warp (coalesced reads along k, butterfly sum) instead of by one lane walking K serially
+  for (long long base = (blockIdx.x * (long long)blockDim.x + threadIdx.x) - lane; base < total;
+       base += (long long)gridDim.x * blockDim.x) {
+    const long long i = base + lane;
+    const bool live = i < total;
+    const int r = live ? (int)(i / g.N) : 0;
+    const int n = live ? (int)(i - (long long)r * g.N) : 0;
+    float y = live ? C[(long long)r * g.ldc + n] : 1.f;
+    const bool flag = live && fabsf(y) < SIGN_TAU * nx[r] * nw[n];
+    unsigned todo = __ballot_sync(0xffffffffu, flag);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int rr = __shfl_sync(0xffffffffu, r, src), nn = __shfl_sync(0xffffffffu, n, src);
+      const float *a = A + (long long)rr * g.sam, *b = B + (long long)nn * g.sbn;
       float acc = 0.f;
-      for (int k = 0; k < g.K; ++k) acc = fmaf(__ldg(a + (long long)k * g.sak), __ldg(b + (long long)k * g.sbk), acc);
-      if (bias) acc += bias[n];
-      if (fb) acc += fb[(r / g.rows_per_frame) * g.ldfb + n];
-      y = acc;
+      for (int k = lane; k < g.K; k += 32) acc = fmaf(__ldg(a + (long long)k * g.sak), __ldg(b + (long long)k * g.sbk), acc);
+      acc = warp_sum(acc);
+      if (lane == src) {
+        if (bias) acc += bias[nn];
+        if (fb) acc += fb[(long long)(rr / g.rows_per_frame) * g.ldfb + nn];
+        y = acc;
+      }
     }
-    C[r * g.ldc + n] = fmaxf(y, 0.f);
+    if (live) C[(long long)r * g.ldc + n] = fmaxf(y, 0.f);
   }
 }
 
