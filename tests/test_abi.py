@@ -106,3 +106,28 @@ def test_knn_plan_prefers_full_waves(lib):
     ns, part = _knn_plan(lib, 1, 2300, 592)
     assert (ns, part) == (18, 128)
     assert lib.plr2_knn_plan(0, 10, 10, None, None) != 0
+
+
+def test_training_workspace_holds_the_tensor_core_scratch(lib):
+    """plr2_net_workspace_bytes(training=1) accounts for the split-bf16 operand planes and the FP32 staging area
+    of the tensor-core training contractions: 3 x 1920 x (max(rows padded to 64, 1024) + 2048) floats."""
+    for frames, n in ((1, 500), (8, 1000), (3, 200)):
+        rows = (frames * n + 63) // 64 * 64
+        scratch = 3 * 1920 * (max(rows, 1024) + 2048) * 4
+        for net in (0, 1):
+            train = lib.plr2_net_workspace_bytes(net, frames, n, 21, 1)
+            infer_fp32_layout = lib.plr2_net_workspace_bytes(net, frames, n, 21, 0)
+            assert train >= scratch
+            assert train - scratch <= 2 * infer_fp32_layout + (1 << 22)
+
+
+def test_loss_dropins_default_to_fast_ranking_knn_dropin_to_exact():
+    from plr2_b200 import ops
+    from plr2_b200.lib.knn import KNearestNeighbor
+    from plr2_b200.lib.loss import Loss
+    from plr2_b200.lib.loss_refiner import Loss_refine
+    assert ops.KNN_LOSS_DEFAULT == ops.KNN_FAST
+    assert Loss(500, [7, 8]).knn_mode == ops.KNN_FAST and Loss_refine(500, [7, 8]).knn_mode == ops.KNN_FAST
+    assert Loss(500, [7, 8], ops.KNN_EXACT).knn_mode == ops.KNN_EXACT
+    assert KNearestNeighbor.mode == ops.KNN_EXACT
+    assert (ops.PREC_FP32, ops.PREC_BF16X2, ops.PREC_BF16X2_ALL) == (0, 1, 2)
