@@ -4,12 +4,15 @@
     python bench.py --gpus N --steps K --warmup W              # this repo (CUDA, sm_100a)
     python bench.py --impl reference --gpus N --steps K ...    # CPU restatement of the reference's path
 
-Workload (config C4 of BASELINE.json / SURVEY.md §8d): per GPU and per step, FRAMES synthetic
-YCB-shaped frames (N=1000 points, 21 classes, 5 of them symmetric, 120x120 crop, M=2300 mesh points)
-go through PoseNet (backbone output given) -> Loss(refine) -> 2 x (PoseRefineNet -> Loss_refine with
-ADD-S for symmetric classes).  One pose per frame => metric poses/sec.  Frames are independent, so
-ranks simply own different frames ("weak" scaling: FRAMES per GPU is fixed); no data-path collective.
-One JSON line is printed by rank 0.
+Workload (config C4 of BASELINE.json / SURVEY.md §8d): per step, FRAMES = 512 synthetic YCB-shaped frames
+(N=1000 points, 21 classes, 5 of them symmetric, 120x120 crop, M=2300 mesh points) go through PoseNet
+(backbone output given) -> Loss(refine) -> 2 x (PoseRefineNet -> Loss_refine with ADD-S for symmetric
+classes).  One pose per frame => metric poses/sec.  Frames are independent: rank r owns the contiguous shard
+shard_range(512, world, r) ("strong" scaling, the 512/G split BASELINE states); no data-path collective.  The
+weak-scaling curve (512 frames PER GPU) is measured in the same run and reported under `weak`.
+The line also carries the other BASELINE configs: `c2` (PoseNet + ADD-S Loss, M=500), `c3_bs1_latency_ms`
+(one frame, plain launches and CUDA-graph replay) and `train_c5` (data-parallel training step with the NCCL
+gradient all-reduce).  One JSON line is printed by rank 0.
 """
 import argparse
 import json
@@ -44,7 +47,7 @@ def peaks():
 
 def make_workload(frames, seed0):
     """dict of CPU tensors (frames, ...) in the reference's per-frame layout."""
-    base = [synth.make_frame(SHAPE, seed0 + i) for i in range(min(DISTINCT, frames))]
+    base = [synth.make_frame(SHAPE, seed0 + i, choose_mode="mask") for i in range(min(DISTINCT, frames))]
     pick = [base[i % len(base)] for i in range(frames)]
     st = lambda k: torch.from_numpy(np.stack([f[k] for f in pick]))
     return {"out_img": st("out_img"), "points": st("points"), "choose": st("choose")[:, None, :],
@@ -163,13 +166,16 @@ def time_gpu_eager(work, pn, rf, frames, dev):
             "sample": f"{frames} frames ({dt:.2f} s)"}
 
 
-def knn_roofline(pk):
-    """ADD-S 1-NN kernel at config C2 size (500 refs x 500 000 queries per frame, 8 frames)."""
+def knn_roofline(pk, ref_kernel=True):
+    """ADD-S 1-NN kernel at config C2 size (500 refs x 500 000 queries per frame, 8 frames), both ranking modes, and - as the
+    same-box baseline SURVEY.md 2 names - the reference's OWN CUDA kernels (lib/knn/src/cuda/knn.cu compiled unmodified for
+    sm_100a into oracle/_ref/libknn_cuda_ref.so; 1 GB distance matrix per frame, driven like lib/knn/src/knn.h:29-41)."""
     from plr2_b200.lib.knn import knn_indices
     g = torch.Generator(device="cuda").manual_seed(0)
     ref = torch.randn(8, 3, 500, device="cuda", generator=g) * 0.05
     qry = torch.randn(8, 3, 500_000, device="cuda", generator=g) * 0.05
     peak_tflops = 148 * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12
+    pairs = 8 * 500 * 500_000
     out = {}
     for name, mode in (("exact", 0), ("fast", 1)):
         for _ in range(3):
@@ -181,11 +187,144 @@ def knn_roofline(pk):
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 10
-        pairs = 8 * 500 * 500_000
         out[name] = {"Gpairs_s": pairs / ms / 1e6, "achieved": 8 * pairs / ms / 1e9, "peak": peak_tflops,
                      "unit": "TFLOP/s", "frac": 8 * pairs / ms / 1e9 / peak_tflops, "bound": "fp32",
                      "ms_per_launch": ms, "pairs_per_launch": pairs}
+    if ref_kernel:
+        try:
+            from oracle import knn_oracle as KO          # baseline leg: the reference's kernel is the thing compared WITH
+            if not KO.have_reference_cuda_knn():
+                raise FileNotFoundError("oracle/_ref/libknn_cuda_ref.so not built")
+            scratch = torch.empty(500 * 500_000, dtype=torch.float32, device="cuda")
+            ridx = KO.knn_reference_cuda(ref, qry, 1, scratch=scratch)
+            same = bool(torch.equal(ridx, knn_indices(ref, qry, 1, 0)))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(2):
+                KO.knn_reference_cuda(ref, qry, 1, scratch=scratch)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 2
+            out["reference_cuda_kernel"] = {
+                "Gpairs_s": pairs / ms / 1e6, "ms": ms, "pairs": pairs,
+                "kind": "lib/knn/src/cuda/knn.cu (cuComputeDistanceGlobal + cuInsertionSort) unmodified, sm_100a, scratch held",
+                "indices_equal_to_exact_mode": same,
+                "speedup_exact": out["exact"]["Gpairs_s"] / (pairs / ms / 1e6),
+                "speedup_fast": out["fast"]["Gpairs_s"] / (pairs / ms / 1e6)}
+            del scratch
+        except Exception as exc:                      # noqa: BLE001 - reported, not hidden
+            out["reference_cuda_kernel"] = {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
     return out
+
+
+def _ev_time(fn, reps, warm=2, dev=None):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    return e0.elapsed_time(e1) / reps
+
+
+def measure_c2(pipe, dev, knn_mode):
+    """BASELINE config 2: YCB-shaped PoseNet (backbone output given) + ADD-S `Loss` on symmetric class 12, N = 1000,
+    num_pt_mesh_small = 500 (2.5e8 nearest-neighbour pairs per frame), one B200.  Inference (64 frames per launch chain)
+    and training (8 frames, forward + backward of network and loss)."""
+    from plr2_b200.lib.loss import Loss
+    shp = synth.YCB
+    crit = Loss(shp.num_mesh, list(shp.sym_list), knn_mode)
+    base = [synth.make_frame(shp, 2000 + i, obj=12, choose_mode="mask") for i in range(8)]
+
+    def batch(n):
+        st = lambda k: torch.from_numpy(np.stack([base[i % 8][k] for i in range(n)])).to(dev)
+        return st("out_img"), st("points"), st("choose")[:, None], st("idx")[:, None], st("target"), st("model_points")
+    net = pipe.estimator
+    img, pts, ch, ob, tg, md = batch(64)
+
+    def fwd():
+        with torch.no_grad():
+            pr, pt, pc, _ = net.forward_features(img, pts, ch, ob)
+            return crit(pr, pt, pc, tg, md, ob, pts, 0.015, False)
+    ms = _ev_time(fwd, 10, dev=dev)
+    img8, pts8, ch8, ob8, tg8, md8 = batch(8)
+    params = net.hot_path_parameters()
+
+    def train():
+        for p in params:
+            p.grad = None
+        pr, pt, pc, _ = net.forward_features(img8, pts8, ch8, ob8)
+        loss, _, _, _ = crit(pr, pt, pc, tg8, md8, ob8, pts8, 0.015, False)
+        loss.mean().backward()
+    net.train()
+    ms_t = _ev_time(train, 10, dev=dev)
+    net.eval()
+    for p in params:
+        p.grad = None
+    return {"config": "C2: PoseNet + Loss (ADD-S, class 12), N=1000, M=500", "inference_frames_per_s": 64 / (ms / 1e3),
+            "inference_ms_per_64_frames": ms, "adds_gpairs_per_s_inside_step": 64 * 2.5e8 / (ms / 1e3) / 1e9,
+            "train_fwd_bwd_frames_per_s": 8 / (ms_t / 1e3), "train_ms_per_8_frames": ms_t}
+
+
+def measure_c3_latency(pn, rf, dev, knn_mode):
+    """BASELINE config 3: ONE YCB frame through PoseNet -> Loss(refine) -> 2 x (PoseRefineNet -> Loss_refine), bs = 1 -
+    what a tools/lightning.py / tools/train.py:182-188 user waits for per frame.  ~32 launches: launch-bound, so the
+    chain is also measured as a CUDA-graph replay.  Wall time per call including the final synchronisation."""
+    from plr2_b200 import ops
+    from plr2_b200.pipeline import DenseFusionPipeline, INPUT_KEYS
+    out = {}
+    for label, obj in (("nonsym", 3), ("sym", 12)):
+        fr = synth.make_frame(SHAPE, 4242 + obj, obj=obj, choose_mode="mask")
+        t = lambda k: torch.from_numpy(fr[k])[None].to(dev)
+        work = {"out_img": t("out_img"), "points": t("points"), "choose": t("choose")[:, None], "obj": t("idx").reshape(1, 1),
+                "target": t("target"), "model_points": t("model_points")}
+        rec = {}
+        for mode, graph in (("plain", False), ("cuda_graph", True)):
+            pipe = DenseFusionPipeline(SHAPE.num_points, SHAPE.num_obj, SHAPE.num_mesh, SHAPE.sym_list, device=dev,
+                                       precision=ops.PREC_BF16X2, knn_mode=knn_mode, chunk_frames=1, cuda_graph=graph)
+            pipe.load_params(pn, rf)
+            for _ in range(5):
+                res = pipe.infer(*(work[k] for k in INPUT_KEYS))
+            torch.cuda.synchronize(dev)
+            n = 200
+            t0 = time.perf_counter()
+            for _ in range(n):
+                res = pipe.infer(*(work[k] for k in INPUT_KEYS))
+                torch.cuda.synchronize(dev)
+            rec[mode + "_ms"] = (time.perf_counter() - t0) / n * 1e3
+            rec[mode + "_dis"] = float(res[0])
+            del pipe
+        out[label] = rec
+    return out
+
+
+def measure_train_c5(args, world, rank, dev):
+    """BASELINE config 5 under the driver's clock: data-parallel training step, 8 frames per GPU, M = 2300, one NCCL
+    gradient all-reduce per step (plr2_b200/train.py).  Primary record: all contractions on tensor cores, whole step
+    replayed as one CUDA graph; the eager variants are listed beside it."""
+    from plr2_b200 import ops
+    from plr2_b200.train import C5TrainStep
+    knn_mode = ops.KNN_FAST if args.knn == "fast" else ops.KNN_EXACT
+    recs = {}
+    for name, prec, graph in (("tc_all_graph", ops.PREC_BF16X2_ALL, True), ("tc_all_eager", ops.PREC_BF16X2_ALL, False),
+                              ("fp32fwd_tcbwd_eager", ops.PREC_BF16X2, False)):
+        try:
+            ts = C5TrainStep(dev, world, rank, 8, precision=prec, knn_mode=knn_mode, cuda_graph=graph)
+            recs[name] = ts.run(args.train_steps, 3)
+            del ts
+        except Exception as exc:                      # noqa: BLE001
+            recs[name] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        torch.cuda.empty_cache()
+    ok = [k for k in ("tc_all_graph", "tc_all_eager", "fp32fwd_tcbwd_eager") if "frames_per_s" in recs[k]]
+    best = dict(recs[ok[0]]) if ok else {"error": "no variant ran"}
+    best["variant"] = ok[0] if ok else None
+    best["variants"] = {k: ({kk: v[kk] for kk in ("ms_per_step", "frames_per_s", "allreduce_ms_per_step", "cuda_graph",
+                                                  "cuda_graph_error", "replicas_consistent") if kk in v} if "frames_per_s" in v else v)
+                        for k, v in recs.items()}
+    return best
 
 
 # --------------------------------------------------------------------------------------------------
@@ -216,9 +355,10 @@ def run_reference(args, world, rank):
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": "poses/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C4: YCB-shaped frames, PoseNet(out_img given)+Loss(refine)+2x(PoseRefineNet+Loss_refine ADD-S)",
-                   "frames_per_step": frames, "num_points": SHAPE.num_points, "num_mesh": SHAPE.num_mesh,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C4: 512 YCB-shaped frames per step sharded 512/G over the GPUs, PoseNet(out_img given)+Loss(refine)+"
+                               "2x(PoseRefineNet+Loss_refine ADD-S)",
+                   "frames_per_step": frames, "sample_of_frames_per_step": 512, "num_points": SHAPE.num_points, "num_mesh": SHAPE.num_mesh,
                    "num_obj": SHAPE.num_obj},
         "cpu_baseline": {"value": rate, "unit": "poses/s", "cores": torch.get_num_threads(), "kind": "port",
                          "sample": f"{frames} frames/step x {args.steps} steps (oracle: torch CPU fp32 + C/OpenMP 1-NN)"},
@@ -286,25 +426,36 @@ def run_ours(args, world, rank, local):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (this path has no CPU fallback; use --impl reference)")
     from plr2_b200 import _cabi, ops
+    from plr2_b200.parallel import bind_to_gpu_numa, shard_range
     from plr2_b200.pipeline import DenseFusionPipeline, INPUT_KEYS
     import ctypes as C
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     L = _cabi.lib()
     pk = peaks()
-    frames = args.frames
+    total = args.frames                                  # C4: 512 frames in all, sharded 512 / G
+    lo, hi = shard_range(total, world, rank)
+    n_local = hi - lo
     knn_mode = ops.KNN_FAST if args.knn == "fast" else ops.KNN_EXACT
+    # small shards are launch-bound (~32 kernels + glue per chunk): replay the chunk as a CUDA graph
+    use_graph = args.cuda_graph == "on" or (args.cuda_graph == "auto" and n_local < 256)
+    host_chunk = args.host_chunk if args.host_chunk > 0 else min(64, max(16, (n_local + 3) // 4))
     pipe = DenseFusionPipeline(SHAPE.num_points, SHAPE.num_obj, SHAPE.num_mesh, SHAPE.sym_list, device=dev,
                                precision=ops.PREC_BF16X2, knn_mode=knn_mode, chunk_frames=args.chunk,
-                               host_chunk_frames=args.host_chunk)
+                               host_chunk_frames=host_chunk, cuda_graph=False, max_graphs=16)
     pn = synth.make_params("posenet", SHAPE.num_obj, 1)
     rf = synth.make_params("refiner", SHAPE.num_obj, 2)
     pipe.load_params(pn, rf)
-    from plr2_b200.parallel import bind_to_gpu_numa
     numa_cpus = bind_to_gpu_numa(local) if world > 1 else None     # pinned buffers on the GPU's own node
-    work = make_workload(frames, 1000 + 7919 * rank)
+    work_all = make_workload(total, 1000)                # the same global batch on every rank
+    work = {k: v[lo:hi].contiguous() for k, v in work_all.items()}
     host = {k: v.pin_memory() for k, v in work.items()}
-    devw = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+    frame_bytes = DenseFusionPipeline.bytes_per_frame(host)
+    # Device-resident input sets, used in rotation: consecutive steps never read inputs the previous step left in
+    # the 126 MB L2 (one set when the shard alone is larger than twice the L2).
+    l2_bytes = 126 << 20
+    n_sets = 1 if frame_bytes * n_local >= 2 * l2_bytes else min(4, 1 + (2 * l2_bytes) // max(1, frame_bytes * n_local))
+    devsets = [{k: v.to(dev, non_blocking=True).clone() for k, v in host.items()} for _ in range(n_sets)]
     torch.cuda.synchronize()
 
     def barrier():
@@ -321,35 +472,60 @@ def run_ours(args, world, rank, local):
             return float(t.item())
         return ms
 
+    def step(i, p=pipe, sets=devsets):
+        d = sets[i % len(sets)]
+        return p.infer(*(d[k] for k in INPUT_KEYS), return_pose=True)
+
+    # ---- one eager step: launch count per step, and the result the parity check uses ------------
+    step(0)
+    torch.cuda.synchronize()
+    l0 = L.plr2_launch_count()
+    res, poses = step(0)
+    torch.cuda.synchronize()
+    launches_per_step = int(L.plr2_launch_count() - l0)
+    res_eager = res.clone()
+    pipe.cuda_graph = use_graph
+
     # ---- device-resident (value) ---------------------------------------------------------------
-    for _ in range(max(args.warmup, 3)):
-        pipe.infer(*(devw[k] for k in INPUT_KEYS))
+    for i in range(max(args.warmup, 3) + n_sets):
+        step(i)
     barrier()
     if args.profile_step:
         # for `ncu --profile-from-start off`: exactly one device-resident step inside the capture range
+        pipe.cuda_graph = False
         torch.cuda.profiler.start()
-        pipe.infer(*(devw[k] for k in INPUT_KEYS))
+        step(0)
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
         return
     sampler = ClockSampler(local) if rank == 0 else None
-    launches0 = L.plr2_launch_count()
-    L.plr2_profile_begin()
+    if not use_graph:
+        L.plr2_profile_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.time()
     e0.record()
-    for _ in range(args.steps):
-        res = pipe.infer(*(devw[k] for k in INPUT_KEYS))
+    for i in range(args.steps):
+        res, poses = step(i)
     e1.record()
     barrier()
     t1 = time.time()
     ms_dev = max_over_ranks(e0.elapsed_time(e1))
     tc_ms, tc_n, tc_fl = C.c_double(), C.c_longlong(), C.c_double()
+    roofline_pass = "timed region"
+    if use_graph:
+        # the timed region replayed CUDA graphs (no per-kernel events inside a replay): bracket the same launches in an
+        # eager pass of the same steps right behind it
+        pipe.cuda_graph = False
+        L.plr2_profile_begin()
+        for i in range(args.steps):
+            step(i)
+        pipe.cuda_graph = True
+        roofline_pass = "separate eager pass of the same steps (the timed region replays CUDA graphs)"
     L.plr2_profile_end(C.byref(tc_ms), C.byref(tc_n), C.byref(tc_fl))
     tc_exec = float(L.plr2_profile_executed_flops())
-    launches = L.plr2_launch_count() - launches0
     clocks = sampler.stop(t0, t1) if sampler else None
-    value = world * frames * args.steps / (ms_dev / 1e3)
+    value = total * args.steps / (ms_dev / 1e3)
+    res = res.clone()
 
     # ---- end to end from pinned host buffers (e2e) ---------------------------------------------
     for _ in range(3):
@@ -361,27 +537,76 @@ def run_ours(args, world, rank, local):
     e1.record()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
-    e2e = world * frames * args.steps / (ms_e2e / 1e3)
-    h2d = DenseFusionPipeline.bytes_per_frame(host) * frames
-    d2h = frames * 4 + frames * 12 * 4       # per-frame distance + refined pose (R | t)
-    finite = bool(torch.isfinite(res_host).all()) and bool(torch.isfinite(res).all())
+    e2e = total * args.steps / (ms_e2e / 1e3)
+    h2d = frame_bytes * n_local
+    d2h = n_local * 4 + n_local * 12 * 4       # per-frame distance + refined pose (R | t)
+
+    # ---- weak-scaling curve (N > 1): 512 frames PER GPU, plain launches ------------------------
+    weak = None
+    if world > 1 and args.weak_steps > 0:
+        pipe.cuda_graph = False
+        wk = make_workload(args.frames, 1000 + 7919 * rank)
+        wdev = [{k: v.to(dev) for k, v in wk.items()}]
+        for i in range(3):
+            step(i, sets=wdev)
+        barrier()
+        e0.record()
+        for i in range(args.weak_steps):
+            step(i, sets=wdev)
+        e1.record()
+        barrier()
+        ms_w = max_over_ranks(e0.elapsed_time(e1))
+        weak = {"value": world * args.frames * args.weak_steps / (ms_w / 1e3), "unit": "poses/s", "scaling": "weak",
+                "frames_per_gpu_per_step": args.frames, "steps": args.weak_steps, "ms_per_step": ms_w / args.weak_steps}
+        del wdev, wk
+        torch.cuda.empty_cache()
+        pipe.cuda_graph = use_graph
+
+    # ---- C5 training step (all ranks: it contains the gradient all-reduce) ----------------------
+    train_c5 = measure_train_c5(args, world, rank, dev) if args.train_steps > 0 else None
+    barrier()
     if rank != 0:
         return
+
+    # ---- parity check of the timed results (rank 0) ---------------------------------------------
+    rel = lambda a, b: float(((a - b).abs() / b.abs().clamp_min(1e-12)).max())
+    parity = {"max_rel_err_device_path_vs_host_path": rel(res.cpu(), res_host),
+              "max_rel_err_graph_vs_eager": rel(res, res_eager) if use_graph else None,
+              "device_chunk_frames": min(args.chunk, n_local), "host_chunk_frames": host_chunk,
+              "results_finite": bool(torch.isfinite(res_host).all()) and bool(torch.isfinite(res).all())}
+    if args.check_frames > 0:
+        torch.set_num_threads(os.cpu_count() or 1)
+        pnt = {k: torch.from_numpy(v) for k, v in pn.items()}
+        rft = {k: torch.from_numpy(v) for k, v in rf.items()}
+        ids = sorted(set(int(i) for i in np.linspace(0, n_local - 1, args.check_frames)))
+        sub = {k: v[ids] for k, v in work.items()}
+        ref = torch.tensor(cpu_reference_step(sub, pnt, rft, len(ids)))     # the oracle is the checker, never the product
+        got = res.cpu()[ids]
+        parity.update({"frames_vs_cpu_oracle": ids, "max_rel_err_vs_cpu_oracle": rel(got, ref),
+                       "sym_frames_checked": int(sum(int(work["obj"][i, 0]) in SHAPE.sym_list for i in ids))})
+        parity["ok"] = bool(parity["max_rel_err_vs_cpu_oracle"] < 2e-3 and parity["max_rel_err_device_path_vs_host_path"] < 2e-3
+                            and parity["results_finite"])
+        if not parity["ok"]:
+            print("bench.py: PARITY CHECK FAILED: %s" % json.dumps(parity), file=sys.stderr, flush=True)
 
     # ---- rooflines, CPU baseline (rank 0, N == 1 only for the CPU leg) --------------------------
     achieved = tc_fl.value / (tc_ms.value / 1e3) / 1e12 if tc_ms.value > 0 else 0.0
     executed = tc_exec / (tc_ms.value / 1e3) / 1e12 if tc_ms.value > 0 else 0.0
     peak = pk["bf16_tflops_sustained"]
-    traffic = None          # dram__bytes_{read,write}.sum per launch of this kernel, from the committed ncu capture
+    traffic, traffic_src = None, None   # dram__bytes_{read,write}.sum per launch of this kernel, from the committed ncu capture
     tp = os.path.join(ROOT, "profiles", "gemm_traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("avg_dram_bytes_per_launch")
+        tj = json.load(open(tp))
+        traffic = tj.get("avg_dram_bytes_per_launch")
+        traffic_src = "profiles/gemm_traffic.json (ncu --set full capture of a 512-frame step, not measured in this run)"
     roofline = {"bound": "tensor", "kernel": "gemm_bf16x2_kernel (tcgen05 cta_group::2 kind::f16 on split-bf16 operands: 3 MMAs per "
                                              "algorithmic MAC, 2 for the pooled-only layers)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": traffic_src,
                 "executed_tflops": executed, "frac_executed": executed / peak,
                 "launches": int(tc_n.value), "avg_launch_ms": tc_ms.value / max(1, tc_n.value),
-                "share_of_step": tc_ms.value / ms_dev if ms_dev else None,
+                "share_of_step": tc_ms.value / (ms_dev if not use_graph else max(ms_dev, tc_ms.value)) if ms_dev else None,
+                "measured_over": roofline_pass,
                 "peak_source": pk["source"] + " bf16_tflops_sustained"}
     knn = knn_roofline(pk)
     cpu = None
@@ -392,34 +617,53 @@ def run_ours(args, world, rank, local):
         rate, dt = time_cpu_reference(work, pnt, rft, args.cpu_frames, 2, 1)
         cpu = {"value": rate, "unit": "poses/s", "cores": torch.get_num_threads(), "kind": "port",
                "sample": f"{args.cpu_frames} frames x 2 passes of the same workload ({dt:.1f} s; oracle: torch CPU fp32 + C/OpenMP 1-NN)"}
-        # cross-check the first frames against the oracle (the oracle is the checker, never the product)
-        ref = cpu_reference_step(work, pnt, rft, 2)
-        got = [float(x) for x in res_host[:2]]
-        cpu["check_first2_rel_err"] = [abs(a - b) / max(abs(b), 1e-12) for a, b in zip(got, ref)]
+    c2 = c3 = None
+    if world == 1 and not args.skip_configs:
+        c2 = measure_c2(pipe, dev, knn_mode)
+        c3 = measure_c3_latency(pn, rf, dev, knn_mode)
+    graph_extra = None
+    if world == 1 and not use_graph and not args.skip_configs:
+        # the same device-resident step replayed as CUDA graphs (one per input set), for comparison with `value`
+        pipe.cuda_graph = True
+        ms_g = _ev_time(lambda: step(0), args.steps, warm=3, dev=dev)
+        pipe.cuda_graph = False
+        graph_extra = {"value": total / (ms_g / 1e3), "ms_per_step": ms_g}
     with_bb = None
     if world == 1 and args.backbone_frames > 0:
-        with_bb = time_with_backbone(pipe, devw, min(args.backbone_frames, frames), dev)
+        with_bb = time_with_backbone(pipe, devsets[0], min(args.backbone_frames, n_local), dev)
     eager = None
     if world == 1 and args.eager_frames > 0:
         eager = time_gpu_eager(work, pn, rf, args.eager_frames, dev)
     line = {
         "metric": METRIC, "value": value, "unit": "poses/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16x2-split operands, f32 accumulate (f32 SIMT for small layers/losses)",
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16x2-split operands, f32 accumulate (f32 SIMT for small layers/losses)",
         "data": "synthetic",
-        "config": {"workload": "C4: YCB-shaped frames, PoseNet(out_img given)+Loss(refine)+2x(PoseRefineNet+Loss_refine ADD-S)",
-                   "frames_per_gpu_per_step": frames, "chunk_frames": args.chunk, "host_chunk_frames": args.host_chunk,
+        "config": {"workload": "C4: 512 YCB-shaped frames per step sharded 512/G over the GPUs, PoseNet(out_img given)+Loss(refine)+"
+                               "2x(PoseRefineNet+Loss_refine ADD-S)",
+                   "frames_per_step": total, "frames_per_gpu_per_step": n_local, "chunk_frames": args.chunk,
+                   "host_chunk_frames": host_chunk, "cuda_graph": use_graph,
                    "numa_bound_cpus": len(numa_cpus) if numa_cpus else None, "num_points": SHAPE.num_points,
                    "num_mesh": SHAPE.num_mesh, "num_obj": SHAPE.num_obj, "crop": [SHAPE.height, SHAPE.width],
-                   "knn_mode": args.knn, "l2": "inputs (%.0f MB per step) larger than L2" % (h2d / 1e6),
-                   "results_finite": finite},
-        "e2e": {"value": e2e, "unit": "poses/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": int(launches),
+                   "choose": "pixels of a compact object mask (datasets/ycb/dataset.py:177-184)",
+                   "knn_mode": args.knn,
+                   "l2": "%d device-resident input set(s) of %.0f MB used in rotation (> 2x the 126 MB L2 between re-reads); "
+                         "%.2f GB of activations stream through L2 per step" % (n_sets, frame_bytes * n_local / 1e6,
+                                                                               n_local * 1000 * 13.5e3 / 1e9)},
+        "e2e": {"value": e2e, "unit": "poses/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
+                "ms_per_step": ms_e2e / args.steps, "h2d_gbs_per_rank": h2d / (ms_e2e / args.steps / 1e3) / 1e9},
+        "gpu_launches": launches_per_step * args.steps,
+        "gpu_launches_note": "%d kernels of this library per step and rank (counted on an eager step; graph replays launch the same kernels)" % launches_per_step,
         "clocks": clocks,
         "roofline": roofline,
+        "parity_check": parity,
+        "weak": weak,
+        "train_c5": train_c5,
+        "c2": c2,
+        "c3_bs1_latency_ms": c3,
+        "value_cuda_graph": graph_extra,
         "roofline_knn": knn,
-        "knn_gpairs_per_s": {k: v["Gpairs_s"] for k, v in knn.items()},
+        "knn_gpairs_per_s": {k: v["Gpairs_s"] for k, v in knn.items() if "Gpairs_s" in v},
         "cpu_baseline": cpu,
         "gpu_eager_baseline": eager,
         "with_backbone": with_bb,
@@ -433,9 +677,16 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--frames", type=int, default=512, help="frames per GPU per step (config C4)")
+    ap.add_argument("--frames", type=int, default=512, help="frames per step over ALL GPUs (config C4: sharded 512/G)")
     ap.add_argument("--chunk", type=int, default=512, help="frames per launch chunk, device-resident path")
-    ap.add_argument("--host-chunk", type=int, default=64, help="frames per chunk of the host (e2e) path: H2D of chunk i+1 overlaps chunk i")
+    ap.add_argument("--host-chunk", type=int, default=0,
+                    help="frames per chunk of the host (e2e) path: H2D of chunk i+1 overlaps chunk i (0 = min(64, max(16, shard/4)))")
+    ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
+                    help="replay each chunk's launch chain as a CUDA graph (auto: shards below 256 frames)")
+    ap.add_argument("--weak-steps", type=int, default=5, help="steps of the extra weak-scaling measurement at N > 1 (0 = skip)")
+    ap.add_argument("--train-steps", type=int, default=10, help="steps of the C5 training record (0 = skip)")
+    ap.add_argument("--check-frames", type=int, default=4, help="frames of the timed result compared with the CPU oracle (rank 0)")
+    ap.add_argument("--skip-configs", action="store_true", help="skip the C2 / C3 / graph-replay side records")
     ap.add_argument("--knn", default="fast", choices=["exact", "fast"],
                     help="ranking arithmetic of the 1-NN scan fused into the ADD-S losses (ops.KNN_LOSS_DEFAULT = fast)")
     ap.add_argument("--cpu-frames", type=int, default=8, help="frames of the CPU baseline sample (0 = skip)")

@@ -77,3 +77,50 @@ def knn_reference_cpu(ref, query, k=1):
     rc = _ref.ref_knn_cpu(ref.ctypes.data, n_ref, query.ctypes.data, n_query, d, k, idx.ctypes.data)
     assert rc == 0
     return idx
+
+
+_REF_CUDA_SO = os.path.join(_HERE, "_ref", "libknn_cuda_ref.so")
+_ref_cuda = None
+
+
+def have_reference_cuda_knn():
+    return os.path.exists(_REF_CUDA_SO)
+
+
+def _ref_cuda_lib():
+    global _ref_cuda
+    if _ref_cuda is None:
+        if not os.path.exists(_REF_CUDA_SO):
+            raise FileNotFoundError(_REF_CUDA_SO + " (build with `make -C oracle` where /root/reference exists)")
+        _ref_cuda = C.CDLL(_REF_CUDA_SO)
+        _ref_cuda.ref_knn_cuda.restype = C.c_int
+        _ref_cuda.ref_knn_cuda.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 5 + [C.c_void_p, C.c_void_p]
+        _ref_cuda.ref_knn_cuda_scratch_bytes.restype = C.c_size_t
+        _ref_cuda.ref_knn_cuda_scratch_bytes.argtypes = [C.c_int, C.c_int]
+    return _ref_cuda
+
+
+def knn_reference_cuda(ref, query, k=1, scratch=None, return_dist=False):
+    """The reference's OWN CUDA kernels (lib/knn/src/cuda/knn.cu: cuComputeDistanceGlobal + cuInsertionSort through
+    knn_device, compiled unmodified for sm_100a) on torch CUDA tensors ref (B,D,n_ref), query (B,D,n_query), driven
+    like lib/knn/src/knn.h:29-41.  Returns idx (B,k,n_query) i64 1-based [, the first k rows of the distance matrix
+    of the LAST batch element].  `scratch`: optional float32 CUDA tensor of >= n_ref*n_query elements (re-used
+    across calls the way torch's caching allocator re-uses the reference's THCudaMalloc block)."""
+    import torch
+    L = _ref_cuda_lib()
+    assert ref.is_cuda and query.is_cuda and ref.dtype == torch.float32 and query.dtype == torch.float32
+    ref, query = ref.contiguous(), query.contiguous()
+    B, D, n_ref = ref.shape
+    n_query = query.shape[2]
+    if scratch is None:
+        scratch = torch.empty(n_ref * n_query, dtype=torch.float32, device=ref.device)
+    assert scratch.numel() >= n_ref * n_query
+    idx = torch.empty((B, k, n_query), dtype=torch.int64, device=ref.device)
+    with torch.cuda.device(ref.device):
+        rc = L.ref_knn_cuda(ref.data_ptr(), query.data_ptr(), idx.data_ptr(), B, D, n_ref, n_query, k,
+                            scratch.data_ptr(), torch.cuda.current_stream(ref.device).cuda_stream)
+    if rc != 0:
+        raise RuntimeError(f"reference knn.cu failed with cudaError {rc}")
+    if return_dist:
+        return idx, scratch[: k * n_query].view(k, n_query)
+    return idx

@@ -11,6 +11,16 @@ void set_error(const char *fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+int device_sm_count() {
+  static PerDeviceInt cache;
+  const int dev = current_device();
+  int n = cache.get(dev);
+  if (!n) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) { cudaGetLastError(); n = 148; }
+    cache.set(dev, n);
+  }
+  return n;
+}
 }  // namespace plr2
 
 extern "C" int plr2_abi_version(void) { return PLR2_ABI_VERSION; }

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <atomic>
 #include "../../include/plr2_b200.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
@@ -13,6 +14,25 @@ namespace plr2 {
 
 // thread-local last-error text, set by the C-ABI wrappers
 void set_error(const char *fmt, ...);
+
+// One-time host set-up (cudaFuncSetAttribute, occupancy and SM-count queries) is PER DEVICE: a process may drive
+// several GPUs (the Python layer accepts any device=).  Caches are small arrays indexed by the current device;
+// entries are written with the same value by whichever thread gets there first (forward thread / autograd worker),
+// through std::atomic so the race is benign.
+constexpr int PLR2_MAX_DEVICES = 64;
+inline int current_device() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= PLR2_MAX_DEVICES) d = 0;
+  return d;
+}
+struct PerDeviceInt {
+  std::atomic<int> v[PLR2_MAX_DEVICES];
+  PerDeviceInt() { for (auto &x : v) x.store(0, std::memory_order_relaxed); }
+  int get(int dev) const { return v[dev].load(std::memory_order_acquire); }
+  void set(int dev, int val) { v[dev].store(val, std::memory_order_release); }
+};
+// SM count of the current device (cached per device)
+int device_sm_count();
 
 // number of kernels this library has launched (plr2_launch_count)
 extern long long g_launch_count;

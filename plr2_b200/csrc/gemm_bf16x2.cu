@@ -682,16 +682,7 @@ static int make_store_map(CUtensorMap *m, void *base, bool f32, long long cols, 
   return 0;
 }
 
-static int sm_count() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+static int sm_count() { return device_sm_count(); }
 
 // Optional CUDA-event timing of every tensor-core launch (plr2_profile_begin / plr2_profile_end).
 struct TcProfile {
@@ -766,11 +757,16 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   k.w4 = g.w4; k.b4 = g.b4; k.obj = g.obj; k.num_obj = g.num_obj; k.pred_r = g.pred_r; k.pred_t = g.pred_t; k.pred_c = g.pred_c;
   { static int dbg = -1; if (dbg < 0) { const char *e = getenv("PLR2_TC_DEBUG"); dbg = e ? atoi(e) : 0; } k.debug = dbg; }
   auto kfn = gemm_bf16x2_kernel<BN, NPROD, CG>;
-  static int units_max = 0;            // per instantiation: CTAs (CG == 1) or CTA pairs (CG == 2) resident at once
+  // per instantiation AND device: CTAs (CG == 1) or CTA pairs (CG == 2) resident at once; the shared-memory
+  // attribute is a per-device property of the function
+  static PerDeviceInt units_cache;
+  const int dev = current_device();
+  int units_max = units_cache.get(dev);
   if (!units_max) {
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess) { set_error("gemm_bf16x2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
     units_max = CG == 2 ? max_pairs_resident((const void *)kfn, Cfg::SMEM_BYTES) : sm_count();
+    units_cache.set(dev, units_max);
   }
   const long long tiles = (long long)k.m_tiles * k.n_tiles * k.batch;
   const int units = (int)(tiles < units_max ? tiles : units_max);
@@ -820,8 +816,7 @@ int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
   const bool hi_only = g.a_hi_only != 0;
   if (tc_cta_group() == 2) {
     // few 256-wide tiles (M = frames problems): halve the tile so twice as many CTA pairs share the work
-    static int pairs = 0;
-    if (!pairs) { const int n = plr2_device_sm_count(); pairs = (n > 0 ? n : 148) / 2; }
+    const int pairs = sm_count() / 2;
     const long long tiles256 = (long long)((g.M + 2 * TC_BM - 1) / (2 * TC_BM)) * ((g.N + 255) / 256) * g.batch;
     static int allow_narrow = -1;
     if (allow_narrow < 0) { const char *e = getenv("PLR2_TC_NARROW"); allow_narrow = (e && e[0] == '0') ? 0 : 1; }

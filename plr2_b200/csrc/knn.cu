@@ -266,20 +266,21 @@ extern "C" int plr2_knn_f32(const float *ref, const float *query, int64_t *idx, 
     const int tile_r = min(knn_pad(n_ref), KNN_TILE_MAX);
     const size_t smem = (size_t)tile_r * sizeof(float) * (fast ? 4 : 3);
     auto kern = fast ? knn3_kernel<true> : knn3_kernel<false>;
-    static int slots[2] = {0, 0};  // resident CTAs on the device, per mode (smem: n_ref <= 1024)
-    static int sms = 0;
-    if (!sms) {
-      int dev = 0;
-      cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      cudaFuncSetAttribute(knn3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, KNN_TILE_MAX * 16);
-      cudaFuncSetAttribute(knn3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KNN_TILE_MAX * 12);
+    static PerDeviceInt slots[2];  // resident CTAs per SM of the device, per mode (smem: n_ref <= 1024)
+    static PerDeviceInt attr_set;  // the shared-memory attribute is per device
+    const int dev = current_device();
+    const int sms = device_sm_count();
+    if (!attr_set.get(dev)) {
+      cudaError_t e = cudaFuncSetAttribute(knn3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, KNN_TILE_MAX * 16);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(knn3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KNN_TILE_MAX * 12);
+      if (e != cudaSuccess) { set_error("plr2_knn_f32: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
+      attr_set.set(dev, 1);
     }
-    int per_sm = slots[fast];
+    int per_sm = slots[fast].get(dev);
     if (!per_sm || tile_r > 1024) {
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, KNN_THREADS, smem);
       if (per_sm < 1) per_sm = 1;
-      if (tile_r <= 1024) slots[fast] = per_sm;
+      if (tile_r <= 1024) slots[fast].set(dev, per_sm);
     }
     const Knn3Plan plan = knn3_plan(batch, n_query, sms * per_sm);
     dim3 grid(plan.nsplit, batch);

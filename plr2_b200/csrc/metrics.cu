@@ -230,11 +230,12 @@ extern "C" int plr2_pose_metric(const float *model_points, long long model_strid
   dim3 grid(slices, frames);
   if (adds) {
     const size_t smem = (size_t)knn_pad(n_mesh) * 3 * sizeof(float);
-    static bool attr = false;
-    if (!attr) {
+    static PerDeviceInt attr;     // per-device function attribute
+    const int dev = current_device();
+    if (!attr.get(dev)) {
       cudaError_t e = cudaFuncSetAttribute(pose_metric_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 3 * 4);
       if (e != cudaSuccess) { set_error("plr2_pose_metric: %s", cudaGetErrorString(e)); return (int)e; }
-      attr = true;
+      attr.set(dev, 1);
     }
     pose_metric_kernel<true><<<grid, PM_THREADS, smem, st>>>(model_points, model_stride, pose_a, pose_b, n_mesh, partial);
   } else {

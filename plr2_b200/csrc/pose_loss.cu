@@ -790,8 +790,7 @@ extern "C" int plr2_pose_loss_fwd(const float *pred_r, const float *pred_t, cons
   else {
     // Most slices whose grid still fits the ~3 resident blocks per SM at once (a 1.15-wave grid costs
     // almost two waves); many-wave grids use 8.
-    static int slots = 0;
-    if (!slots) { int n = plr2_device_sm_count(); slots = 3 * (n > 0 ? n : 148); }
+    const int slots = 3 * device_sm_count();
     auto blocks = [&](int S) { const int npb = (ADDI_THREADS / S) * ADDI_H; return (long long)((n_points + npb - 1) / npb) * frames; };
 #define ADDI_LAUNCH(S) do { const int npb = (ADDI_THREADS / S) * ADDI_H; dim3 gi((n_points + npb - 1) / npb, frames);   \
       add_dis_kernel<S><<<gi, ADDI_THREADS, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj,  \
@@ -875,7 +874,7 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
   const bool may_sym = sym_lut != nullptr && obj != nullptr;
   const size_t smem = may_sym ? (size_t)knn_pad(n_mesh) * sizeof(float) * (fast ? 4 : 3) : 0;
   // four queries per thread once one-query CTAs alone would fill the GPU eight times over
-  const int qpt = (long long)frames * refine_split(n_mesh, 1) >= 8LL * 3 * plr2_device_sm_count() ? REFINE_QPT_MAX : 1;
+  const int qpt = (long long)frames * refine_split(n_mesh, 1) >= 8LL * 3 * device_sm_count() ? REFINE_QPT_MAX : 1;
   const int S = refine_split(n_mesh, qpt);
   int slice = (n_mesh + S - 1) / S;
   slice = (slice + 31) / 32 * 32;               // warp granularity

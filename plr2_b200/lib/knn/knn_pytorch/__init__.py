@@ -19,10 +19,15 @@ def knn(ref, query, idx, mode=0):
         raise RuntimeError("expected scalar type Long")   # data_ptr<long>() in knn.h:24
     b, d, n_ref = ref.shape
     k, n_query = idx.shape[1], query.shape[2]
+    if not idx.is_contiguous():
+        raise RuntimeError("idx must be contiguous (written in place, knn.h:24)")
+    # bind the contiguous copies to locals: a temporary would go back to the caching allocator (and could be handed
+    # to the next .contiguous()) before the kernel that reads it has been enqueued
+    r, q = ref.contiguous(), query.contiguous()
     with torch.cuda.device(ref.device):
-        st = _cabi.lib().plr2_knn_f32(_cabi.ptr(ref.contiguous()), _cabi.ptr(query.contiguous()),
-                                      _cabi.ptr(idx), None, b, d, n_ref, n_query, k, mode, None, 0,
-                                      _cabi.stream_ptr(ref.device))
+        st = _cabi.lib().plr2_knn_f32(_cabi.ptr(r), _cabi.ptr(q), _cabi.ptr(idx), None, b, d, n_ref, n_query, k,
+                                      mode, None, 0, _cabi.stream_ptr(ref.device))
+    del r, q
     _cabi.check(st, "plr2_knn_f32")
     return 1
 

@@ -15,10 +15,11 @@ def loss_calculation(pred_r, pred_t, pred_c, target, model_points, idx, points, 
     F = pred_r.shape[0]
     assert model_points.shape[-2] == num_point_mesh, "model_points does not have num_points_mesh rows"
     lut = ops.sym_lut(sym_list, pred_r.device)
-    loss, dis, new_points, new_target, _, _, pose = ops.PoseLossFn.apply(
+    loss, dis, new_points, new_target, dis_all, _, pose = ops.PoseLossFn.apply(
         pred_r, pred_t, pred_c, target.reshape(F, num_point_mesh, 3), model_points.reshape(F, num_point_mesh, 3),
         idx, points, w, refine, lut, knn_mode)
     loss_calculation.last_pose = pose    # (F,12): R* row-major | t* of the selected hypothesis (lib/loss.py:57-60)
+    loss_calculation.last_dis_all = dis_all   # (F,N): the distance of every hypothesis (lib/loss.py:48)
     if F == 1:   # the reference returns 0-d loss and dis (lib/loss.py:49,69)
         return loss[0], dis[0], new_points, new_target
     return loss, dis, new_points, new_target
@@ -36,4 +37,5 @@ class Loss(_Loss):
         out = loss_calculation(pred_r, pred_t, pred_c, target, model_points, idx, points, w, refine,
                                self.num_pt_mesh, self.sym_list, self.knn_mode)
         self.last_pose = loss_calculation.last_pose     # extension: the pose the returned clouds were re-centred by
+        self.last_dis_all = loss_calculation.last_dis_all
         return out

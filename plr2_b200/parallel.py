@@ -27,6 +27,35 @@ def shard_frames(batch, world_size, rank):
     return {k: v[a:b] for k, v in batch.items()}
 
 
+def frame_cost(obj, sym_list, n_points, n_mesh):
+    """Relative cost of one training frame in pair evaluations: ADD-S frames search the nearest of `n_mesh` targets
+    for each of the n_points * n_mesh transformed model points (lib/loss.py:39-46), ADD frames evaluate n_points *
+    n_mesh matched pairs (lib/loss.py:48); the network part is the same for every frame (~4 GFLOP on tensor cores,
+    a small constant next to either)."""
+    pairs = n_points * n_mesh
+    return float(pairs * n_mesh) if int(obj) in sym_list else float(pairs)
+
+
+def deal_by_cost(costs, world_size):
+    """Cost-aware assignment of the frames of a global batch to ranks: frames sorted by decreasing cost (ties by
+    index) are dealt to the currently lightest rank that still has room, every rank ending with the same number of
+    frames (+-1).  Frames are independent, so any assignment is a valid data-parallel step; this one keeps the
+    ranks' step times level (the all-reduce waits for the slowest rank).  Deterministic: every rank computes the
+    same table.  Returns a list of `world_size` index lists (each ascending)."""
+    n = len(costs)
+    if world_size <= 0:
+        raise ValueError("world_size must be positive")
+    cap = [(n // world_size) + (1 if r < n % world_size else 0) for r in range(world_size)]
+    order = sorted(range(n), key=lambda i: (-float(costs[i]), i))
+    load = [0.0] * world_size
+    out = [[] for _ in range(world_size)]
+    for i in order:
+        r = min((r for r in range(world_size) if len(out[r]) < cap[r]), key=lambda r: (load[r], r))
+        out[r].append(i)
+        load[r] += float(costs[i])
+    return [sorted(ix) for ix in out]
+
+
 def gather_results(local, n_frames, group=None):
     """All-gather per-frame results (f_local, ...) of uneven shards into (n_frames, ...) on every rank."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:

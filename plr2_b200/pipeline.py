@@ -26,7 +26,7 @@ INPUT_KEYS = ("out_img", "points", "choose", "obj", "target", "model_points")
 class DenseFusionPipeline:
     def __init__(self, num_points, num_obj, num_mesh, sym_list, device="cuda", precision=ops.PREC_BF16X2,
                  knn_mode=ops.KNN_LOSS_DEFAULT, refine_iters=2, chunk_frames=512, w=0.015, refine_start=True,
-                 with_backbone=False, host_chunk_frames=64):
+                 with_backbone=False, host_chunk_frames=64, cuda_graph=False, max_graphs=8):
         self.device = torch.device(device)
         self.estimator = PoseNet(num_points, num_obj, precision=precision)
         if not with_backbone:
@@ -41,6 +41,12 @@ class DenseFusionPipeline:
         self.w = w
         self.refine_start = refine_start
         self._staging = None
+        # cuda_graph: the launch chain of a chunk (~32 kernels + the PyTorch glue around them) is captured once per
+        # (input addresses, shapes, parameter versions) and replayed; pays off where a chunk is launch-bound
+        # (bs = 1 latency, small shards of a strongly scaled batch).  Results are identical: same kernels, same order.
+        self.cuda_graph = cuda_graph
+        self.max_graphs = max_graphs
+        self._graphs = {}
 
     def load_params(self, posenet_params, refiner_params):
         """dicts name -> numpy/torch array in the reference's state-dict naming."""
@@ -63,6 +69,35 @@ class DenseFusionPipeline:
             ops.pose_compose_(pose, self.criterion_refine.last_pose)    # stays on the device (kernel (5))
         return dis, pose
 
+    def _param_signature(self):
+        return tuple((p.data_ptr(), p._version) for m in (self.estimator, self.refiner) for p in m.hot_path_parameters())
+
+    def _run_chunk(self, *args):
+        """`_chunk`, through a captured CUDA graph when enabled.  The returned tensors of a graphed chunk live in the
+        graph's memory pool and are overwritten by its next replay: callers copy them out (infer / infer_host do)."""
+        if not self.cuda_graph:
+            return self._chunk(*args)
+        key = tuple((t.data_ptr(), tuple(t.shape), t.dtype) for t in args) + (self.refine_iters, self.w, self.refine_start,
+                                                                              self._param_signature())
+        g = self._graphs.get(key)
+        if g is None:
+            if len(self._graphs) >= self.max_graphs:
+                self._graphs.pop(next(iter(self._graphs)))          # oldest capture
+            cur = torch.cuda.current_stream(self.device)
+            side = torch.cuda.Stream(device=self.device)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):                            # warm-up outside the capture: lazily created state
+                self._chunk(*args)                                   # (packed weights, workspaces, LUTs, function attributes)
+            cur.wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = self._chunk(*args)
+            # keep the inputs and the workspaces the captured kernels point at alive with the graph
+            g = (graph, out, args, (self.estimator._state.ws, self.refiner._state.ws))
+            self._graphs[key] = g
+        g[0].replay()
+        return g[1]
+
     @torch.no_grad()
     def infer(self, out_img, points, choose, obj, target, model_points, return_pose=False):
         """Device-resident inputs (F, ...).  Returns the final ADD / ADD-S distance per frame (F,) and, with
@@ -72,8 +107,8 @@ class DenseFusionPipeline:
         poses = torch.empty((F, 12), dtype=torch.float32, device=out_img.device)
         for a in range(0, F, self.chunk_frames):
             b = min(F, a + self.chunk_frames)
-            out[a:b], poses[a:b] = self._chunk(out_img[a:b], points[a:b], choose[a:b], obj[a:b], target[a:b],
-                                               model_points[a:b])
+            out[a:b], poses[a:b] = self._run_chunk(out_img[a:b], points[a:b], choose[a:b], obj[a:b], target[a:b],
+                                                   model_points[a:b])
         return (out, poses) if return_pose else out
 
     @torch.no_grad()
@@ -115,7 +150,7 @@ class DenseFusionPipeline:
             main.wait_event(self._ready[i & 1])
             s = self._staging[i & 1]
             n = b - a
-            res_dev[a:b], pose_dev[a:b] = self._chunk(*(s[k][:n] for k in INPUT_KEYS))
+            res_dev[a:b], pose_dev[a:b] = self._run_chunk(*(s[k][:n] for k in INPUT_KEYS))
             self._free[i & 1].record(main)
         res_host.copy_(res_dev, non_blocking=True)
         pose_host.copy_(pose_dev, non_blocking=True)

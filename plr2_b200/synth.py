@@ -55,10 +55,45 @@ def mesh_points(rng, m):
     return np.stack([r * np.cos(phi), r * np.sin(phi), h * z], 1).astype(np.float32)
 
 
-def make_frame(shape: Shape, seed: int, obj=None, with_image=True):
+def object_mask(rng, height, width):
+    """Synthetic object mask inside its crop, shaped like the reference's `mask = mask_label * mask_depth` cropped to
+    `get_bbox` (datasets/ycb/dataset.py:143-146,177): a compact blob that touches the four sides of the crop
+    (the crop IS the blob's bounding box, rounded up to a multiple of 40) with ~3 % invalid-depth holes."""
+    yy, xx = np.mgrid[0:height, 0:width]
+    cy, cx = (height - 1) / 2.0, (width - 1) / 2.0
+    ang = np.arctan2(yy - cy, xx - cx)
+    # superellipse radius modulated by a few low harmonics: a convex-ish silhouette filling 60-75 % of the box
+    k = rng.uniform(0.05, 0.15, 3)
+    ph = rng.uniform(0, 2 * np.pi, 3)
+    mod = 1.0 + sum(k[i] * np.cos((i + 2) * ang + ph[i]) for i in range(3))
+    ry, rx = 0.47 * height * mod, 0.47 * width * mod
+    inside = ((yy - cy) / ry) ** 4 + ((xx - cx) / rx) ** 4 <= 1.0
+    holes = rng.random((height, width)) < 0.03
+    return inside & ~holes
+
+
+def choose_from_mask(rng, mask, n):
+    """datasets/ycb/dataset.py:177-184: indices of the non-zero mask pixels of the crop, flattened row-major; more than
+    `n` -> a random subset of n keeping ascending order, fewer -> np.pad(..., 'wrap')."""
+    choose = mask.flatten().nonzero()[0]
+    if len(choose) > n:
+        c_mask = np.zeros(len(choose), dtype=int)
+        c_mask[:n] = 1
+        rng.shuffle(c_mask)
+        choose = choose[c_mask.nonzero()]
+    elif len(choose) > 0:
+        choose = np.pad(choose, (0, n - len(choose)), 'wrap')
+    else:
+        choose = np.zeros(n, dtype=np.int64)
+    return choose
+
+
+def make_frame(shape: Shape, seed: int, obj=None, with_image=True, choose_mode="uniform"):
     """One frame as a dict of numpy arrays in the reference's per-frame layout (batch dim of 1
     omitted): points (N,3), choose (N,) i64, out_img (32,H,W), target (M,3), model_points (M,3),
-    idx () i64, plus gt_R (3,3), gt_t (3,), gt_q (4,)."""
+    idx () i64, plus gt_R (3,3), gt_t (3,), gt_q (4,).  choose_mode: "uniform" = sorted random subset of the crop
+    (what the golden fixtures were generated with), "mask" = pixels of a compact object blob (separate
+    random streams, so every other array of the frame is identical in both modes)."""
     rng = _rng(seed)
     n, m = shape.num_points, shape.num_mesh
     hw = shape.height * shape.width
@@ -72,6 +107,8 @@ def make_frame(shape: Shape, seed: int, obj=None, with_image=True):
         choose = np.sort(rng.choice(hw, n, replace=False))
     else:  # wrap-pad like datasets/ycb/dataset.py:178-184
         choose = np.sort(np.resize(rng.permutation(hw), n))
+    if choose_mode == "mask":      # what the reference's loader produces: the object's pixels (bench.py workload)
+        choose = choose_from_mask(_rng(seed + 0x5eed), object_mask(_rng(seed + 0x3a5c), shape.height, shape.width), n)
     frame = {
         "points": points, "choose": choose.astype(np.int64), "target": target, "model_points": model,
         "idx": np.array(rng.integers(0, shape.num_obj) if obj is None else obj, dtype=np.int64),

@@ -136,3 +136,82 @@ def test_full_size_properties_c2():
     assert np.array_equal(idx[:, sl], KO.knn_oracle(ref, query[:, sl], 1)[0])
     fidx = run(ref, query, 1, KNN_FAST)
     assert (fidx != idx).mean() < 1e-3
+
+
+# ---------------------------------------------------------------------------------------------
+# The reference's OWN CUDA kernels (lib/knn/src/cuda/knn.cu, compiled unmodified for sm_100a into
+# oracle/_ref/libknn_cuda_ref.so by oracle/Makefile) as the witness of bit-exactness.
+needs_ref_cuda = pytest.mark.skipif(not KO.have_reference_cuda_knn(),
+                                    reason="oracle/_ref/libknn_cuda_ref.so not built (make -C oracle where /root/reference exists)")
+
+
+@needs_ref_cuda
+@pytest.mark.parametrize("n_ref,n_query", [(500, 120_000), (2300, 60_000), (17, 4099), (1, 300)])
+def test_exact_mode_bit_equal_to_reference_cuda_kernel(n_ref, n_query):
+    """knn3_kernel<EXACT>: indices AND squared distances bit-equal to cuComputeDistanceGlobal + cuInsertionSort
+    (knn.cu:36-176) run on the same B200, >= 1e5 queries, with planted exact ties (duplicated references, queries
+    sitting on references, queries equidistant from two references)."""
+    rng = np.random.default_rng(n_ref * 13 + n_query)
+    ref = (rng.standard_normal((3, n_ref)) * 0.1 + 0.7).astype(np.float32)
+    query = (rng.standard_normal((3, n_query)) * 0.1 + 0.7).astype(np.float32)
+    if n_ref >= 17:
+        ref[:, 11] = ref[:, 3]                                   # duplicated reference: index 4 (1-based) must win over 12
+        ref[:, n_ref - 1] = ref[:, 5]
+        query[:, :64] = ref[:, rng.integers(0, n_ref, 64)]       # queries on references (distance 0)
+        mid = 0.5 * (ref[:, 7] + ref[:, 9])                      # equidistant in exact arithmetic, decided by rounding
+        query[:, 64:96] = mid[:, None]
+    r = torch.from_numpy(ref).cuda()[None].contiguous()
+    q = torch.from_numpy(query).cuda()[None].contiguous()
+    ridx, rdist = KO.knn_reference_cuda(r, q, 1, return_dist=True)
+    idx, dist = knn_indices(r, q, 1, KNN_EXACT, return_dist=True)
+    torch.cuda.synchronize()
+    assert torch.equal(idx, ridx)
+    assert torch.equal(dist[0], rdist)
+    if n_ref >= 17:
+        assert int(idx[0, 0, :64].max()) <= n_ref and not bool((idx[0, 0, :96] == 12).any())
+    # and our C restatement of that arithmetic agrees with the real kernel too (pins oracle/knn_oracle.c, contract=1)
+    sl = slice(0, min(n_query, 20_000))
+    oidx, odist = KO.knn_oracle(ref, query[:, sl], 1, contract=True)
+    assert np.array_equal(ridx[0, :, sl].cpu().numpy(), oidx) and np.array_equal(rdist[:, sl].cpu().numpy(), odist)
+
+
+@needs_ref_cuda
+def test_generic_k_and_dim_equal_reference_cuda_kernel():
+    """k = 4 (dim 3) and k = 2 (dim 16) against the reference kernel: indices equal, batched."""
+    rng = np.random.default_rng(17)
+    for d, k, n_ref, n_query in ((3, 4, 300, 5000), (16, 2, 129, 3000)):
+        ref = torch.from_numpy(rng.standard_normal((2, d, n_ref)).astype(np.float32)).cuda()
+        query = torch.from_numpy(rng.standard_normal((2, d, n_query)).astype(np.float32)).cuda()
+        assert torch.equal(knn_indices(ref, query, k, KNN_EXACT), KO.knn_reference_cuda(ref, query, k))
+
+
+@needs_ref_cuda
+def test_fast_mode_gap_rule_against_reference_cuda_kernel():
+    """FAST ranking against the real reference kernel at C2 size: same neighbour wherever best and second-best
+    squared distances (from the C oracle) differ by more than 1e-6."""
+    rng = np.random.default_rng(99)
+    ref = (rng.standard_normal((3, 500)) * 0.05 + np.array([[0.1], [-0.1], [0.9]])).astype(np.float32)
+    query = (rng.standard_normal((3, 200_000)) * 0.05 + np.array([[0.1], [-0.1], [0.9]])).astype(np.float32)
+    r, q = torch.from_numpy(ref).cuda()[None], torch.from_numpy(query).cuda()[None]
+    ridx = KO.knn_reference_cuda(r, q, 1)[0].cpu().numpy()
+    fidx = knn_indices(r, q, 1, KNN_FAST)[0].cpu().numpy()
+    _, best, second = KO.knn_oracle(ref, query, 1, contract=True, want_second=True)
+    bad, decided, diff = knn_gap_ok(fidx, ridx, best, second)
+    assert bad == 0 and decided > 0.99 * query.shape[1]
+
+
+def test_reference_wrapper_entry_with_non_contiguous_inputs():
+    """knn_pytorch.knn on transposed (non-contiguous) ref AND query of equal byte size: the contiguous copies must
+    both be alive when the kernel is enqueued (a freed ref copy could be handed to query.contiguous())."""
+    from plr2_b200.lib.knn import knn_pytorch
+    rng = np.random.default_rng(5)
+    ref_t = torch.from_numpy(rng.standard_normal((2, 4000, 3)).astype(np.float32)).cuda()
+    qry_t = torch.from_numpy(rng.standard_normal((2, 4000, 3)).astype(np.float32)).cuda()
+    ref, qry = ref_t.transpose(1, 2), qry_t.transpose(1, 2)          # (2,3,4000) views, not contiguous
+    assert not ref.is_contiguous() and not qry.is_contiguous()
+    out = torch.empty(2, 1, 4000, dtype=torch.int64, device="cuda")
+    for _ in range(3):
+        assert knn_pytorch.knn(ref, qry, out) == 1
+        for b in range(2):
+            want = KO.knn_oracle(ref[b].contiguous().cpu().numpy(), qry[b].contiguous().cpu().numpy(), 1)[0]
+            assert np.array_equal(out[b].cpu().numpy(), want)

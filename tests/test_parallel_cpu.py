@@ -105,3 +105,46 @@ def test_cpulist_parser_and_numa_binding_is_optional():
     assert _parse_cpulist("") == set()
     # no CUDA device / no sysfs topology here: must be a silent no-op, never an exception
     assert bind_to_gpu_numa(0) is None
+
+
+# ---------------------------------------------------------------------------------------------
+# cost-aware assignment of the global training batch (config C5)
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("n_frames", [8, 16, 64, 61])
+def test_deal_by_cost_is_a_balanced_partition(world, n_frames):
+    sym = [12, 15, 18, 19, 20]
+    g = torch.Generator().manual_seed(n_frames * 31 + world)
+    objs = torch.randint(0, 21, (n_frames,), generator=g).tolist()
+    cost = [parallel.frame_cost(o, sym, 1000, 2300) for o in objs]
+    parts = parallel.deal_by_cost(cost, world)
+    assert len(parts) == world
+    flat = sorted(i for p in parts for i in p)
+    assert flat == list(range(n_frames))                                  # a partition: every frame exactly once
+    sizes = [len(p) for p in parts]
+    assert max(sizes) - min(sizes) <= 1                                   # same batch size per rank (+-1)
+    nsym = [sum(objs[i] in sym for i in p) for p in parts]
+    assert max(nsym) - min(nsym) <= 1                                     # symmetric (expensive) frames level across ranks
+    assert parts == parallel.deal_by_cost(cost, world)                    # deterministic: every rank computes the same table
+    assert all(p == sorted(p) for p in parts)
+
+
+def test_deal_by_cost_beats_contiguous_shards_on_a_skewed_batch():
+    sym = [12, 15, 18, 19, 20]
+    objs = [12, 15, 18, 19, 20, 12, 15, 18] + [0] * 56                    # all symmetric frames at the front
+    cost = [parallel.frame_cost(o, sym, 1000, 2300) for o in objs]
+    dealt = [sum(cost[i] for i in p) for p in parallel.deal_by_cost(cost, 8)]
+    contig = [sum(cost[a:b]) for a, b in (parallel.shard_range(64, 8, r) for r in range(8))]
+    assert max(dealt) < 0.2 * max(contig) and max(dealt) / min(dealt) < 1.01
+
+
+def test_synthetic_global_batch_composition():
+    from plr2_b200 import synth
+    from plr2_b200.train import synthetic_global_batch
+    shp = synth.Shape(32, 21, 20, 8, 8, tuple(synth.YCB_SYM))
+    for world in (1, 2, 8):
+        frames = synthetic_global_batch(shp, 8 * world)
+        nsym = sum(int(f["idx"]) in shp.sym_list for f in frames)
+        assert nsym == 2 * world                                          # one frame in four is symmetric
+        cost = [parallel.frame_cost(int(f["idx"]), shp.sym_list, 1000, 2300) for f in frames]
+        per_rank = [sum(int(frames[i]["idx"]) in shp.sym_list for i in p) for p in parallel.deal_by_cost(cost, world)]
+        assert per_rank == [2] * world

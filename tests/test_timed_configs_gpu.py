@@ -1,0 +1,214 @@
+"""GPU: parity of the kernel instantiations the TIMED configurations run (bench.py C4 / C5 / C2), which the
+small-shape tests elsewhere never reach:
+
+  * refine_loss_kernel<.,.,QPT=4>  - selected from 148 frames up at M = 2300 (csrc/pose_loss.cu, plr2_refine_loss_fwd)
+  * adds_loss_kernel at M = 2300    - mesh walked in rounds of 8 + 8 + 2 points per lane (C5 training loss)
+  * FAST ranking (the product default of the fused losses) at full C1/C2/C3 loss sizes
+  * one 512-frame chunk through DenseFusionPipeline (M = frames GEMMs with narrow tiles, > 1 round of tile slots,
+    512 000-row TMA maps)
+
+All against oracle.densefusion_oracle (lib/loss.py:12-69, lib/loss_refiner.py:12-62, lib/network.py:53-206) on the
+same seeded inputs, through the C-ABI.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import densefusion_oracle as DO
+from plr2_b200 import ops, synth
+from plr2_b200.lib.loss import Loss
+from plr2_b200.lib.loss_refiner import Loss_refine
+from tests.util import assert_close, tt
+
+pytestmark = pytest.mark.gpu
+
+MODES = [ops.KNN_EXACT, ops.KNN_FAST]
+
+
+def _refine_batch(shp, frames, seed):
+    """`frames` frames built from 8 distinct synthetic frames (mixed classes, 3 of 8 symmetric) with an individual
+    perturbed pose per frame."""
+    objs8 = [12, 3, 19, 0, 7, 20, 5, 16]
+    base = [synth.make_frame(shp, seed + i, obj=o, with_image=False) for i, o in enumerate(objs8)]
+    pick = [i % 8 for i in range(frames)]
+    rng = np.random.default_rng(seed)
+    pr = np.stack([base[i]["gt_q"] + 0.05 * rng.standard_normal(4) for i in pick]).astype(np.float32)
+    pt = np.stack([base[i]["gt_t"] + 0.005 * rng.standard_normal(3) for i in pick]).astype(np.float32)
+    return base, pick, pr, pt
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("with_grad", [False, True])
+def test_refine_loss_large_batch_four_queries_per_thread(mode, with_grad):
+    """160 frames x M = 2300: plr2_refine_loss_fwd takes the QPT = 4 instantiation (frames * 24 slices >= 8 * 3 * SMs).
+    12 sampled frames (symmetric and not) against the oracle; every frame against the one-query-per-thread
+    instantiation (the same frame evaluated alone)."""
+    shp = synth.YCB_REFINE
+    frames = 160
+    base, pick, pr, pt = _refine_batch(shp, frames, 5100)
+    st = lambda key: tt(np.stack([base[i][key] for i in pick]), "cuda")
+    tgt, mdl, pts = st("target"), st("model_points"), st("points")
+    objs = tt(np.array([int(base[i]["idx"]) for i in pick])[:, None], "cuda")
+    crit = Loss_refine(shp.num_mesh, list(shp.sym_list), mode)
+    a, b = tt(pr, "cuda", grad=with_grad), tt(pt, "cuda", grad=with_grad)
+    if with_grad:
+        dis, npts, ntgt = crit(a, b, tgt, mdl, objs, pts)
+        dis.sum().backward()
+    else:
+        with torch.no_grad():
+            dis, npts, ntgt = crit(a, b, tgt, mdl, objs, pts)
+    assert tuple(dis.shape) == (frames,)
+    # (i) the small-batch instantiation on single frames: same math, other slice order -> fp32 round-off only
+    for i in (0, 1, 2, 77, 159):
+        a1, b1 = tt(pr[i:i + 1], "cuda", grad=with_grad), tt(pt[i:i + 1], "cuda", grad=with_grad)
+        d1, np1, nt1 = crit(a1, b1, tgt[i:i + 1], mdl[i:i + 1], objs[i:i + 1], pts[i:i + 1])
+        assert_close(dis[i].detach().cpu().numpy(), d1.detach().cpu().numpy(), "dis batch vs single", rtol=1e-5, frac=1.0)
+        assert torch.equal(np1[0], npts[i]) and torch.equal(nt1[0], ntgt[i])
+    # (ii) the oracle on sampled frames
+    gtol = (lambda g: None) if mode == ops.KNN_EXACT else (lambda g: 2e-3 * float(np.abs(g).max()))
+    for i in (0, 1, 2, 3, 5, 8, 10, 45, 77, 130, 158, 159):
+        f = base[pick[i]]
+        obj = int(f["idx"])
+        oa, ob = tt(pr[i:i + 1], grad=True), tt(pt[i:i + 1], grad=True)
+        od, onp, ont, _ = DO.refine_loss(oa, ob, tt(f["target"]), tt(f["model_points"]), obj, tt(f["points"]), shp.sym_list)
+        assert_close(dis[i].detach().cpu().numpy(), od.detach().numpy(), f"dis[{i}] (obj {obj})", frac=1.0)
+        assert_close(npts[i].cpu().numpy(), onp.numpy(), "new_points")
+        assert_close(ntgt[i].cpu().numpy(), ont.numpy(), "new_target")
+        if with_grad:
+            od.backward()
+            gr, gt = oa.grad[0].numpy(), ob.grad[0].numpy()
+            assert_close(a.grad[i].cpu().numpy(), gr, "g_pred_r", rtol=2e-3, atol=gtol(gr), frac=1.0)
+            assert_close(b.grad[i].cpu().numpy(), gt, "g_pred_t", rtol=2e-3, atol=gtol(gt), frac=1.0)
+
+
+def _loss_vs_oracle(shape, obj, n_hyp, mode, seed, grad=True, refine=False):
+    fr = synth.make_frame(shape, seed, obj=obj, with_image=False)
+    preds = [p[:n_hyp] for p in synth.make_predictions(fr, seed + 1)]
+    fr = dict(fr, points=fr["points"][:n_hyp])
+    w = 0.015
+    pr, pt, pc = [tt(a, "cuda", grad=grad) for a in preds]
+    crit = Loss(shape.num_mesh, list(shape.sym_list), mode)
+    args = (tt(fr["target"], "cuda")[None], tt(fr["model_points"], "cuda")[None], tt(fr["idx"], "cuda").reshape(1, 1),
+            tt(fr["points"], "cuda")[None], w, refine)
+    if grad:
+        loss, dis, npts, ntgt = crit(pr[None], pt[None], pc[None], *args)
+        (loss + 0.5 * dis).backward()
+    else:
+        with torch.no_grad():
+            loss, dis, npts, ntgt = crit(pr[None], pt[None], pc[None], *args)
+    dis_all = crit.last_dis_all[0].cpu().numpy() if hasattr(crit, "last_dis_all") else None
+    opr, opt_, opc = [tt(a, grad=grad) for a in preds]
+    ol, od, onp, ont, ex = DO.pose_loss(opr, opt_, opc, tt(fr["target"]), tt(fr["model_points"]), obj, tt(fr["points"]),
+                                        w, refine, shape.sym_list)
+    assert_close(loss.detach().cpu().numpy(), ol.item(), "loss", frac=1.0)
+    assert_close(dis.detach().cpu().numpy(), od.item(), "dis", frac=1.0)
+    if dis_all is not None:
+        assert_close(dis_all, ex["dis"].detach().numpy(), "dis of every hypothesis", frac=1.0)
+    assert_close(npts[0].cpu().numpy(), onp.numpy(), "new_points")
+    assert_close(ntgt[0].cpu().numpy(), ont.numpy(), "new_target")
+    if grad:
+        (ol + 0.5 * od).backward()
+        # ADD-S gradients are discontinuous at equidistant targets; FAST may break a < 1e-8 tie the other way
+        # (allowed by the gap rule), which moves a hypothesis' gradient by up to ~1/M of its norm
+        tol = dict(rtol=1e-3) if mode == ops.KNN_EXACT else dict(rtol=2e-3)
+        assert_close(pr.grad.cpu().numpy(), opr.grad.numpy(), "g_pred_r", **tol)
+        assert_close(pt.grad.cpu().numpy(), opt_.grad.numpy(), "g_pred_t", **tol)
+        assert_close(pc.grad.cpu().numpy(), opc.grad.numpy(), "g_pred_c", **tol)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("grad", [False, True])
+def test_loss_adds_mesh_2300_rounds_of_8_8_2(mode, grad):
+    """Loss(refine=False) on a symmetric class at M = 2300 (num_pt_mesh_large, the C5 training shape): 128 lanes walk the
+    mesh in rounds of 8 + 8 + 2 points; 96 hypotheses keep the CPU oracle (5.1e8 pairs) under a few seconds."""
+    _loss_vs_oracle(synth.YCB_REFINE, 12, 96, mode, 7300, grad=grad)
+
+
+@pytest.mark.parametrize("m", [2300, 2600, 1920, 1153, 257])
+def test_loss_adds_round_decomposition(m):
+    """Other mesh sizes: 2600 (datasets/ycb/dataset.py:91) = 8+8+4+1 (the last lane row ragged), 1920 = 8+4+2+1,
+    1153 = 8+1+1 with a one-point tail, 257 = 2+1."""
+    shp = synth.Shape(64, 21, m, 8, 8, tuple(synth.YCB_SYM))
+    _loss_vs_oracle(shp, 15, 24, ops.KNN_FAST, 7400 + m, grad=True)
+    _loss_vs_oracle(shp, 15, 24, ops.KNN_EXACT, 7400 + m, grad=False)
+
+
+def test_loss_adds_c5_full_frame():
+    """One full C5 frame: N = 1000 hypotheses x M = 2300, symmetric class, product default ranking (FAST), forward and
+    Jacobians.  5.29e9 oracle pairs (~10 s on 8 cores)."""
+    _loss_vs_oracle(synth.YCB_REFINE, 19, 1000, ops.KNN_LOSS_DEFAULT, 7500, grad=True)
+
+
+@pytest.mark.parametrize("shape,obj,refine", [(synth.LINEMOD, 3, False), (synth.LINEMOD, 7, False),
+                                              (synth.YCB, 12, False), (synth.YCB, 5, False),
+                                              (synth.YCB_REFINE, 12, True), (synth.YCB_REFINE, 3, True)])
+def test_loss_full_size_vs_oracle_fast_ranking(shape, obj, refine):
+    """BASELINE configs C1/C2/C3 loss shapes with the product default ranking of the fused losses (FAST)."""
+    _loss_vs_oracle(shape, obj, shape.num_points, ops.KNN_FAST, 77 + obj, grad=True, refine=refine)
+
+
+def test_fast_ranking_gap_rule_full_c2_size():
+    """north_star rule at full C2 size (500 refs x 500 000 queries): FAST must return the reference neighbour wherever
+    best and second best squared distance differ by more than 1e-6; EXACT must return it everywhere.  Queries are the
+    model points transformed by all 1000 hypotheses of a C2 frame (what the fused loss scans)."""
+    from oracle import knn_oracle as KO
+    from plr2_b200.lib.knn import KNN_EXACT, KNN_FAST, knn_indices
+    from tests.util import knn_gap_ok
+    fr = synth.make_frame(synth.YCB, 11, obj=12, with_image=False)
+    pr, pt, _ = synth.make_predictions(fr, 12)
+    q = pr / np.linalg.norm(pr, axis=1, keepdims=True)
+    rot = np.stack([synth.quat_to_rot_np(v) for v in q]).astype(np.float32)          # (N,3,3)
+    pred = np.einsum("nck,jk->njc", rot, fr["model_points"]) + (fr["points"] + pt)[:, None, :]
+    query = np.ascontiguousarray(pred.reshape(-1, 3).T.astype(np.float32))           # (3, 500 000)
+    ref = np.ascontiguousarray(fr["target"].T)
+    oidx, best, second = KO.knn_oracle(ref, query, 1, contract=True, want_second=True)
+    r, qd = torch.from_numpy(ref).cuda()[None], torch.from_numpy(query).cuda()[None]
+    for mode in (KNN_EXACT, KNN_FAST):
+        idx = knn_indices(r, qd, 1, mode)[0].cpu().numpy()
+        bad, decided, diff = knn_gap_ok(idx, oidx, best, second)
+        assert bad == 0 and decided > 0.99 * query.shape[1], (mode, bad, decided, diff)
+        if mode == KNN_EXACT:
+            assert diff == 0
+
+
+@pytest.mark.parametrize("frames", [288])
+def test_pipeline_one_large_chunk_vs_oracle_chain(frames):
+    """DenseFusionPipeline.infer with chunk_frames = 512 on 288 full-size C4 frames (288 000 rows in one launch chain:
+    M = frames GEMMs on BN = 128 tiles, > 1 round of tile slots, QPT = 4 refine loss): 8 sampled frames against the
+    oracle chain of tools/train.py:182-188, and all frames against the 64-frame-chunk path of the same pipeline."""
+    from plr2_b200.pipeline import DenseFusionPipeline, INPUT_KEYS
+    shp = synth.YCB_REFINE
+    pn = synth.make_params("posenet", shp.num_obj, 1)
+    rf = synth.make_params("refiner", shp.num_obj, 2)
+    pipe = DenseFusionPipeline(shp.num_points, shp.num_obj, shp.num_mesh, shp.sym_list, device="cuda:0",
+                               precision=ops.PREC_BF16X2, chunk_frames=512, refine_iters=2)
+    pipe.load_params(pn, rf)
+    objs = [12, 3, 19, 0, 7, 20, 5, 16, 15, 18, 1, 9]
+    base = [synth.make_frame(shp, 8800 + i, obj=o) for i, o in enumerate(objs)]
+    pick = [(i * 5) % len(base) for i in range(frames)]
+    st = lambda k: tt(np.stack([base[i][k] for i in pick]), "cuda")
+    work = {"out_img": st("out_img"), "points": st("points"), "choose": st("choose")[:, None], "obj": st("idx")[:, None],
+            "target": st("target"), "model_points": st("model_points")}
+    dis, pose = pipe.infer(*(work[k] for k in INPUT_KEYS), return_pose=True)
+    pipe.chunk_frames = 64
+    dis64, pose64 = pipe.infer(*(work[k] for k in INPUT_KEYS), return_pose=True)
+    assert_close(dis.cpu().numpy(), dis64.cpu().numpy(), "512-chunk vs 64-chunk dis", rtol=1e-3, frac=0.99)
+    assert_close(pose.cpu().numpy(), pose64.cpu().numpy(), "512-chunk vs 64-chunk pose", rtol=1e-3, frac=0.99)
+    p = {k: tt(v) for k, v in pn.items()}
+    r = {k: tt(v) for k, v in rf.items()}
+    for i in (0, 1, 2, 31, 100, 200, 286, 287):
+        fr = base[pick[i]]
+        obj = int(fr["idx"])
+        with torch.no_grad():
+            pr, pt, pc, emb = DO.posenet_forward(p, tt(fr["out_img"]), tt(fr["points"]), tt(fr["choose"]), obj, shp.num_obj)
+            _, d, npts, ntgt, ex = DO.pose_loss(pr, pt, pc, tt(fr["target"]), tt(fr["model_points"]), obj, tt(fr["points"]),
+                                                0.015, True, shp.sym_list)
+            R, t = ex["R"].double(), ex["t"].double()
+            for _ in range(2):
+                rr, rt = DO.refiner_forward(r, npts, emb, obj, shp.num_obj)
+                d, npts, ntgt, ex = DO.refine_loss(rr, rt, ntgt, tt(fr["model_points"]), obj, npts, shp.sym_list)
+                t = R @ ex["t"].double() + t
+                R = R @ ex["R"].double()
+        assert_close(dis[i].cpu().numpy(), d.numpy(), f"final dis of frame {i}", rtol=2e-3, frac=1.0)
+        assert_close(pose[i, :9].cpu().numpy(), R.numpy().reshape(-1), "composed R", frac=1.0)
+        assert_close(pose[i, 9:].cpu().numpy(), t.numpy(), "composed t", frac=1.0)
