@@ -188,7 +188,7 @@ def test_fast_ranking_gap_rule_full_c2_size():
     for mode in (KNN_EXACT, KNN_FAST):
         idx = knn_indices(r, qd, 1, mode)[0].cpu().numpy()
         bad, decided, diff = knn_gap_ok(idx, oidx, best, second)
-        assert bad == 0 and decided > 0.99 * query.shape[1], (mode, bad, decided, diff)
+        assert bad == 0 and decided > 0.9 * query.shape[1], (mode, bad, decided, diff)
         if mode == KNN_EXACT:
             assert diff == 0
 
