@@ -251,7 +251,9 @@ typedef struct plr2_param_table {
 #define PLR2_NET_POSENET 0
 #define PLR2_NET_REFINER 1
 /* precision of the large contractions */
-#define PLR2_PREC_FP32 0      /* FP32 SIMT everywhere (bit-for-bit reproducible) */
+#define PLR2_PREC_FP32 0      /* FP32 SIMT everywhere.  Forward and input gradients are bit-for-bit reproducible; the weight
+                               * gradients are summed over the points by split-K partial products combined with atomicAdd,
+                               * so their last bits depend on the arrival order (relative spread ~1e-7). */
 #define PLR2_PREC_BF16X2 1    /* tcgen05 kind::f16 on split-bf16 operands (hi+lo, 3 MMAs), FP32 accumulate in TMEM.
                                * Inference keeps activations as bf16 planes.  With training != 0 activations stay FP32:
                                * the forward runs on the FP32 kernel (its ReLU signs are the masks of the backward),
@@ -271,6 +273,15 @@ int plr2_net_pack(int net, const plr2_param_table *params, int num_obj, float *p
 /* Scatter a packed gradient buffer back into per-parameter tensors (overwrites them). */
 int plr2_net_unpack_grads(int net, const float *packed_grad, const plr2_param_table *grads, int num_obj,
                           void *stream);
+
+/* Input-range status of the LAST plr2_posenet_forward / plr2_refiner_forward that used `workspace`.  torch.gather
+ * (lib/network.py:102) and index_select (lib/network.py:123-126, 202-204) raise on an out-of-range index; a kernel
+ * cannot, so the forward clamps the index (no fault), sets a flag in the first word of its workspace, and this call
+ * copies the flags to the host: it SYNCHRONISES `stream` (debug / validation use, not for the hot loop).
+ * *flags == 0: every choose index was in [0, hw) and every class index in [0, num_obj). */
+#define PLR2_STATUS_CHOOSE_RANGE 1u
+#define PLR2_STATUS_OBJ_RANGE 2u
+int plr2_net_input_status(const void *workspace, unsigned int *flags, void *stream);
 
 /* PoseNet.forward without the backbone (lib/network.py:98-132) for `frames` frames:
  *   out_img [F][32][hw] f32 backbone output; choose [F][N] i64; x [F][N][3]; obj [F] i64

@@ -57,6 +57,7 @@ inline NetLayout make_layout(int net, int O) {
 
 // Workspace (floats) for R = frames*n_points rows.
 struct NetWorkspace {
+  unsigned int *status;    // first 128 bytes of every network workspace: input-range flags of the last forward (PLR2_STATUS_*)
   float *pf, *x5, *x6, *ap, *hb, *h1, *h2, *h3, *out, *embT, *dpf, *dap, *dhb;
   float *red;              // training: [BGRAD_SLICES][BGRAD_MAX_COLS] partial column sums of the bias gradients
   // training: scratch of the tensor-core contractions (gemm_tc_f32.cu): split-bf16 planes of the two operands
@@ -75,6 +76,7 @@ inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, 
   float *p = reinterpret_cast<float *>(base);
   size_t o = 0;
   auto take = [&](size_t n) { float *r = p ? p + o : nullptr; o += al32(n); return r; };
+  W.status = reinterpret_cast<unsigned int *>(take(32));
   W.pf = take(R * 384); W.x5 = take(R * 512); W.x6 = take(R * 1024);
   W.ap = take(F * 1024);
   const size_t h1all = (size_t)L.heads * L.h1n, h2all = (size_t)L.heads * L.h2n, h3all = (size_t)L.heads * L.h3n;
@@ -103,6 +105,7 @@ inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, 
 // Workspace of the tensor-core (split-bf16) inference path.  Activations consumed by tcgen05 layers
 // are stored as two bf16 planes [2][R][width]; *_plane is the plane stride in elements.
 struct TcWorkspace {
+  unsigned int *status;                    // same place as NetWorkspace::status
   void *pf, *x5, *h1, *h2;                 // bf16 planes
   long long pf_plane, x5_plane, h1_plane, h2_plane;
   float *pool, *ap, *hb, *h3, *out;        // fp32; refiner: hb = l1 out, h3 = l2 out
@@ -118,6 +121,7 @@ inline TcWorkspace carve_tc_workspace(const NetLayout &L, void *base, int frames
   size_t o = 0;
   auto take = [&](size_t nbytes) { void *r = p ? p + o : nullptr; o += (nbytes + 127) / 128 * 128; return r; };
   const size_t h1all = (size_t)L.heads * L.h1n, h2all = (size_t)L.heads * L.h2n, h3all = (size_t)L.heads * L.h3n;
+  W.status = reinterpret_cast<unsigned int *>(take(128));
   W.pf = take(2 * R * 384 * 2); W.pf_plane = (long long)R * 384;
   W.x5 = take(R * 512 * 2); W.x5_plane = 0;          // hi plane only: conv6 reads it through the pool (hi-only operand)
   W.pool = (float *)take(((R + 31) / 32) * 2 * 1024 * sizeof(float));

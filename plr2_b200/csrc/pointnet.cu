@@ -24,7 +24,8 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
                    const float *__restrict__ out_img, const int64_t *__restrict__ choose,
                    const float *__restrict__ emb_in, const float *__restrict__ x, int N, int hw,
                    float *__restrict__ pf, __nv_bfloat16 *__restrict__ pfb, long long pf_plane,
-                   float *__restrict__ emb_out, float *__restrict__ embT, int skip_e) {
+                   float *__restrict__ emb_out, float *__restrict__ embT, int skip_e,
+                   const int64_t *__restrict__ obj, int num_obj, unsigned int *__restrict__ status) {
   __shared__ __align__(16) float sw1[64 * 4];
   __shared__ __align__(16) float swe[64 * 32];
   __shared__ float sb1[64], sbe[64];
@@ -60,7 +61,10 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
     for (int ch = 0; ch < 32; ++ch) e[ch] = 0.f;
   } else if (choose != nullptr) {
     long long c = choose[row];
-    c = c < 0 ? 0 : (c >= hw ? hw - 1 : c);       // torch.gather would raise; we clamp
+    if (c < 0 || c >= hw) {                         // torch.gather raises; a kernel cannot: flag it (plr2_net_input_status), then clamp
+      if (status != nullptr && live) atomicOr(status, (unsigned int)PLR2_STATUS_CHOOSE_RANGE);
+      c = c < 0 ? 0 : hw - 1;
+    }
     const float *src = out_img + (size_t)f * 32 * hw + c;
 #pragma unroll
     for (int ch = 0; ch < 32; ++ch) e[ch] = __ldg(src + (size_t)ch * hw);
@@ -78,6 +82,10 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
     float4 *dst = reinterpret_cast<float4 *>(embT + row * 32);
 #pragma unroll
     for (int q = 0; q < 8; ++q) dst[q] = make_float4(e[4 * q], e[4 * q + 1], e[4 * q + 2], e[4 * q + 3]);
+  }
+  if (status != nullptr && obj != nullptr && n_raw == 0) {      // one thread per frame: class index the heads will select
+    const long long o = obj[f];
+    if (o < 0 || o >= num_obj) atomicOr(status, (unsigned int)PLR2_STATUS_OBJ_RANGE);
   }
   const float px = x[row * 3], py = x[row * 3 + 1], pz = x[row * 3 + 2];
   // 8 outputs at a time: conv1 (o < 64) then e_conv1 (o >= 64)
@@ -148,21 +156,23 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
 
 int first_layer(const float *packed, const NetLayout &L, const float *out_img, const int64_t *choose,
                 const float *emb_in, const float *x, int frames, int N, int hw, float *pf, float *emb_out,
-                float *embT, cudaStream_t st) {
+                float *embT, const int64_t *obj, unsigned int *status, cudaStream_t st) {
   dim3 grid((N + FL_THREADS - 1) / FL_THREADS, frames);
   first_layer_kernel<false><<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
-                                                         out_img, choose, emb_in, x, N, hw, pf, nullptr, 0, emb_out, embT, 0);
+                                                         out_img, choose, emb_in, x, N, hw, pf, nullptr, 0, emb_out, embT, 0,
+                                                         obj, L.O, status);
   return check_launch("first_layer");
 }
 
 // same, writing the split-bf16 planes consumed by the tensor-core layers
 int first_layer_bf16(const float *packed, const NetLayout &L, const float *out_img, const int64_t *choose,
                      const float *emb_in, const float *x, int frames, int N, int hw, __nv_bfloat16 *pfb,
-                     long long pf_plane, float *emb_out, int skip_e, cudaStream_t st) {
+                     long long pf_plane, float *emb_out, int skip_e, const int64_t *obj, unsigned int *status,
+                     cudaStream_t st) {
   dim3 grid((N + FL_THREADS - 1) / FL_THREADS, frames);
   first_layer_kernel<true><<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
                                                         out_img, choose, emb_in, x, N, hw, nullptr, pfb, pf_plane, emb_out,
-                                                        nullptr, skip_e);
+                                                        nullptr, skip_e, obj, L.O, status);
   return check_launch("first_layer_bf16");
 }
 

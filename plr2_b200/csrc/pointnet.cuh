@@ -7,10 +7,11 @@ namespace plr2 {
 
 int first_layer(const float *packed, const NetLayout &L, const float *out_img, const int64_t *choose,
                 const float *emb_in, const float *x, int frames, int N, int hw, float *pf, float *emb_out,
-                float *embT, cudaStream_t st);
+                float *embT, const int64_t *obj, unsigned int *status, cudaStream_t st);
 int first_layer_bf16(const float *packed, const NetLayout &L, const float *out_img, const int64_t *choose,
                      const float *emb_in, const float *x, int frames, int N, int hw, __nv_bfloat16 *pfb,
-                     long long pf_plane, float *emb_out, int skip_e, cudaStream_t st);
+                     long long pf_plane, float *emb_out, int skip_e, const int64_t *obj, unsigned int *status,
+                     cudaStream_t st);
 int scatter_emb_grad(const float *demb, const int64_t *choose, int frames, int N, int hw, float *g_out_img,
                      cudaStream_t st);
 int segment_colsum(const float *X, long long ld, int nseg, int rows_per_seg, int ncols, float scale, float *out,

@@ -56,12 +56,21 @@ static int check_ws(const NetLayout &L, void *ws, size_t bytes, int frames, int 
   return 0;
 }
 
+// Input-range flags of a forward live in the first word of its workspace (net_layout.cuh): cleared here, set by
+// first_layer_kernel where torch.gather / index_select would have raised, read back by plr2_net_input_status.
+static int reset_status(unsigned int *status, cudaStream_t st) {
+  cudaError_t e = cudaMemsetAsync(status, 0, 128, st);
+  if (e != cudaSuccess) { set_error("network: status reset: %s", cudaGetErrorString(e)); return (int)e; }
+  return 0;
+}
+
 // Shared PointNet feature trunk: first layer, conv2/e_conv2, conv5, conv6, per-frame mean.
 static int feat_forward(const float *pk, const NetLayout &L, const NetWorkspace &W, const float *out_img,
                         const int64_t *choose, const float *emb_in, const float *x, int F, int N, int hw,
-                        float *emb_out, int training, const GemmCtx &cx, cudaStream_t st) {
+                        float *emb_out, int training, const int64_t *obj, const GemmCtx &cx, cudaStream_t st) {
   const int R = F * N;
-  RC(first_layer(pk, L, out_img, choose, emb_in, x, F, N, hw, W.pf, emb_out, training ? W.embT : nullptr, st));
+  RC(reset_status(W.status, st));
+  RC(first_layer(pk, L, out_img, choose, emb_in, x, F, N, hw, W.pf, emb_out, training ? W.embT : nullptr, obj, W.status, st));
   GemmArgs g = gemm_nt(W.pf, 384, pk + L.c2w, 64, W.pf + 128, 384, R, 128, 64);   // conv2
   g.bias = pk + L.c2b; g.relu = 1;
   RC(gemm_run(g, 1, cx, st));
@@ -96,13 +105,15 @@ static int check_tc_ws(const NetLayout &L, void *ws, size_t bytes, int frames, i
 // first layer, conv2/e_conv2, conv5, conv6 + fused per-frame average pooling -> W.ap [F,1024]
 static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspace &W, const float *out_img,
                            const int64_t *choose, const float *emb_in, const float *x, int F, int N, int hw,
-                           float *emb_out, bool reuse_emb, cudaStream_t st) {
+                           float *emb_out, bool reuse_emb, const int64_t *obj, cudaStream_t st) {
   const int R = F * N;
   const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);   // split-bf16 weights
   const long long wplane = (long long)L.total;
   __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *x5 = (__nv_bfloat16 *)W.x5;
   // the refiner's trunk is consumed through the pool only (hi-only readers below): no lo plane needed
-  RC(first_layer_bf16(pk, L, out_img, choose, emb_in, x, F, N, hw, pf, L.net == PLR2_NET_REFINER ? 0 : W.pf_plane, emb_out, reuse_emb ? 1 : 0, st));
+  RC(reset_status(W.status, st));
+  RC(first_layer_bf16(pk, L, out_img, choose, emb_in, x, F, N, hw, pf, L.net == PLR2_NET_REFINER ? 0 : W.pf_plane, emb_out, reuse_emb ? 1 : 0,
+                      obj, W.status, st));
   TcGemm g;
   g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.c2w; g.ldw = 64; g.w_plane = wplane;
   g.M = R; g.N = 128; g.K = 64; g.bias = pk + L.c2b; g.relu = 1;
@@ -143,7 +154,7 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);
   const long long wplane = (long long)L.total;
   __nv_bfloat16 *pf = (__nv_bfloat16 *)W.pf, *h1 = (__nv_bfloat16 *)W.h1, *h2 = (__nv_bfloat16 *)W.h2;
-  RC(feat_forward_tc(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, false, st));
+  RC(feat_forward_tc(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, false, obj, st));
   // per-frame bias of conv1_{r,t,c}: hb[F,1920] = ap W1[:,384:]^T + b1 (an M = frames GEMM, FP32 out)
   TcGemm g;
   g.A = (const __nv_bfloat16 *)W.apb; g.lda = 1024; g.a_plane = W.apb_plane; g.W = wb + L.h1ap; g.ldw = 1024; g.w_plane = wplane;
@@ -176,7 +187,7 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
 static int refiner_forward_tc(const float *pk, const NetLayout &L, const TcWorkspace &W, const float *x,
                               const float *emb, const int64_t *obj, int F, int N, float *pred_r, float *pred_t,
                               bool reuse_emb, cudaStream_t st) {
-  RC(feat_forward_tc(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, reuse_emb, st));
+  RC(feat_forward_tc(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, reuse_emb, obj, st));
   // Linear 1024->512 (x2 heads) as one M = frames tensor-core GEMM; 512->128 (x2) and 128->7 for the frame's
   // class in FP32 SIMT
   const __nv_bfloat16 *wb = reinterpret_cast<const __nv_bfloat16 *>(pk + L.total);
@@ -279,6 +290,15 @@ extern "C" int plr2_net_grad_regions(int net, int num_obj, size_t *early_begin, 
   return 0;
 }
 
+extern "C" int plr2_net_input_status(const void *workspace, unsigned int *flags, void *stream) {
+  if (!workspace || !flags) { set_error("plr2_net_input_status: null pointer"); return PLR2_E_NULLPTR; }
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemcpyAsync(flags, workspace, sizeof(unsigned int), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { set_error("plr2_net_input_status: %s", cudaGetErrorString(e)); return (int)e; }
+  return 0;
+}
+
 extern "C" size_t plr2_net_packed_floats(int net, int num_obj) { return 2 * make_layout(net, num_obj).total; }
 
 extern "C" size_t plr2_net_workspace_bytes(int net, int frames, int n_points, int num_obj, int training) {
@@ -324,7 +344,7 @@ extern "C" int plr2_posenet_forward(const float *packed, const float *out_img, c
   const GemmCtx cx = make_ctx(W, precision, training, n_points, true);
   const int F = frames, N = n_points, R = F * N;
   const float *pk = packed;
-  RC(feat_forward(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, training, cx, st));
+  RC(feat_forward(pk, L, W, out_img, choose, nullptr, x, F, N, hw, emb, training, obj, cx, st));
   // per-frame bias of the three conv1 heads: hb[F,1920] = ap W1[:,384:]^T + b1   (FP32 always)
   GemmArgs g = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.hb, 1920, F, 1920, 1024);
   g.bias = pk + L.h1b;
@@ -375,7 +395,7 @@ extern "C" int plr2_refiner_forward(const float *packed, const float *x, const f
   const GemmCtx cx = make_ctx(W, precision, training, n_points, true);
   const int F = frames, N = n_points;
   const float *pk = packed;
-  RC(feat_forward(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, training, cx, st));
+  RC(feat_forward(pk, L, W, nullptr, nullptr, emb, x, F, N, 0, nullptr, training, obj, cx, st));
   // Linear 1024 -> 512 (x2 heads), 512 -> 128, 128 -> num_obj*{4,3}: M = frames, FP32
   GemmArgs g = gemm_nt(W.ap, 1024, pk + L.h1ap, 1024, W.h1, 1024, F, 1024, 1024);
   g.bias = pk + L.h1b; g.relu = 1;

@@ -73,7 +73,27 @@ class PoseRefineNetFeat(_FeatBase):
         super().__init__(num_points, 384)
 
 
-class PoseNet(nn.Module):
+class _HotPathMixin:
+    """Controls shared by the two fused modules."""
+
+    @property
+    def check_inputs(self):
+        """True: every forward reads the kernels' input-range flags back (one stream synchronisation) and raises
+        IndexError where the reference's torch.gather / index_select would (lib/network.py:102,123-126,202-204);
+        False (default): out-of-range `choose` / class indices are clamped silently."""
+        return self._state.check_inputs
+
+    @check_inputs.setter
+    def check_inputs(self, value):
+        self._state.check_inputs = bool(value)
+
+    def invalidate_packed_weights(self):
+        """Call after updating parameters through `.data` (which does not bump the tensors' version counters the
+        packed-weight cache is keyed on); in-place ops on the parameters themselves are detected automatically."""
+        self._state.invalidate()
+
+
+class PoseNet(_HotPathMixin, nn.Module):
     def __init__(self, num_points, num_obj, precision=ops.PREC_BF16X2):
         super().__init__()
         self.num_points = num_points
@@ -105,7 +125,7 @@ class PoseNet(nn.Module):
         return self.forward_features(out_img, x, choose, obj)
 
 
-class PoseRefineNet(nn.Module):
+class PoseRefineNet(_HotPathMixin, nn.Module):
     def __init__(self, num_points, num_obj, precision=ops.PREC_BF16X2):
         super().__init__()
         self.num_points = num_points

@@ -175,6 +175,27 @@ class NetState:
         self.packed = None
         self.key = None
         self.ws = None
+        # True: after every forward read the input-range flags back (synchronises the stream) and raise IndexError
+        # where torch.gather / index_select would have (out-of-range `choose` / class index); default off: the
+        # kernels then clamp the index silently, like a release build
+        self.check_inputs = False
+
+    def invalidate(self):
+        """Drop the packed weights.  The cache is keyed on every parameter's (data_ptr, _version); an update made
+        through `p.data` (p.data.copy_/mul_, EMA, clipping, some older optimisers) does not bump the version counter,
+        so call this after such an update (or go through `with torch.no_grad(): p.copy_(...)`, which does)."""
+        self.key = None
+
+    def raise_on_bad_inputs(self, ws, dev, what):
+        import ctypes as C
+        flags = C.c_uint(0)
+        with torch.cuda.device(dev):
+            _cabi.check(_cabi.lib().plr2_net_input_status(_cabi.ptr(ws), C.byref(flags), _cabi.stream_ptr(dev)),
+                        "plr2_net_input_status")
+        if flags.value & 1:
+            raise IndexError(f"{what}: index out of range in gather (`choose` outside [0, H*W), lib/network.py:102)")
+        if flags.value & 2:
+            raise IndexError(f"{what}: index out of range in index_select (class index outside [0, num_obj), lib/network.py:123-126)")
 
     def packed_for(self, params, precision):
         dev = params[0].device
@@ -217,6 +238,18 @@ def _unpack_grads(net, num_obj, gpacked, params, dev):
     return views
 
 
+def _check_backward_state(ctx, what):
+    """The backward overwrites the activations kept in the workspace in place and reads the weights packed by the
+    forward: a second backward through the same graph, or parameters modified in between, cannot be honoured."""
+    if getattr(ctx, "saved", None) is None:
+        raise RuntimeError(f"{what}: backward through this forward a second time: its activations were consumed by the "
+                           "first backward (retain_graph=True is not supported by the fused path)")
+    cur = tuple((p.data_ptr(), p._version) for p in ctx.params)
+    if cur != ctx.packed_key[2:]:
+        raise RuntimeError(f"{what}: one of the parameters needed for gradient computation has been modified by an inplace "
+                           "operation between forward and backward (the packed weights of the forward no longer match)")
+
+
 class PoseNetFn(torch.autograd.Function):
     """PoseNet.forward minus the backbone (lib/network.py:98-132) for F frames.
     out_img (F,32,H,W), x (F,N,3), choose (F,1,N)|(F,N) i64, obj (F,1)|(F,) i64, then the 36 parameters
@@ -245,6 +278,8 @@ class PoseNetFn(torch.autograd.Function):
                 state.num_obj, _cabi.ptr(ws), nbytes, _cabi.ptr(pred_r), _cabi.ptr(pred_t), _cabi.ptr(pred_c),
                 _cabi.ptr(emb), int(training), precision, _cabi.stream_ptr(dev))
         _cabi.check(rc, "plr2_posenet_forward")
+        if state.check_inputs:
+            state.raise_on_bad_inputs(ws, dev, "PoseNet")
         if training:
             ctx.state, ctx.precision = state, precision
             ctx.saved = (packed.clone() if False else packed, ws, nbytes, ch, xs, ob, (F, N, H, Wd))
@@ -255,10 +290,9 @@ class PoseNetFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_r, g_t, g_c, _g_emb):
+        _check_backward_state(ctx, "PoseNet")
         packed, ws, nbytes, ch, xs, ob, (F, N, H, Wd) = ctx.saved
         state = ctx.state
-        if state.key != ctx.packed_key:     # parameters changed between forward and backward
-            packed = state.packed_for(ctx.params, ctx.precision)
         dev = xs.device
         gp = torch.empty(packed.numel() // 2, dtype=torch.float32, device=dev)
         g_img = torch.zeros((F, 32, H, Wd), dtype=torch.float32, device=dev) if ctx.needs_input_grad[3] else None
@@ -328,6 +362,8 @@ class RefinerFn(torch.autograd.Function):
                 _cabi.ptr(ws), nbytes, _cabi.ptr(pred_r), _cabi.ptr(pred_t), mode, precision,
                 _cabi.stream_ptr(dev))
         _cabi.check(rc, "plr2_refiner_forward")
+        if state.check_inputs:
+            state.raise_on_bad_inputs(ws, dev, "PoseRefineNet")
         if training:
             ctx.state, ctx.precision, ctx.params, ctx.packed_key = state, precision, params, state.key
             ctx.saved = (packed, ws, nbytes, xs, em, ob, (F, N))
@@ -335,10 +371,9 @@ class RefinerFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_r, g_t):
+        _check_backward_state(ctx, "PoseRefineNet")
         packed, ws, nbytes, xs, em, ob, (F, N) = ctx.saved
         state = ctx.state
-        if state.key != ctx.packed_key:
-            packed = state.packed_for(ctx.params, ctx.precision)
         dev = xs.device
         gp = torch.empty(packed.numel() // 2, dtype=torch.float32, device=dev)
         g_r = _f32c(g_r) if g_r is not None else torch.zeros((F, 4), dtype=torch.float32, device=dev)

@@ -358,3 +358,94 @@ def test_refiner_next_iteration_reuses_the_emb_branch_bit_identically():
         r, t = net.forward_next_iteration(x2, emb, idx)
         ref = net(x2, emb, idx)
         assert torch.equal(r, ref[0]) and torch.equal(t, ref[1])
+
+
+# ---------------------------------------------------------------------------------------------
+# boundary behaviour: input-range flags, packed-weight cache, backward guards
+def _small_posenet_inputs(shp, frames=2):
+    frs = [synth.make_frame(shp, 9100 + i, obj=3 + i) for i in range(frames)]
+    st = lambda k: tt(np.stack([f[k] for f in frs]), "cuda")
+    return st("out_img"), st("points"), st("choose")[:, None], st("idx")[:, None]
+
+
+@pytest.mark.parametrize("precision", [ops.PREC_FP32, ops.PREC_BF16X2])
+def test_out_of_range_choose_and_class_are_reported(precision):
+    """torch.gather / index_select raise on a bad index (lib/network.py:102,123-126); the kernels clamp and flag it:
+    with check_inputs the drop-in raises IndexError too, without it the call goes through (clamped)."""
+    shp = synth.Shape(256, 21, 50, 20, 20, tuple(synth.YCB_SYM))
+    net = build_posenet(shp, 5, precision)
+    img, pts, ch, ob = _small_posenet_inputs(shp)
+    net.check_inputs = True
+    with torch.no_grad():
+        net(img, pts, ch, ob)                                      # clean inputs: no error
+        bad = ch.clone(); bad[1, 0, 17] = shp.height * shp.width   # one past the end
+        with pytest.raises(IndexError, match="choose"):
+            net(img, pts, bad, ob)
+        bad[1, 0, 17] = -1
+        with pytest.raises(IndexError, match="choose"):
+            net(img, pts, bad, ob)
+        with pytest.raises(IndexError, match="class index"):
+            net(img, pts, ch, torch.tensor([[3], [shp.num_obj]], device="cuda"))
+        net(img, pts, ch, ob)                                      # flags are per forward: clean again
+        net.check_inputs = False
+        out = net(img, pts, bad, ob)                               # release behaviour: clamped, finite
+        assert all(bool(torch.isfinite(t).all()) for t in out)
+    ref = build_refiner(shp, 6, precision)
+    ref.check_inputs = True
+    emb = torch.randn(2, 32, shp.num_points, device="cuda")
+    with torch.no_grad():
+        ref(pts, emb, ob)
+        with pytest.raises(IndexError, match="class index"):
+            ref(pts, emb, torch.tensor([[-2], [3]], device="cuda"))
+
+
+def test_packed_weight_cache_and_backward_guards():
+    shp = synth.Shape(256, 21, 50, 20, 20, tuple(synth.YCB_SYM))
+    net = build_posenet(shp, 7, ops.PREC_BF16X2)
+    img, pts, ch, ob = _small_posenet_inputs(shp)
+    with torch.no_grad():
+        a = net(img, pts, ch, ob)[0].clone()
+        net.conv4_r.bias.data.add_(0.5)              # .data: no version bump -> stale packed weights until told
+        stale = net(img, pts, ch, ob)[0].clone()
+        net.invalidate_packed_weights()
+        fresh = net(img, pts, ch, ob)[0].clone()
+        assert torch.equal(a, stale)
+        assert_close((fresh - a).cpu().numpy(), np.full(tuple(a.shape), 0.5, np.float32), "bias shift", rtol=1e-4, frac=1.0)
+        net.conv4_r.bias.add_(0.25)                  # in-place on the parameter: detected by its version counter
+        assert_close((net(img, pts, ch, ob)[0] - a).cpu().numpy(), np.full(tuple(a.shape), 0.75, np.float32), "bias shift",
+                     rtol=1e-4, frac=1.0)
+    pr, pt, pc, _ = net(img, pts, ch, ob)
+    loss = pr.sum() + pt.sum() + pc.sum()
+    loss.backward(retain_graph=True)
+    with pytest.raises(RuntimeError, match="second time"):
+        loss.backward()
+    pr, pt, pc, _ = net(img, pts, ch, ob)
+    with torch.no_grad():
+        net.conv1_r.weight.mul_(1.01)                # modified between forward and backward
+    with pytest.raises(RuntimeError, match="modified by an inplace operation"):
+        (pr.sum() + pt.sum() + pc.sum()).backward()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_one_process_two_devices():
+    """Function attributes (232 KB of dynamic shared memory for the tcgen05 GEMM, the k-NN tile) and occupancy figures
+    are per DEVICE: the same process must be able to run the whole pipeline on cuda:0 and then on cuda:1."""
+    from plr2_b200.lib.knn import knn_indices
+    from plr2_b200.pipeline import DenseFusionPipeline, INPUT_KEYS
+    shp = synth.Shape(1000, 21, 2300, 40, 40, tuple(synth.YCB_SYM))
+    pn = synth.make_params("posenet", shp.num_obj, 31)
+    rf = synth.make_params("refiner", shp.num_obj, 32)
+    frs = [synth.make_frame(shp, 300 + i, obj=o) for i, o in enumerate([12, 3, 19])]
+    res = []
+    for dev in ("cuda:0", "cuda:1"):
+        pipe = DenseFusionPipeline(shp.num_points, shp.num_obj, shp.num_mesh, shp.sym_list, device=dev, chunk_frames=4)
+        pipe.load_params(pn, rf)
+        st = lambda k: tt(np.stack([f[k] for f in frs]), dev)
+        work = {"out_img": st("out_img"), "points": st("points"), "choose": st("choose")[:, None], "obj": st("idx")[:, None],
+                "target": st("target"), "model_points": st("model_points")}
+        res.append(pipe.infer(*(work[k] for k in INPUT_KEYS)).cpu())
+        rng = np.random.default_rng(1)
+        ref = torch.from_numpy(rng.standard_normal((1, 3, 5000)).astype(np.float32)).to(dev)     # > 3072 refs: large smem tile
+        qry = torch.from_numpy(rng.standard_normal((1, 3, 4000)).astype(np.float32)).to(dev)
+        res.append(knn_indices(ref, qry, 1).cpu())
+    assert torch.equal(res[0], res[2]) and torch.equal(res[1], res[3])
