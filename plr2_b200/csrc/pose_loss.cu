@@ -3,6 +3,7 @@
 // that neither the (N, M, 3) prediction tensor nor the KNN index tensor is ever materialised.
 // Reference: lib/loss.py:12-69, lib/loss_refiner.py:12-62.
 #include "knn_core.cuh"
+#include <stdlib.h>
 namespace plr2 {
 
 // ---------------------------------------------------------------------------------------------
@@ -286,6 +287,9 @@ __device__ __forceinline__ void acc_block_reduce(Acc &A, float *red) {
 }
 
 // Stage the M target points of one frame as the SoA reference tile of the 1-NN scan.
+// [A coalesced float4 read of the AoS rows scattered into the SoA arrays, with |r-c|^2 in a second pass, was measured
+// SLOWER than this scalar form (all-symmetric 512 x 2300^2: 546 -> 565 us): the three strided loads per point already
+// overlap across the loop iterations, the scatter's index arithmetic and the extra barrier do not pay.]
 template <bool FAST>
 __device__ __forceinline__ void stage_targets(const float *__restrict__ tb, int M, int Mp, float *sx,
                                               float *sy, float *sz, float *sw, float cx, float cy,
@@ -674,19 +678,28 @@ refine_loss_kernel(const float *__restrict__ pred_r, const float *__restrict__ p
     s_last = atomicAdd(counters + f, 1u) == (unsigned)(S - 1);
   }
   __syncthreads();
-  if (s_last && threadIdx.x == 0) {
+  if (s_last && threadIdx.x < 13) {
+    // lane c sums component c of the S partial records in slice order (deterministic); the loads of a lane are
+    // independent, so they are issued eight at a time instead of one L2 round trip per slice
     __threadfence();
-    acc_zero(A);
-    for (int r = 0; r < S; ++r) {                 // fixed slice order
-      const float *rp = partials + ((size_t)f * S + r) * 13;
-      A.dis += __ldcg(rp);
-      if (JAC) {
+    const float *rp = partials + (size_t)f * S * 13 + threadIdx.x;
+    float tot = 0.f;
+    for (int r0 = 0; r0 < S; r0 += 8) {
+      float v[8];
 #pragma unroll
-        for (int i = 0; i < 3; ++i) A.gs[i] += __ldcg(rp + 1 + i);
+      for (int u = 0; u < 8; ++u) v[u] = r0 + u < S ? __ldcg(rp + (size_t)(r0 + u) * 13) : 0.f;
 #pragma unroll
-        for (int i = 0; i < 9; ++i) A.G[i] += __ldcg(rp + 4 + i);
-      }
+      for (int u = 0; u < 8; ++u) tot += v[u];
     }
+    red[threadIdx.x] = tot;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    A.dis = red[0];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) A.gs[i] = red[1 + i];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) A.G[i] = red[4 + i];
     counters[f] = 0;
     const float invM = 1.0f / (float)M;
     dis[f] = A.dis * invM;
@@ -788,16 +801,35 @@ extern "C" int plr2_pose_loss_fwd(const float *pred_r, const float *pred_t, cons
   if (jac)
     add_loss_kernel<true><<<g1, ADD_SLICES * ADD_NPB, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, n_points, n_mesh, may_sym ? 1 : 0, dis, jac_r, jac_t);
   else {
-    // Most slices whose grid still fits the ~3 resident blocks per SM at once (a 1.15-wave grid costs
-    // almost two waves); many-wave grids use 8.
+    // Mesh slices per hypothesis group, S in {16, 8, 4, 2}: a block covers (256 / S) * 4 hypotheses, ~3 blocks are
+    // resident per SM.  Cost model fitted to measurements (64 frames: 121 / 131 / 131 / 143 us for S = 16 / 8 / 4 / 2;
+    // 512 frames: 795 / 755 / 737 / 738): waves(S) / S for the wave quantisation, times (1 + 0.02 S) for the mesh tile
+    // every block re-stages; grids of many waves take S = 4.
     const int slots = 3 * device_sm_count();
     auto blocks = [&](int S) { const int npb = (ADDI_THREADS / S) * ADDI_H; return (long long)((n_points + npb - 1) / npb) * frames; };
 #define ADDI_LAUNCH(S) do { const int npb = (ADDI_THREADS / S) * ADDI_H; dim3 gi((n_points + npb - 1) / npb, frames);   \
       add_dis_kernel<S><<<gi, ADDI_THREADS, 0, st>>>(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj,  \
                                                      n_points, n_mesh, may_sym ? 1 : 0, dis); } while (0)
-    if (blocks(8) <= slots || blocks(8) >= 4LL * slots) ADDI_LAUNCH(8);
-    else if (blocks(4) <= slots) ADDI_LAUNCH(4);
-    else ADDI_LAUNCH(2);
+    static int force_s = -1;           // PLR2_ADDI_S: tuning experiments only
+    if (force_s < 0) { const char *e = getenv("PLR2_ADDI_S"); force_s = e ? atoi(e) : 0; }
+    if (force_s == 16) ADDI_LAUNCH(16);
+    else if (force_s == 8) ADDI_LAUNCH(8);
+    else if (force_s == 4) ADDI_LAUNCH(4);
+    else if (force_s == 2) ADDI_LAUNCH(2);
+    else {
+      int best_s = 4;
+      if (blocks(4) < 4LL * slots) {
+        double best_c = 1e30;
+        for (int S = 16; S >= 2; S >>= 1) {
+          const double c = (double)((blocks(S) + slots - 1) / slots) / S * (1.0 + 0.02 * S);
+          if (c < best_c) { best_c = c; best_s = S; }
+        }
+      }
+      if (best_s == 16) ADDI_LAUNCH(16);
+      else if (best_s == 8) ADDI_LAUNCH(8);
+      else if (best_s == 4) ADDI_LAUNCH(4);
+      else ADDI_LAUNCH(2);
+    }
 #undef ADDI_LAUNCH
   }
   if (may_sym) {
@@ -873,8 +905,12 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
   const bool fast = knn_mode == PLR2_KNN_FAST, jac = jac_r != nullptr;
   const bool may_sym = sym_lut != nullptr && obj != nullptr;
   const size_t smem = may_sym ? (size_t)knn_pad(n_mesh) * sizeof(float) * (fast ? 4 : 3) : 0;
-  // four queries per thread once one-query CTAs alone would fill the GPU eight times over
-  const int qpt = (long long)frames * refine_split(n_mesh, 1) >= 8LL * 3 * device_sm_count() ? REFINE_QPT_MAX : 1;
+  // queries per thread: 4 once one-query CTAs alone would fill the GPU eight times over, 2 for medium batches (measured at
+  // 64 frames, 5 of 16 symmetric: 61 / 51 / 65 us for 1 / 2 / 4), 1 for a handful of frames (most CTAs, shortest critical path)
+  int qpt = (long long)frames * refine_split(n_mesh, 1) >= 8LL * 3 * device_sm_count() ? REFINE_QPT_MAX : (frames >= 24 ? 2 : 1);
+  static int force_q = -1;             // PLR2_REFINE_QPT: tuning experiments only
+  if (force_q < 0) { const char *e = getenv("PLR2_REFINE_QPT"); force_q = e ? atoi(e) : 0; }
+  if (force_q == 1 || force_q == 2 || force_q == 4) qpt = force_q;
   const int S = refine_split(n_mesh, qpt);
   int slice = (n_mesh + S - 1) / S;
   slice = (slice + 31) / 32 * 32;               // warp granularity
@@ -888,6 +924,7 @@ extern "C" int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t, co
 #define REFINE_LAUNCH(FASTV, JACV)                                                               \
   do {                                                                                           \
     if (qpt == 1) PLR2_LAUNCH_ADDS3(refine_loss_kernel, FASTV, JACV, 1, grid, REFINE_THREADS, smem, st, ARGS);                \
+    else if (qpt == 2) PLR2_LAUNCH_ADDS3(refine_loss_kernel, FASTV, JACV, 2, grid, REFINE_THREADS, smem, st, ARGS);           \
     else PLR2_LAUNCH_ADDS3(refine_loss_kernel, FASTV, JACV, REFINE_QPT_MAX, grid, REFINE_THREADS, smem, st, ARGS);            \
   } while (0)
   if (fast && jac) REFINE_LAUNCH(true, true);

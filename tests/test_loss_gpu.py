@@ -142,11 +142,11 @@ def test_refine_loss_full_size_vs_oracle(obj):
     assert_close(b.grad.cpu().numpy(), ob.grad.numpy(), "g_pred_t", frac=1.0)
 
 
-@pytest.mark.parametrize("frames", [2, 64, 150])
+@pytest.mark.parametrize("frames", [2, 150, 200, 450])
 def test_inference_add_kernel_slice_variants(frames):
-    """The no-grad ADD path picks 8, 4 or 2 mesh slices per hypothesis group from the grid size
-    (frames = 2 / 64 / 150 at N = 1000); every variant must agree with the autograd path's kernel
-    (IEEE sqrt) and with the oracle."""
+    """The no-grad ADD path picks 16, 8, 2 or 4 mesh slices per hypothesis group from the grid size
+    (frames = 2 / 150 / 200 / 450 at N = 1000 on 148 SMs); every variant must agree with the autograd path's
+    kernel (IEEE sqrt) and with the oracle."""
     shp = synth.Shape(1000, 21, 300, 20, 20, tuple(synth.YCB_SYM))
     base = [synth.make_frame(shp, 600 + i, obj=o, with_image=False) for i, o in enumerate([3, 12, 0, 19])]
     prs = [synth.make_predictions(f, 650 + i) for i, f in enumerate(base)]
