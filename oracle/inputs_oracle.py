@@ -6,9 +6,11 @@ numpy restatement of the reference's per-frame input step, stat
     pointcloud        <- datasets/ycb/dataset.py:186-196  (= src/loaders_v2/dataset_ycb.py:108-119)
     transform_target  <- datasets/ycb/dataset.py:215-219,229
 
-The reference's dataset classes need the YCB-Video files on disk and cannot be instantiated here; these
-functions are the same numpy calls on explicit arrays (numpy itself is the third-party arithmetic, so the
-float32/float64 promotion rules are the reference's own).  xmap holds the row index and ymap the column index
+PINNED: tests/golden/make_inputs_golden.py runs the reference's OWN loader (PoseDataset.__getitem__ and get_bbox,
+imported from /root/reference) on seeded synthetic YCB-Video files and commits its outputs
+(tests/golden/inputs_ycb.npz); tests/test_inputs_golden.py checks these functions against them exactly (box, choose
+and the float32 cloud bit for bit).  The functions are the loader's numpy calls on explicit arrays (numpy itself is
+the third-party arithmetic, so the float32/float64 promotion rules are the reference's own).  xmap holds the row index and ymap the column index
 (dataset.py:83-84).
 """
 import numpy as np
