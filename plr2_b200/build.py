@@ -15,6 +15,8 @@ FLAGS = [
 ]
 if os.environ.get("PLR2_PTXAS_V"):
     FLAGS += ["-Xptxas", "-v"]
+if os.environ.get("PLR2_EXTRA_NVCC_FLAGS"):          # tuning experiments (tools/knn_variants.sh): -D knobs of the kernels
+    FLAGS += os.environ["PLR2_EXTRA_NVCC_FLAGS"].split()
 
 
 def sources():

@@ -24,8 +24,18 @@
 
 namespace plr2 {
 
-constexpr int KNN_THREADS = 128;
-constexpr int KNN_QPT = 8;          // queries per lane in a full round
+// Tuning knobs (compile-time; the defaults are the shipped configuration, tools/knn_variants.sh sweeps them)
+#ifndef PLR2_KNN_THREADS
+#define PLR2_KNN_THREADS 128
+#endif
+#ifndef PLR2_KNN_MINB
+#define PLR2_KNN_MINB 4
+#endif
+#ifndef PLR2_KNN_QPT
+#define PLR2_KNN_QPT 8
+#endif
+constexpr int KNN_THREADS = PLR2_KNN_THREADS;
+constexpr int KNN_QPT = PLR2_KNN_QPT;   // queries per lane in a full round
 constexpr int KNN_TILE_MAX = 4096;  // references per smem tile (64 KB in FAST mode)
 
 template <bool FAST>
@@ -128,7 +138,7 @@ __device__ __forceinline__ void knn3_round(float *sx, float *sy, float *sz, floa
 }
 
 template <bool FAST>
-__global__ void __launch_bounds__(KNN_THREADS, 4)
+__global__ void __launch_bounds__(KNN_THREADS, PLR2_KNN_MINB)
 knn3_kernel(const float *__restrict__ ref, const float *__restrict__ query,
                      int64_t *__restrict__ idx, float *__restrict__ dist, int n_ref, int n_query,
                      int part, int tile_r) {

@@ -7,6 +7,10 @@
 namespace plr2 {
 
 constexpr int KNN_CHUNK = 16;  // references per bookkeeping chunk (index recovery granularity)
+#ifndef PLR2_KNN_UNROLL
+#define PLR2_KNN_UNROLL 2
+#endif
+constexpr int KNN_SCAN_UNROLL = PLR2_KNN_UNROLL;   // chunks per unrolled iteration of the scan loop (tuning knob)
 
 __host__ __device__ constexpr int knn_pad(int n) { return (n + KNN_CHUNK - 1) / KNN_CHUNK * KNN_CHUNK; }
 
@@ -56,7 +60,7 @@ __device__ __forceinline__ void nn_scan(const float *__restrict__ sx, const floa
   if (nchunk <= 0) return;
   NnRefs4<FAST> cur, nxt;
   cur.load(sx, sy, sz, sw, 0);
-#pragma unroll 2
+#pragma unroll KNN_SCAN_UNROLL
   for (int c = 0; c < nchunk; ++c) {
     float m[QPT];
 #pragma unroll
