@@ -1,6 +1,7 @@
 // C-ABI housekeeping: version, last-error text, device query.
 #include "common.cuh"
 #include <stdarg.h>
+#include <stdlib.h>
 
 namespace plr2 {
 static thread_local char g_err[512] = "";
@@ -10,6 +11,16 @@ void set_error(const char *fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+bool infer_fp16() {
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("PLR2_INFER_FMT"); v = (e && e[0] == 'b') ? 0 : 1; }
+  return v != 0;
+}
+int infer_conv6_nprod() {
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("PLR2_CONV6_NPROD"); v = e ? atoi(e) : 2; if (v != 1) v = 2; }
+  return v;
 }
 int device_sm_count() {
   static PerDeviceInt cache;

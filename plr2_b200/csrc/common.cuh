@@ -33,6 +33,19 @@ struct PerDeviceInt {
 };
 // SM count of the current device (cached per device)
 int device_sm_count();
+// Operand format of the INFERENCE tensor-core path (activation planes, packed weight planes): IEEE fp16 hi/lo
+// (2 x 11 = 22 mantissa bits; default) or bf16 hi/lo (16 bits; PLR2_INFER_FMT=bf16, the round-1 format).  Same
+// layout and MMA rate; the refiner's poses come out 10x closer to FP32, PoseNet's per-point outputs 3-4x
+// (profiles/r2_precision_sweep*.txt).
+// Values: activations are post-ReLU O(1e-3..1e2), weights O(1e-2): inside fp16's range; lo parts fall into fp16
+// subnormals (absolute spacing 6e-8), which tcgen05 multiplies exactly.  The training path keeps bf16 planes
+// (gradients span more than fp16's range).
+bool infer_fp16();
+// Products per MAC of conv6 on the inference path: 2 = X_hi (W_hi + W_lo) (default), 1 = X_hi W_hi (PLR2_CONV6_NPROD=1,
+// experiment only: measured -0.40 ms of a 8.27 ms step - the layer turns shared-memory/L2 bound at 0.79 of the MMA
+// peak instead of halving - while the refiner's pose error grows 20x to 1e-4 of its largest component: the weight
+// rounding is the same for every point and does not average out in the pool)
+int infer_conv6_nprod();
 
 // number of kernels this library has launched (plr2_launch_count)
 extern long long g_launch_count;

@@ -19,6 +19,7 @@
 #include "tc_ptx.cuh"
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdlib.h>
 #include <vector>
 
@@ -36,7 +37,8 @@ constexpr int TC_SLAB_BYTES = 2048;                    // one 32-row x 16-column
 constexpr int TC_SLABS = 2;                            // slabs per epilogue warp (TMA store of one in flight while the next fills)
 static_assert(TC_EPI_FLOATS * 4 <= TC_SLABS * TC_SLAB_BYTES, "fallback transpose slab fits");
 
-// BN = output-tile width, NPROD = 3 (hi+lo activations) | 2 (hi-only activations: X_hi W_hi + X_hi W_lo),
+// BN = output-tile width, NPROD = 3 (hi+lo activations) | 2 (hi-only activations: X_hi W_hi + X_hi W_lo) |
+// 1 (single product X_hi W_hi: neither lo plane is loaded),
 // CG = 1 (one CTA per tile of 128 rows) | 2 (CTA pair, cta_group::2: one 256-row tile per pair, each CTA
 // stages its own 128 rows of X and HALF of the W tile, so the L2->smem traffic per FLOP drops by a third
 // and a third pipeline stage fits).
@@ -45,7 +47,8 @@ template <int BN, int NPROD, int CG> struct TcCfg {
   static constexpr int B_ROWS = BN / CG;                       // W rows staged by this CTA
   static constexpr int B_BYTES = B_ROWS * TC_BK * 2;
   static constexpr int A_PLANES = NPROD == 3 ? 2 : 1;
-  static constexpr int STAGE_BYTES = A_PLANES * A_BYTES + 2 * B_BYTES;
+  static constexpr int B_PLANES = NPROD == 1 ? 1 : 2;
+  static constexpr int STAGE_BYTES = A_PLANES * A_BYTES + B_PLANES * B_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;                      // two accumulator stages
   static constexpr int EPI_BYTES = TC_EPI_WARPS * TC_SLABS * TC_SLAB_BYTES;   // per-warp rings of output slabs
   static constexpr int BIAS_BYTES = 2 * BN * 4;                             // [frame a|b][BN] staged bias of the current tile
@@ -71,9 +74,26 @@ struct TcKernelArgs {
   float *pool;                   // [ceil(M/32)][2][N]
   const float *w4, *b4; const int64_t *obj; int num_obj;   // TC_OUT_HEAD
   float *pred_r, *pred_t, *pred_c;
+  int fp16;                      // operand planes (and TC_OUT_BF16X2 outputs) are IEEE fp16 hi/lo instead of bf16 hi/lo
   int tma_store;                 // tile outputs leave through TMA stores (maps tmC_*)
   int debug;                     // PLR2_TC_DEBUG (timing experiments only): 1 = no global stores, 2 = no epilogue work
 };
+
+// v = hi + lo with hi = round(v), lo = round(v - hi), two values packed per 32-bit word
+__device__ __forceinline__ void split2_bf16(float a, float b, uint32_t &hi, uint32_t &lo) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  hi = *reinterpret_cast<const uint32_t *>(&h);
+  const float h0 = __uint_as_float(hi << 16), h1 = __uint_as_float(hi & 0xffff0000u);
+  const __nv_bfloat162 l = __floats2bfloat162_rn(a - h0, b - h1);
+  lo = *reinterpret_cast<const uint32_t *>(&l);
+}
+__device__ __forceinline__ void split2_f16(float a, float b, uint32_t &hi, uint32_t &lo) {
+  const __half2 h = __floats2half2_rn(a, b);
+  hi = *reinterpret_cast<const uint32_t *>(&h);
+  const float2 hf = __half22float2(h);
+  const __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
+  lo = *reinterpret_cast<const uint32_t *>(&l);
+}
 
 template <int BN, int NPROD, int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -147,13 +167,13 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
             tma_load_2d_cg2(sA, &tmA_hi, bar, ka, m0);
             if (NPROD == 3) tma_load_2d_cg2(sA + Cfg::A_BYTES, &tmA_lo, bar, ka, m0);
             tma_load_2d_cg2(sB, &tmB_hi, bar, kw, rw);
-            tma_load_2d_cg2(sB + Cfg::B_BYTES, &tmB_lo, bar, kw, rw);
+            if (NPROD != 1) tma_load_2d_cg2(sB + Cfg::B_BYTES, &tmB_lo, bar, kw, rw);
           } else {
             mbar_arrive_expect_tx(full_bar + stage, Cfg::STAGE_BYTES);
             tma_load_2d(sA, &tmA_hi, full_bar + stage, ka, m0);
             if (NPROD == 3) tma_load_2d(sA + Cfg::A_BYTES, &tmA_lo, full_bar + stage, ka, m0);
             tma_load_2d(sB, &tmB_hi, full_bar + stage, kw, rw);
-            tma_load_2d(sB + Cfg::B_BYTES, &tmB_lo, full_bar + stage, kw, rw);
+            if (NPROD != 1) tma_load_2d(sB + Cfg::B_BYTES, &tmB_lo, full_bar + stage, kw, rw);
           }
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
@@ -162,7 +182,9 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
     if (lane == 0 && rank == 0) {
-      constexpr uint32_t idesc_full = make_idesc_bf16(TC_BM * CG, BN), idesc_half = make_idesc_bf16(TC_BM * CG, BN / 2);
+      // operand planes are bf16 (training scratch, stand-alone entry) or fp16 (inference activations / packed weights)
+      const uint32_t idesc_full = g.fp16 ? make_idesc_f16(TC_BM * CG, BN) : make_idesc_bf16(TC_BM * CG, BN);
+      const uint32_t idesc_half = g.fp16 ? make_idesc_f16(TC_BM * CG, BN / 2) : make_idesc_bf16(TC_BM * CG, BN / 2);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
       for (int it = 0, t; (t = tile_of(it)) < num_tiles; ++it) {
@@ -182,12 +204,12 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
             const uint64_t adv = static_cast<uint64_t>(k * 2);   // 32 bytes >> 4 inside the swizzle atom
             if (CG == 2) {
               if (NPROD == 3) mma_f16_cg2(tmem_d, a_lo + adv, b_hi + adv, idesc, (kb | k) != 0);
-              mma_f16_cg2(tmem_d, a_hi + adv, b_lo + adv, idesc, NPROD == 3 ? 1 : (kb | k) != 0);
-              mma_f16_cg2(tmem_d, a_hi + adv, b_hi + adv, idesc, 1);
+              if (NPROD != 1) mma_f16_cg2(tmem_d, a_hi + adv, b_lo + adv, idesc, NPROD == 3 ? 1 : (kb | k) != 0);
+              mma_f16_cg2(tmem_d, a_hi + adv, b_hi + adv, idesc, NPROD == 1 ? (kb | k) != 0 : 1);
             } else {
               if (NPROD == 3) mma_f16(tmem_d, a_lo + adv, b_hi + adv, idesc, (kb | k) != 0);
-              mma_f16(tmem_d, a_hi + adv, b_lo + adv, idesc, NPROD == 3 ? 1 : (kb | k) != 0);
-              mma_f16(tmem_d, a_hi + adv, b_hi + adv, idesc, 1);
+              if (NPROD != 1) mma_f16(tmem_d, a_hi + adv, b_lo + adv, idesc, NPROD == 3 ? 1 : (kb | k) != 0);
+              mma_f16(tmem_d, a_hi + adv, b_hi + adv, idesc, NPROD == 1 ? (kb | k) != 0 : 1);
             }
           }
           if (CG == 2) mma_commit_cg2(empty_bar + stage, 3); else mma_commit(empty_bar + stage);   // smem slot reusable
@@ -374,13 +396,12 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
             if (lane == 0) { if (g.debug != 1) tma_store_2d(&tmC_hi, slab, ncol, rbase); bulk_commit(); }
           } else {
             uint32_t hi[8], lo[8];
+            if (g.fp16) {
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const __nv_bfloat162 h = __floats2bfloat162_rn(a[2 * q], a[2 * q + 1]);
-              hi[q] = *reinterpret_cast<const uint32_t *>(&h);
-              const float h0 = __uint_as_float(hi[q] << 16), h1 = __uint_as_float(hi[q] & 0xffff0000u);
-              const __nv_bfloat162 l = __floats2bfloat162_rn(a[2 * q] - h0, a[2 * q + 1] - h1);
-              lo[q] = *reinterpret_cast<const uint32_t *>(&l);
+              for (int q = 0; q < 8; ++q) split2_f16(a[2 * q], a[2 * q + 1], hi[q], lo[q]);
+            } else {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) split2_bf16(a[2 * q], a[2 * q + 1], hi[q], lo[q]);
             }
             const bool want_lo = g.c_plane != 0;          // c_plane == 0: the consumer only reads the hi plane
             uint8_t *slab = slabs + (slab_i++ % TC_SLABS) * TC_SLAB_BYTES;
@@ -506,11 +527,8 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
             }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              const __nv_bfloat162 h = __floats2bfloat162_rn(a[2 * q], a[2 * q + 1]);
-              hi[q] = *reinterpret_cast<const uint32_t *>(&h);
-              const float h0 = __uint_as_float(hi[q] << 16), h1 = __uint_as_float(hi[q] & 0xffff0000u);
-              const __nv_bfloat162 l = __floats2bfloat162_rn(a[2 * q] - h0, a[2 * q + 1] - h1);
-              lo[q] = *reinterpret_cast<const uint32_t *>(&l);
+              if (g.fp16) split2_f16(a[2 * q], a[2 * q + 1], hi[q], lo[q]);
+              else split2_bf16(a[2 * q], a[2 * q + 1], hi[q], lo[q]);
             }
             if (row < g.M && g.debug != 1) {
               __nv_bfloat16 *dh = g.Cb + (long long)row * g.ldcb + z * g.c_col_z + n;
@@ -560,7 +578,7 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
 // is only ever read for the group that straddles the start of frame f (the GEMM epilogue writes it only then).
 __global__ void __launch_bounds__(256)
 pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, int ncols, float *__restrict__ ap,
-                   __nv_bfloat16 *__restrict__ apb, long long apb_plane) {
+                   __nv_bfloat16 *__restrict__ apb, long long apb_plane, int fp16) {
   __shared__ float4 red[4][64];
   const int f = blockIdx.y;
   const int cl = threadIdx.x & 63, gl = threadIdx.x >> 6;
@@ -588,12 +606,9 @@ pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, in
     const float4 o = make_float4(t.x * inv, t.y * inv, t.z * inv, t.w * inv);
     *reinterpret_cast<float4 *>(ap + (long long)f * ncols + c) = o;
     if (apb) {                                                  // operand planes of the M = frames GEMMs
-      const __nv_bfloat162 h01 = __floats2bfloat162_rn(o.x, o.y), h23 = __floats2bfloat162_rn(o.z, o.w);
-      const __nv_bfloat162 l01 = __floats2bfloat162_rn(o.x - __low2float(h01), o.y - __high2float(h01));
-      const __nv_bfloat162 l23 = __floats2bfloat162_rn(o.z - __low2float(h23), o.w - __high2float(h23));
       uint2 ph, pl;
-      ph.x = *reinterpret_cast<const uint32_t *>(&h01); ph.y = *reinterpret_cast<const uint32_t *>(&h23);
-      pl.x = *reinterpret_cast<const uint32_t *>(&l01); pl.y = *reinterpret_cast<const uint32_t *>(&l23);
+      if (fp16) { split2_f16(o.x, o.y, ph.x, pl.x); split2_f16(o.z, o.w, ph.y, pl.y); }
+      else { split2_bf16(o.x, o.y, ph.x, pl.x); split2_bf16(o.z, o.w, ph.y, pl.y); }
       *reinterpret_cast<uint2 *>(apb + (long long)f * ncols + c) = ph;
       *reinterpret_cast<uint2 *>(apb + apb_plane + (long long)f * ncols + c) = pl;
     }
@@ -601,10 +616,10 @@ pool_finish_kernel(const float *__restrict__ pool, int rows_per_frame, int M, in
 }
 
 int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap,
-                __nv_bfloat16 *apb, long long apb_plane, cudaStream_t st) {
+                __nv_bfloat16 *apb, long long apb_plane, int fp16, cudaStream_t st) {
   if (ncols % 4) { set_error("pool_finish: ncols must be a multiple of 4"); return PLR2_E_SHAPE; }
   dim3 grid((ncols / 4 + 63) / 64, frames);
-  pool_finish_kernel<<<grid, 256, 0, st>>>(pool, rows_per_frame, M, ncols, ap, apb, apb_plane);
+  pool_finish_kernel<<<grid, 256, 0, st>>>(pool, rows_per_frame, M, ncols, ap, apb, apb_plane, fp16);
   return check_launch("pool_finish");
 }
 
@@ -728,7 +743,7 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   if ((rc = make_map(&ma_hi, g.A, a_cols, g.M, g.lda, TC_BM))) return rc;
   if ((rc = make_map(&ma_lo, g.A + (NPROD == 3 ? g.a_plane : 0), a_cols, g.M, g.lda, TC_BM))) return rc;
   if ((rc = make_map(&mb_hi, g.W, g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
-  if ((rc = make_map(&mb_lo, g.W + g.w_plane, g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
+  if ((rc = make_map(&mb_lo, g.W + (NPROD == 1 ? 0 : g.w_plane), g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
   // Output maps: TMA stores need 16-byte aligned base and pitch; with batch > 1 a partial last chunk would
   // spill into the next problem's columns, so N must then be a multiple of the chunk width.
   CUtensorMap mc_hi = ma_hi, mc_lo = ma_hi;
@@ -748,6 +763,7 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   }
   TcKernelArgs k{};
   k.tma_store = tma_store;
+  k.fp16 = g.fp16;
   k.M = g.M; k.N = g.N; k.K = g.K; k.batch = g.batch;
   k.m_tiles = (g.M + TC_BM * CG - 1) / (TC_BM * CG); k.n_tiles = (g.N + BN - 1) / BN;
   k.a_col_z = g.a_col_z; k.b_row_z = g.b_row_z; k.c_col_z = g.c_col_z; k.bias_z = g.bias_z;
@@ -814,6 +830,11 @@ int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
   }
   if ((g.out_mode == TC_OUT_POOL || g.out_mode == TC_OUT_HEAD || g.frame_bias) && g.rows_per_frame < TC_BM) { set_error("gemm_bf16x2: per-frame epilogues need rows_per_frame >= %d", TC_BM); return PLR2_E_UNSUPPORTED; }
   const bool hi_only = g.a_hi_only != 0;
+  if (g.w_hi_only && !hi_only) { set_error("gemm_bf16x2: w_hi_only needs a_hi_only (single product)"); return PLR2_E_UNSUPPORTED; }
+  if (g.w_hi_only) {              // single product X_hi W_hi (large layers only: 256-wide tiles on CTA pairs)
+    if (tc_cta_group() == 2) return g.N >= 256 ? launch_tc<256, 1, 2>(g, st) : launch_tc<128, 1, 2>(g, st);
+    return g.N >= 256 ? launch_tc<256, 1, 1>(g, st) : launch_tc<128, 1, 1>(g, st);
+  }
   if (tc_cta_group() == 2) {
     // few 256-wide tiles (M = frames problems): halve the tile so twice as many CTA pairs share the work
     const int pairs = sm_count() / 2;

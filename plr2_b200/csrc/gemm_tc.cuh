@@ -18,6 +18,8 @@ struct TcGemm {
   const float *bias = nullptr, *frame_bias = nullptr; int rows_per_frame = 1; long long ldfb = 0;
   int relu = 0, out_mode = TC_OUT_F32;
   int a_hi_only = 0;          // 1: use only the hi plane of X (2 MMAs per MAC; for layers whose output is only pooled)
+  int w_hi_only = 0;          // 1 (with a_hi_only): single product X_hi W_hi (1 MMA per MAC)
+  int fp16 = 0;               // operand planes and TC_OUT_BF16X2 outputs are IEEE fp16 (11-bit mantissa) instead of bf16; same layout
   float *Cf = nullptr; long long ldc = 0;
   __nv_bfloat16 *Cb = nullptr; long long ldcb = 0, c_plane = 0;
   float *pool = nullptr;      // TC_OUT_POOL: [ceil(M/32)][2][N] partial column sums
@@ -32,7 +34,7 @@ int gemm_bf16x2(const TcGemm &g, cudaStream_t st);
 // ap[f][c] = (1/rows_per_frame) * sum of the pooling partials belonging to frame f; apb (optional): the same
 // values as split-bf16 planes [2][frames][ncols], plane stride apb_plane elements
 int pool_finish(const float *pool, int frames, int rows_per_frame, int M, int ncols, float *ap,
-                __nv_bfloat16 *apb, long long apb_plane, cudaStream_t st);
+                __nv_bfloat16 *apb, long long apb_plane, int fp16, cudaStream_t st);
 // dst planes <- split(src): hi = bf16(v), lo = bf16(v - hi)
 int split_bf16x2(const float *src, long long ld, long long rows, int cols, __nv_bfloat16 *dst, long long ldd,
                  long long plane, cudaStream_t st);

@@ -6,6 +6,7 @@
 //   * bias-gradient column sums, embedding-gradient scatter, weight pack / unpack
 #include "pointnet.cuh"
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 namespace plr2 {
 
@@ -25,7 +26,7 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
                    const float *__restrict__ emb_in, const float *__restrict__ x, int N, int hw,
                    float *__restrict__ pf, __nv_bfloat16 *__restrict__ pfb, long long pf_plane,
                    float *__restrict__ emb_out, float *__restrict__ embT, int skip_e,
-                   const int64_t *__restrict__ obj, int num_obj, unsigned int *__restrict__ status) {
+                   const int64_t *__restrict__ obj, int num_obj, unsigned int *__restrict__ status, int fp16) {
   __shared__ __align__(16) float sw1[64 * 4];
   __shared__ __align__(16) float swe[64 * 32];
   __shared__ float sb1[64], sbe[64];
@@ -118,11 +119,19 @@ first_layer_kernel(const float *__restrict__ c1w, const float *__restrict__ c1b,
       uint32_t hi[4], lo[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * q]), h1 = __float2bfloat16_rn(v[2 * q + 1]);
-        const __nv_bfloat16 l0 = __float2bfloat16_rn(v[2 * q] - __bfloat162float(h0));
-        const __nv_bfloat16 l1 = __float2bfloat16_rn(v[2 * q + 1] - __bfloat162float(h1));
-        hi[q] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-        lo[q] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+        if (fp16) {
+          const __half2 h = __floats2half2_rn(v[2 * q], v[2 * q + 1]);
+          const float2 hf = __half22float2(h);
+          const __half2 l = __floats2half2_rn(v[2 * q] - hf.x, v[2 * q + 1] - hf.y);
+          hi[q] = *reinterpret_cast<const uint32_t *>(&h);
+          lo[q] = *reinterpret_cast<const uint32_t *>(&l);
+        } else {
+          const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * q]), h1 = __float2bfloat16_rn(v[2 * q + 1]);
+          const __nv_bfloat16 l0 = __float2bfloat16_rn(v[2 * q] - __bfloat162float(h0));
+          const __nv_bfloat16 l1 = __float2bfloat16_rn(v[2 * q + 1] - __bfloat162float(h1));
+          hi[q] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          lo[q] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+        }
       }
       // Stage 64 output columns of the warp's 32 points ([32][8 x 16 B], pitch 144 B: conflict-free), then
       // write them out as 128-byte row segments (4 rows per instruction instead of 32 scattered 16-byte pieces).
@@ -160,7 +169,7 @@ int first_layer(const float *packed, const NetLayout &L, const float *out_img, c
   dim3 grid((N + FL_THREADS - 1) / FL_THREADS, frames);
   first_layer_kernel<false><<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
                                                          out_img, choose, emb_in, x, N, hw, pf, nullptr, 0, emb_out, embT, 0,
-                                                         obj, L.O, status);
+                                                         obj, L.O, status, 0);
   return check_launch("first_layer");
 }
 
@@ -172,7 +181,7 @@ int first_layer_bf16(const float *packed, const NetLayout &L, const float *out_i
   dim3 grid((N + FL_THREADS - 1) / FL_THREADS, frames);
   first_layer_kernel<true><<<grid, FL_THREADS, 0, st>>>(packed + L.c1w, packed + L.c1b, packed + L.e1w, packed + L.e1b,
                                                         out_img, choose, emb_in, x, N, hw, nullptr, pfb, pf_plane, emb_out,
-                                                        nullptr, skip_e, obj, L.O, status);
+                                                        nullptr, skip_e, obj, L.O, status, infer_fp16() ? 1 : 0);
   return check_launch("first_layer_bf16");
 }
 
@@ -341,8 +350,9 @@ struct CopyTable {
   CopyEntry e[MAX_ENTRIES];
   int n;
   const float *base;            // packed FP32 region (for the element offset of a destination)
-  __nv_bfloat16 *planes;        // split-bf16 planes of the same layout, or nullptr
+  __nv_bfloat16 *planes;        // split hi/lo planes of the same layout (bf16 or fp16 bits), or nullptr
   long long plane_stride;
+  int fp16;
 };
 
 __global__ void __launch_bounds__(256) copy_blocks_kernel(const __grid_constant__ CopyTable T) {
@@ -354,9 +364,16 @@ __global__ void __launch_bounds__(256) copy_blocks_kernel(const __grid_constant_
     E.dst[r * E.dst_ld + c] = v;
     if (E.round && T.planes != nullptr) {     // split-bf16 copy for the tensor-core layers
       const long long off = (E.dst - T.base) + (long long)(r * E.dst_ld + c);
-      const __nv_bfloat16 h = __float2bfloat16_rn(v);
-      T.planes[off] = h;
-      T.planes[T.plane_stride + off] = __float2bfloat16_rn(v - __bfloat162float(h));
+      if (T.fp16) {
+        const __half h = __float2half_rn(v);
+        __half *pl = reinterpret_cast<__half *>(T.planes);
+        pl[off] = h;
+        pl[T.plane_stride + off] = __float2half_rn(v - __half2float(h));
+      } else {
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        T.planes[off] = h;
+        T.planes[T.plane_stride + off] = __float2bfloat16_rn(v - __bfloat162float(h));
+      }
     }
   }
 }
@@ -424,6 +441,7 @@ int net_copy_params(const NetLayout &L, const plr2_param_table *P, float *packed
   T.base = packed;
   T.planes = (to_packed && round) ? reinterpret_cast<__nv_bfloat16 *>(packed + L.total) : nullptr;
   T.plane_stride = (long long)L.total;
+  T.fp16 = infer_fp16() ? 1 : 0;   // the packed planes feed the inference path only (training packs its operands per contraction)
   if (to_packed) {
     // conv1 weight is padded from 3 to 4 columns: clear the pad lane once
     cudaError_t e = cudaMemsetAsync(packed + L.c1w, 0, 64 * 4 * sizeof(float), st);

@@ -129,21 +129,22 @@ static int feat_forward_tc(const float *pk, const NetLayout &L, const TcWorkspac
   const bool pooled_only = L.net == PLR2_NET_REFINER;
   g.a_hi_only = pooled_only ? 1 : 0;
   if (pooled_only) g.c_plane = 0;
-  RC(gemm_bf16x2(g, st));
+  g.fp16 = infer_fp16(); RC(gemm_bf16x2(g, st));
   g = TcGemm();
   g.A = L.c5k == 256 ? pf + 128 : pf; g.lda = 384; g.a_plane = W.pf_plane;
   g.W = wb + L.c5w; g.ldw = L.c5k; g.w_plane = wplane;
   g.M = R; g.N = 512; g.K = L.c5k; g.bias = pk + L.c5b; g.relu = 1;
   g.out_mode = TC_OUT_BF16X2; g.Cb = x5; g.ldcb = 512; g.c_plane = 0;                // hi plane only (see above)
   g.a_hi_only = 1;
-  RC(gemm_bf16x2(g, st));                                                            // conv5
+  g.fp16 = infer_fp16(); RC(gemm_bf16x2(g, st));                                                            // conv5
   g = TcGemm();
   g.A = x5; g.lda = 512; g.a_plane = W.x5_plane; g.W = wb + L.c6w; g.ldw = 512; g.w_plane = wplane;
   g.M = R; g.N = 1024; g.K = 512; g.bias = pk + L.c6b; g.relu = 1;
   g.out_mode = TC_OUT_POOL; g.pool = W.pool; g.rows_per_frame = N;
   g.a_hi_only = 1;
-  RC(gemm_bf16x2(g, st));                                                            // conv6 + AvgPool partials
-  RC(pool_finish(W.pool, F, N, R, 1024, W.ap, (__nv_bfloat16 *)W.apb, W.apb_plane, st));
+  g.w_hi_only = infer_conv6_nprod() == 1 ? 1 : 0;   // single product: experiment only, see common.cuh
+  g.fp16 = infer_fp16(); RC(gemm_bf16x2(g, st));                                                            // conv6 + AvgPool partials
+  RC(pool_finish(W.pool, F, N, R, 1024, W.ap, (__nv_bfloat16 *)W.apb, W.apb_plane, infer_fp16() ? 1 : 0, st));
   return 0;
 }
 
@@ -159,18 +160,18 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   TcGemm g;
   g.A = (const __nv_bfloat16 *)W.apb; g.lda = 1024; g.a_plane = W.apb_plane; g.W = wb + L.h1ap; g.ldw = 1024; g.w_plane = wplane;
   g.M = F; g.N = 1920; g.K = 1024; g.bias = pk + L.h1b; g.out_mode = TC_OUT_F32; g.Cf = W.hb; g.ldc = 1920;
-  RC(gemm_bf16x2(g, st));
+  g.fp16 = infer_fp16(); RC(gemm_bf16x2(g, st));
   g = TcGemm();
   g.A = pf; g.lda = 384; g.a_plane = W.pf_plane; g.W = wb + L.h1pf; g.ldw = 384; g.w_plane = wplane;
   g.M = R; g.N = 1920; g.K = 384; g.frame_bias = W.hb; g.rows_per_frame = N; g.ldfb = 1920; g.relu = 1;
   g.out_mode = TC_OUT_BF16X2; g.Cb = h1; g.ldcb = 1920; g.c_plane = W.h1_plane;
-  RC(gemm_bf16x2(g, st));                                                            // conv1_{r,t,c}
+  g.fp16 = infer_fp16(); RC(gemm_bf16x2(g, st));                                                            // conv1_{r,t,c}
   g = TcGemm();
   g.A = h1; g.lda = 1920; g.a_plane = W.h1_plane; g.W = wb + L.h2w; g.ldw = 640; g.w_plane = wplane;
   g.M = R; g.N = 256; g.K = 640; g.batch = 3; g.a_col_z = 640; g.b_row_z = 256; g.c_col_z = 256; g.bias_z = 256;
   g.bias = pk + L.h2b; g.relu = 1;
   g.out_mode = TC_OUT_BF16X2; g.Cb = h2; g.ldcb = 768; g.c_plane = W.h2_plane;
-  RC(gemm_bf16x2(g, st));                                                            // conv2_*
+  g.fp16 = infer_fp16(); RC(gemm_bf16x2(g, st));                                                            // conv2_*
   g = TcGemm();
   g.A = h2; g.lda = 768; g.a_plane = W.h2_plane; g.W = wb + L.h3w; g.ldw = 256; g.w_plane = wplane;
   g.M = R; g.N = 128; g.K = 256; g.batch = 3; g.a_col_z = 256; g.b_row_z = 128; g.c_col_z = 128; g.bias_z = 128;
@@ -180,7 +181,7 @@ static int posenet_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   g.out_mode = TC_OUT_HEAD; g.rows_per_frame = N;
   g.w4 = pk + L.h4w; g.b4 = pk + L.h4b; g.obj = obj; g.num_obj = L.O;
   g.pred_r = pred_r; g.pred_t = pred_t; g.pred_c = pred_c;
-  RC(gemm_bf16x2(g, st));
+  g.fp16 = infer_fp16(); RC(gemm_bf16x2(g, st));
   return 0;
 }
 
@@ -195,7 +196,7 @@ static int refiner_forward_tc(const float *pk, const NetLayout &L, const TcWorks
   g.A = (const __nv_bfloat16 *)W.apb; g.lda = 1024; g.a_plane = W.apb_plane; g.W = wb + L.h1ap; g.ldw = 1024;
   g.w_plane = (long long)L.total;
   g.M = F; g.N = 1024; g.K = 1024; g.bias = pk + L.h1b; g.relu = 1; g.out_mode = TC_OUT_F32; g.Cf = W.hb; g.ldc = 1024;
-  RC(gemm_bf16x2(g, st));
+  g.fp16 = infer_fp16(); RC(gemm_bf16x2(g, st));
   RC(frame_linear(W.hb, 1024, pk + L.h2w, 512, pk + L.h2b, W.h3, 256, F, 128, 512, 1, 2, 512, 128 * 512, 128, 128, st));
   RC(head_out(W.h3, 256, pk + L.h4w, pk + L.h4b, obj, L.O, F, 1, pred_r, pred_t, nullptr, st));
   return 0;

@@ -190,3 +190,57 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+# ---------------------------------------------------------------------------------------------
+# PoseRefineNet (lib/network.py:151-206): everything behind conv6 sees the per-frame MEAN of 1000 points, so the
+# rounding of the activations averages out - the rounding of the WEIGHTS is the same for every point and does not.
+def refiner(p, x, emb, obj, num_obj, fmt, dtype=torch.float32):
+    c = lambda t: t.to(dtype)
+    W = lambda n: c(p[n + ".weight"].reshape(p[n + ".weight"].shape[0], -1))
+    B = lambda n: c(p[n + ".bias"])
+    if dtype == torch.float64:
+        fmt = {g: "f32" for g in GROUPS}
+    x1 = torch.relu(c(x) @ W("feat.conv1").t() + B("feat.conv1"))
+    e1 = torch.relu(c(emb).t() @ W("feat.e_conv1").t() + B("feat.e_conv1"))
+    x2 = lin(x1, W("feat.conv2"), B("feat.conv2"), fmt["c2"])
+    e2 = lin(e1, W("feat.e_conv2"), B("feat.e_conv2"), fmt["c2"])
+    pf = torch.cat([x1, e1, x2, e2], 1)
+    x5 = lin(pf, W("feat.conv5"), B("feat.conv5"), fmt["c5"])
+    x6 = lin(x5, W("feat.conv6"), B("feat.conv6"), fmt["c6"])
+    ap = x6.mean(0, keepdim=True)
+    out = []
+    for h, width in (("r", 4), ("t", 3)):
+        y = lin(ap, W(f"conv1_{h}"), B(f"conv1_{h}"), fmt["hb"])           # M = frames tensor-core GEMM
+        y = torch.relu(y @ W(f"conv2_{h}").t() + B(f"conv2_{h}"))          # FP32 SIMT
+        y = y @ W(f"conv3_{h}").t() + B(f"conv3_{h}")
+        out.append(y.reshape(num_obj, width)[int(obj)])
+    return out
+
+
+def sweep_refiner(n_frames=16, dev="cpu", shape=synth.YCB_REFINE, param_seeds=(2, 8), log=print):
+    torch.backends.cuda.matmul.allow_tf32 = False
+    for ps in param_seeds:
+        params = {k: torch.from_numpy(v).to(dev) for k, v in synth.make_params("refiner", shape.num_obj, ps).items()}
+        frames = [synth.make_frame(shape, 3500 + 17 * i, obj=[12, 3, 19, 0, 7, 20, 5, 16][i % 8]) for i in range(n_frames)]
+        g = torch.Generator().manual_seed(ps)
+
+        def run(name, fmt):
+            worst = {"r": 0.0, "t": 0.0}
+            for fr in frames:
+                x = torch.from_numpy(fr["points"] - fr["points"].mean(0)).to(dev)        # re-centred cloud, like new_points
+                emb = torch.from_numpy(fr["out_img"].reshape(32, -1)[:, fr["choose"]]).to(dev)
+                with torch.no_grad():
+                    got = refiner(params, x, emb, int(fr["idx"]), shape.num_obj, fmt)
+                    ref = refiner(params, x, emb, int(fr["idx"]), shape.num_obj, fmt, dtype=torch.float64)
+                for k, a, b in zip("rt", got, ref):
+                    worst[k] = max(worst[k], float(((a.double() - b).abs() / b.abs().max()).max()))
+            log("refiner params %d  %-34s max |err| / max|ref| over %d frames:  pred_r %.2e   pred_t %.2e"
+                % (ps, name, n_frames, worst["r"], worst["t"]))
+        f3 = {g_: "fp16x3" for g_ in GROUPS}
+        run("fp32 everywhere", {g_: "f32" for g_ in GROUPS})
+        run("round-1 scheme (bf16; c2,c5,c6 = x2)", dict({g_: "bf16x3" for g_ in GROUPS}, c2="bf16x2", c5="bf16x2", c6="bf16x2"))
+        run("fp16; c2,c5,c6 = x2", dict(f3, c2="fp16x2", c5="fp16x2", c6="fp16x2"))
+        run("fp16; c2,c5 = x2, c6 = x1", dict(f3, c2="fp16x2", c5="fp16x2", c6="fp16x1"))
+        run("fp16; c2,c5,c6 = x1", dict(f3, c2="fp16x1", c5="fp16x1", c6="fp16x1"))
+        run("bf16; c6 = x1", dict({g_: "bf16x3" for g_ in GROUPS}, c2="bf16x2", c5="bf16x2", c6="bf16x1"))
