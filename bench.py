@@ -470,7 +470,14 @@ def run_ours(args, world, rank, local):
     numa_cpus = bind_to_gpu_numa(local) if world > 1 else None     # pinned buffers on the GPU's own node
     work_all = make_workload(total, 1000)                # the same global batch on every rank
     work = {k: v[lo:hi].contiguous() for k, v in work_all.items()}
-    host = {k: v.pin_memory() for k, v in work.items()}
+    if args.host_alloc == "wc":                       # write-combined staging buffers (experiment for host-bound N = 8)
+        from plr2_b200.pipeline import host_staging_buffer
+        host = {}
+        for k, v in work.items():
+            host[k] = host_staging_buffer(tuple(v.shape), v.dtype, write_combined=True)
+            host[k].copy_(v)
+    else:
+        host = {k: v.pin_memory() for k, v in work.items()}
     frame_bytes = DenseFusionPipeline.bytes_per_frame(host)
     # Device-resident input sets, used in rotation: consecutive steps never read inputs the previous step left in
     # the 126 MB L2 (one set when the shard alone is larger than twice the L2).
@@ -665,7 +672,7 @@ def run_ours(args, world, rank, local):
         "config": {"workload": "C4: 512 YCB-shaped frames per step sharded 512/G over the GPUs, PoseNet(out_img given)+Loss(refine)+"
                                "2x(PoseRefineNet+Loss_refine ADD-S)",
                    "frames_per_step": total, "frames_per_gpu_per_step": n_local, "chunk_frames": args.chunk,
-                   "host_chunk_frames": host_chunk, "cuda_graph": use_graph,
+                   "host_chunk_frames": host_chunk, "cuda_graph": use_graph, "host_alloc": args.host_alloc,
                    "numa_bound_cpus": len(numa_cpus) if numa_cpus else None, "num_points": SHAPE.num_points,
                    "num_mesh": SHAPE.num_mesh, "num_obj": SHAPE.num_obj, "crop": [SHAPE.height, SHAPE.width],
                    "choose": "pixels of a compact object mask (datasets/ycb/dataset.py:177-184)",
@@ -706,6 +713,8 @@ def main():
                     help="frames per chunk of the host (e2e) path: H2D of chunk i+1 overlaps chunk i (0 = min(64, max(16, shard/4)))")
     ap.add_argument("--cuda-graph", default="on", choices=["auto", "on", "off"],
                     help="replay each chunk's launch chain as a CUDA graph (on / auto) or launch eagerly (off)")
+    ap.add_argument("--host-alloc", default="pinned", choices=["pinned", "wc"],
+                    help="host buffers of the e2e path: page-locked (default) or page-locked write-combined")
     ap.add_argument("--weak-steps", type=int, default=5, help="steps of the extra weak-scaling measurement at N > 1 (0 = skip)")
     ap.add_argument("--train-steps", type=int, default=10, help="steps of the C5 training record (0 = skip)")
     ap.add_argument("--check-frames", type=int, default=4, help="frames of the timed result compared with the CPU oracle (rank 0)")

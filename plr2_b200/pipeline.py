@@ -161,3 +161,35 @@ class DenseFusionPipeline:
     @staticmethod
     def bytes_per_frame(host):
         return sum(int(host[k][0].numel()) * host[k].element_size() for k in INPUT_KEYS)
+
+
+def host_staging_buffer(shape, dtype, write_combined=False):
+    """A page-locked host tensor for `infer_host`.  write_combined=True allocates it with cudaHostAllocWriteCombined:
+    memory the CPU only WRITES (a staging buffer filled by the loader) and the GPU reads over PCIe without cache
+    snooping - worth trying where several ranks stream from the same host (e2e at N = 8 is host-bound).
+    CPU reads of such memory are slow: do not use it for results.  The storage is freed when the tensor is."""
+    if not write_combined:
+        return torch.empty(shape, dtype=dtype, pin_memory=True)
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")          # the runtime torch itself has loaded
+    rt.cudaHostAlloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_size_t, ctypes.c_uint]
+    rt.cudaFreeHost.argtypes = [ctypes.c_void_p]
+    nbytes = int(torch.empty((), dtype=dtype).element_size())
+    for d in shape:
+        nbytes *= int(d)
+    ptr = ctypes.c_void_p()
+    rc = rt.cudaHostAlloc(ctypes.byref(ptr), max(nbytes, 1), 0x04)          # cudaHostAllocWriteCombined
+    if rc != 0:
+        raise RuntimeError(f"cudaHostAlloc(write-combined, {nbytes} bytes) failed with cudaError {rc}")
+
+    class _Owner:                                  # keeps the allocation alive as long as the tensor's buffer is
+        def __init__(self, p):
+            self.p = p
+            self.buf = (ctypes.c_byte * max(nbytes, 1)).from_address(p.value)
+
+        def __del__(self):
+            rt.cudaFreeHost(self.p)
+    owner = _Owner(ptr)
+    t = torch.frombuffer(owner.buf, dtype=dtype, count=nbytes // torch.empty((), dtype=dtype).element_size()).reshape(shape)
+    t._plr2_owner = owner
+    return t

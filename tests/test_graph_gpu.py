@@ -94,3 +94,23 @@ def test_c5_train_step_graph_equals_eager():
         l = ts_g.step()
     torch.cuda.synchronize()
     assert bool(torch.isfinite(l).all()) and any(not torch.equal(a, b) for a, b in zip(before, ts_g.params))
+
+
+def test_infer_host_from_write_combined_staging_buffers():
+    """pipeline.host_staging_buffer(write_combined=True): page-locked write-combined host memory is a valid source of
+    the host path (recognised as pinned, same results as ordinary pinned buffers) and is released with the tensor."""
+    from plr2_b200.pipeline import host_staging_buffer
+    shp = synth.Shape(1000, 21, 600, 40, 40, tuple(synth.YCB_SYM))
+    w = _work(shp, [12, 3, 19, 0, 7], 950)
+    pinned = {k: v.cpu().pin_memory() for k, v in w.items()}
+    wc = {}
+    for k, v in w.items():
+        wc[k] = host_staging_buffer(tuple(v.shape), v.dtype, write_combined=True)
+        assert wc[k].is_pinned() and tuple(wc[k].shape) == tuple(v.shape) and wc[k].dtype == v.dtype
+        wc[k].copy_(v.cpu())
+    pipe = _pipe(shp, False, 4)
+    pipe.host_chunk_frames = 2
+    a = pipe.infer_host(pinned).clone()
+    b = pipe.infer_host(wc).clone()
+    assert torch.equal(a, b)
+    del wc
