@@ -254,8 +254,10 @@ typedef struct plr2_param_table {
 #define PLR2_PREC_FP32 0      /* FP32 SIMT everywhere.  Forward and input gradients are bit-for-bit reproducible; the weight
                                * gradients are summed over the points by split-K partial products combined with atomicAdd,
                                * so their last bits depend on the arrival order (relative spread ~1e-7). */
-#define PLR2_PREC_BF16X2 1    /* tcgen05 kind::f16 on split-bf16 operands (hi+lo, 3 MMAs), FP32 accumulate in TMEM.
-                               * Inference keeps activations as bf16 planes.  With training != 0 activations stay FP32:
+#define PLR2_PREC_BF16X2 1    /* tcgen05 kind::f16 on operands split into two 16-bit planes (hi+lo, 3 MMAs), FP32 accumulate in
+                               * TMEM.  Inference keeps activations and packed weights as IEEE fp16 planes (22 mantissa bits;
+                               * environment PLR2_INFER_FMT=bf16 selects bf16 planes, 16 bits - set it before the first
+                               * plr2_net_pack, the planes of the packed buffer must match).  With training != 0 activations stay FP32:
                                * the forward runs on the FP32 kernel (its ReLU signs are the masks of the backward),
                                * the operands of every input-gradient / weight-gradient contraction are packed into
                                * scratch planes of the workspace (n_points >= 128, else FP32 SIMT). */
@@ -267,7 +269,8 @@ typedef struct plr2_param_table {
 size_t plr2_net_packed_floats(int net, int num_obj);
 size_t plr2_net_workspace_bytes(int net, int frames, int n_points, int num_obj, int training);
 /* Gather the state-dict tensors into the packed layout: packed[0, T) holds the FP32 copy and, when
- * split_bf16 != 0, packed[T, 2T) (T = plr2_net_packed_floats/2) the split-bf16 planes of the same layout. */
+ * split_bf16 != 0, packed[T, 2T) (T = plr2_net_packed_floats/2) the hi/lo 16-bit planes of the same layout (fp16 by
+ * default, see PLR2_PREC_BF16X2; they feed the inference path only - training packs its operands per contraction). */
 int plr2_net_pack(int net, const plr2_param_table *params, int num_obj, float *packed, int split_bf16,
                   void *stream);
 /* Scatter a packed gradient buffer back into per-parameter tensors (overwrites them). */
