@@ -121,6 +121,25 @@ int plr2_refine_loss_fwd(const float *pred_r, const float *pred_t,
                          float *jac_r, float *jac_t, float *pose_out,
                          void *workspace, size_t workspace_bytes, void *stream);
 
+/* The same refiner loss for callers that cannot provide (or allocate) scratch memory: code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * Arguments and results are those of plr2_refine_loss_fwd without the workspace; the arrival counters
+ * and partial sums live in a device array inside the library (plr2_refine_loss_static_scratch_bytes() = 427 008 bytes,
+ * held by every GPU that loads the library until exit), so the call allocates nothing.
+ * Limits: frames <= PLR2_REFINE_LOSS_STATIC_MAX_FRAMES and n_mesh <= 8192; anything larger returns
+ * PLR2_E_UNSUPPORTED with a message naming plr2_refine_loss_fwd.  ALL calls on a device share the one array: calls that
+ * overlap on the GPU (different streams, concurrent graph branches, several host threads) race on it - serialise
+ * them, or use plr2_refine_loss_fwd with one workspace per concurrent call.  Calls on one stream are safe back to back
+ * (each call re-clears the counters on its stream before its launch). */
+#define PLR2_REFINE_LOSS_STATIC_MAX_FRAMES 256
+size_t plr2_refine_loss_static_scratch_bytes(void);
+int plr2_refine_loss_fwd_static(const float *pred_r, const float *pred_t,
+                                const float *target, const float *model_points, const float *points,
+                                const int64_t *obj, const uint8_t *sym_lut, int num_obj,
+                                int frames, int n_points, int n_mesh, int knn_mode,
+                                float *dis, float *new_points, float *new_target,
+                                float *jac_r, float *jac_t, float *pose_out, void *stream);
+
 /* Pose hand-off between refinement stages (tools/train.py:141-145; the composition DenseFusion's evaluation
  * performs): pose_acc [F][12] (R row-major, t) <- pose_acc o pose_delta, i.e. R <- R Rd, t <- R td + t, where
  * pose_delta is the pose_out of the NEXT stage (estimated in the frame re-centred by pose_acc). */

@@ -943,3 +943,61 @@ extern "C" int plr2_pose_compose(float *pose_acc, const float *pose_delta, int f
   pose_compose_kernel<<<(frames + 127) / 128, 128, 0, (cudaStream_t)stream>>>(pose_acc, pose_delta, frames);
   return check_launch("plr2_pose_compose");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Refiner loss without caller-provided scratch (no counterpart in the reference; added
+// for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc).  The per-frame arrival counters and per-CTA partial sums of refine_loss_kernel live in
+// a file-scope device array of fixed size; every GPU that loads the library holds these 417 KB until exit.
+// In HOST code the array's name is only a stand-in: its device address is obtained once per device, with that
+// device current, by cudaGetSymbolAddress, and that pointer is what the kernel receives.
+constexpr int STATIC_REFINE_MAX_FRAMES = PLR2_REFINE_LOSS_STATIC_MAX_FRAMES;
+constexpr int STATIC_REFINE_MAX_MESH = 8192;                               // limit of refine_loss_kernel itself
+constexpr size_t STATIC_REFINE_BYTES =
+    ((size_t)STATIC_REFINE_MAX_FRAMES * sizeof(unsigned int) + 127) / 128 * 128 +
+    (size_t)STATIC_REFINE_MAX_FRAMES * REFINE_MAX_SPLIT * 13 * sizeof(float);
+static __device__ __align__(256) unsigned char g_refine_static_scratch[STATIC_REFINE_BYTES];
+
+// device address of the array on the current device (cached per device; racing initialisers store the same value)
+static int refine_static_scratch_ptr(void **out) {
+  static std::atomic<void *> cache[plr2::PLR2_MAX_DEVICES];
+  const int dev = plr2::current_device();
+  void *p = cache[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
+    cudaError_t e = cudaGetSymbolAddress(&p, g_refine_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      plr2::set_error("plr2_refine_loss_fwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : PLR2_E_WORKSPACE;
+    }
+    cache[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return 0;
+}
+
+extern "C" size_t plr2_refine_loss_static_scratch_bytes(void) { return STATIC_REFINE_BYTES; }
+
+extern "C" int plr2_refine_loss_fwd_static(const float *pred_r, const float *pred_t, const float *target,
+                                           const float *model_points, const float *points, const int64_t *obj,
+                                           const uint8_t *sym_lut, int num_obj, int frames, int n_points,
+                                           int n_mesh, int knn_mode, float *dis, float *new_points,
+                                           float *new_target, float *jac_r, float *jac_t, float *pose_out,
+                                           void *stream) {
+  if (frames > STATIC_REFINE_MAX_FRAMES || n_mesh > STATIC_REFINE_MAX_MESH) {
+    plr2::set_error("plr2_refine_loss_fwd_static: frames=%d / n_mesh=%d beyond the static scratch (max %d frames, %d mesh "
+                    "points): use plr2_refine_loss_fwd with a caller-provided workspace",
+                    frames, n_mesh, STATIC_REFINE_MAX_FRAMES, STATIC_REFINE_MAX_MESH);
+    return PLR2_E_UNSUPPORTED;
+  }
+  if (frames <= 0 || n_mesh <= 0)      // shape errors / the empty batch: same answers as the workspace entry, no scratch needed
+    return plr2_refine_loss_fwd(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, frames, n_points,
+                                n_mesh, knn_mode, dis, new_points, new_target, jac_r, jac_t, pose_out, nullptr, 0, stream);
+  void *scratch = nullptr;
+  const int rc = refine_static_scratch_ptr(&scratch);
+  if (rc) return rc;
+  // plr2_refine_loss_fwd clears the arrival counters on `stream` before the launch (the array keeps the previous
+  // call's contents; the partial sums are fully overwritten before they are read).  It allocates nothing.
+  return plr2_refine_loss_fwd(pred_r, pred_t, target, model_points, points, obj, sym_lut, num_obj, frames, n_points,
+                              n_mesh, knn_mode, dis, new_points, new_target, jac_r, jac_t, pose_out, scratch,
+                              STATIC_REFINE_BYTES, stream);
+}
