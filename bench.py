@@ -463,7 +463,7 @@ def run_ours(args, world, rank, local):
     host_chunk = args.host_chunk if args.host_chunk > 0 else min(64, max(16, (n_local + 3) // 4))
     pipe = DenseFusionPipeline(SHAPE.num_points, SHAPE.num_obj, SHAPE.num_mesh, SHAPE.sym_list, device=dev,
                                precision=ops.PREC_BF16X2, knn_mode=knn_mode, chunk_frames=args.chunk,
-                               host_chunk_frames=host_chunk, cuda_graph=False, max_graphs=16)
+                               host_chunk_frames=host_chunk, cuda_graph=False, max_graphs=16, copy_streams=args.copy_streams)
     pn = synth.make_params("posenet", SHAPE.num_obj, 1)
     rf = synth.make_params("refiner", SHAPE.num_obj, 2)
     pipe.load_params(pn, rf)
@@ -672,7 +672,7 @@ def run_ours(args, world, rank, local):
         "config": {"workload": "C4: 512 YCB-shaped frames per step sharded 512/G over the GPUs, PoseNet(out_img given)+Loss(refine)+"
                                "2x(PoseRefineNet+Loss_refine ADD-S)",
                    "frames_per_step": total, "frames_per_gpu_per_step": n_local, "chunk_frames": args.chunk,
-                   "host_chunk_frames": host_chunk, "cuda_graph": use_graph, "host_alloc": args.host_alloc,
+                   "host_chunk_frames": host_chunk, "cuda_graph": use_graph, "host_alloc": args.host_alloc, "copy_streams": args.copy_streams,
                    "numa_bound_cpus": len(numa_cpus) if numa_cpus else None, "num_points": SHAPE.num_points,
                    "num_mesh": SHAPE.num_mesh, "num_obj": SHAPE.num_obj, "crop": [SHAPE.height, SHAPE.width],
                    "choose": "pixels of a compact object mask (datasets/ycb/dataset.py:177-184)",
@@ -713,6 +713,7 @@ def main():
                     help="frames per chunk of the host (e2e) path: H2D of chunk i+1 overlaps chunk i (0 = min(64, max(16, shard/4)))")
     ap.add_argument("--cuda-graph", default="on", choices=["auto", "on", "off"],
                     help="replay each chunk's launch chain as a CUDA graph (on / auto) or launch eagerly (off)")
+    ap.add_argument("--copy-streams", type=int, default=1, help="streams the H2D copies of a host chunk are spread over (e2e path)")
     ap.add_argument("--host-alloc", default="pinned", choices=["pinned", "wc"],
                     help="host buffers of the e2e path: page-locked (default) or page-locked write-combined")
     ap.add_argument("--weak-steps", type=int, default=5, help="steps of the extra weak-scaling measurement at N > 1 (0 = skip)")

@@ -26,7 +26,7 @@ INPUT_KEYS = ("out_img", "points", "choose", "obj", "target", "model_points")
 class DenseFusionPipeline:
     def __init__(self, num_points, num_obj, num_mesh, sym_list, device="cuda", precision=ops.PREC_BF16X2,
                  knn_mode=ops.KNN_LOSS_DEFAULT, refine_iters=2, chunk_frames=512, w=0.015, refine_start=True,
-                 with_backbone=False, host_chunk_frames=64, cuda_graph=False, max_graphs=8):
+                 with_backbone=False, host_chunk_frames=64, cuda_graph=False, max_graphs=8, copy_streams=1):
         self.device = torch.device(device)
         self.estimator = PoseNet(num_points, num_obj, precision=precision)
         if not with_backbone:
@@ -41,6 +41,7 @@ class DenseFusionPipeline:
         self.w = w
         self.refine_start = refine_start
         self._staging = None
+        self.copy_streams = copy_streams            # host path: H2D copies of a chunk spread over this many streams (out_img split by frames)
         # cuda_graph: the launch chain of a chunk (~32 kernels + the PyTorch glue around them) is captured once per
         # (input addresses, shapes, parameter versions) and replayed; pays off where a chunk is launch-bound
         # (bs = 1 latency, small shards of a strongly scaled batch).  Results are identical: same kernels, same order.
@@ -124,6 +125,7 @@ class DenseFusionPipeline:
             self._staging = [{k: torch.empty((cf,) + tuple(host[k].shape[1:]), dtype=host[k].dtype, device=dev)
                               for k in INPUT_KEYS} for _ in range(2)]
             self._copy_stream = torch.cuda.Stream(device=dev)
+            self._copy_extra = [torch.cuda.Stream(device=dev) for _ in range(max(0, self.copy_streams - 1))]
             self._ready = [torch.cuda.Event() for _ in range(2)]
             self._free = [torch.cuda.Event() for _ in range(2)]
         res_dev = torch.empty(F, dtype=torch.float32, device=dev)
@@ -139,8 +141,17 @@ class DenseFusionPipeline:
             with torch.cuda.stream(self._copy_stream):
                 if i >= 2:
                     self._copy_stream.wait_event(self._free[i & 1])   # compute of chunk i-2 has finished
-                for k in INPUT_KEYS:
-                    s[k][: b - a].copy_(host[k][a:b], non_blocking=True)
+                n = b - a
+                parts = 1 + len(self._copy_extra)
+                cut = [n * j // parts for j in range(parts + 1)]
+                for k in INPUT_KEYS:                 # the large tensor (out_img) is split by frames over the copy streams
+                    hi = cut[1] if (k == "out_img" and parts > 1) else n
+                    s[k][:hi].copy_(host[k][a:a + hi], non_blocking=True)
+                for j, xs in enumerate(self._copy_extra, start=1):
+                    xs.wait_stream(self._copy_stream)          # ordering against the staging set's previous use
+                    with torch.cuda.stream(xs):
+                        s["out_img"][cut[j]:cut[j + 1]].copy_(host["out_img"][a + cut[j]:a + cut[j + 1]], non_blocking=True)
+                    self._copy_stream.wait_stream(xs)
                 self._ready[i & 1].record(self._copy_stream)
 
         issue_copy(0)
