@@ -348,6 +348,27 @@ int plr2_refiner_backward(const float *packed, const float *x, const float *emb,
                           const float *g_pred_r, const float *g_pred_t, float *packed_grad, int precision,
                           void *stream);
 
+/* ---- batched pose Kalman filter ----------------------------------------------------------
+ * The per-sequence loop of src/helper/postprocess.py:35-61 over Kalman_Filter.update / .predict
+ * (src/estimation/filter.py:132-189), State_R3xQuat (src/estimation/state.py:100-185) and Linear_Motion
+ * (src/estimation/motion.py:15-60) for `sequences` independent sequences of `steps` observations, float64 like the
+ * reference.  State = t xyz | q xyzw.
+ *   prior, prior_var [S][7]         set_prior(prior, covariance) with a 7-vector covariance (filter.py:148-157)
+ *   obs, sensor_var  [S][T][7]      update(observation, covariance_sensor); kf_sequence passes var_sensor / obs_c
+ *   motion_var       [7]            variance_motion (diagonal of Q)
+ *   lengths          [S] or NULL    observations of sequence s used (<= steps); outputs beyond stay untouched
+ *   a_t, a_r                        Linear_Motion params (motion.py:18-26)
+ *   filtered  [S][T][7]             the state update() returns for each observation
+ *   p_diag    [S][T][7] or NULL     diagonal of the covariance after each update (the reference's element-wise update,
+ *                                   filter.py:186, leaves nothing else)
+ *   predicted [S][T][7] or NULL     the state predict() appends after each observation
+ * Deviation (stated): the covariance is propagated with the ANALYTIC Jacobian of the pose composition; the reference
+ * differences it with a step of machine epsilon (state.py:150-161), which returns rounding noise. */
+int plr2_kalman_filter_f64(const double *prior, const double *prior_var, const double *obs,
+                           const double *sensor_var, const double *motion_var, const int32_t *lengths,
+                           double a_t, double a_r, int sequences, int steps,
+                           double *filtered, double *p_diag, double *predicted, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -40,6 +40,7 @@ SIGNATURES = {
     "plr2_auc_f32": (_i, [_vp, _i, C.c_double, C.c_double, _vp, _vp, _sz, _vp]),
     "plr2_refine_loss_workspace_bytes": (_sz, [_i, _i]),
     "plr2_refine_loss_fwd": (_i, [_vp] * 7 + [_i] * 5 + [_vp] * 6 + [_vp, _sz, _vp]),
+    "plr2_kalman_filter_f64": (_i, [_vp] * 6 + [C.c_double, C.c_double, _i, _i] + [_vp] * 4),
     "plr2_refine_loss_static_scratch_bytes": (_sz, []),
     "plr2_refine_loss_fwd_static": (_i, [_vp] * 7 + [_i] * 5 + [_vp] * 6 + [_vp]),
 }

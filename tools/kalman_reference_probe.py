@@ -1,6 +1,7 @@
 #!/usr/bin/env python
-"""Evidence for SURVEY.md 8(f) row 4 (batched pose Kalman filter, src/estimation/filter.py:107-202): why it cannot be
-built "to parity".  Run in the build container (imports the reference from /root/reference/src):
+"""Evidence for SURVEY.md 8(f) row 4 (batched pose Kalman filter, src/estimation/filter.py:107-202): why the device filter
+(csrc/kalman.cu) propagates its covariance with the ANALYTIC Jacobian instead of reproducing the reference's.  Run in
+the build container (imports the reference from /root/reference/src):
 
     python tools/kalman_reference_probe.py > profiles/r2_kalman_reference_probe.txt
 
@@ -9,9 +10,10 @@ a central difference with step h = np.finfo(np.float64).eps.  At state values of
 units in the last place (or not at all), so (f(x+h) - f(x-h)) / 2h is the ROUNDING NOISE of scipy's Rotation
 (from_quat -> as_matrix -> matmul -> from_matrix -> as_quat) and of numpy's 4x4 matmul, divided by 4.4e-16: entries
 are multiples of 1/4, 1/2 ... that have nothing to do with the derivative and change with the BLAS / scipy build.  The
-Kalman gain K = P (P + R)^-1 and hence every filtered pose inherit that noise.  A CUDA kernel can implement the intended
-filter (analytic Jacobian), but its outputs cannot be "identical to the reference's on the same inputs" in any
-build-independent sense - there is no oracle to pin.
+Kalman gain K = P (P + R)^-1 and hence every filtered pose inherit that noise, so bit-level agreement with it has no
+build-independent meaning.  Everything else of the filter is deterministic and is pinned on the reference's own
+outputs (tests/golden/make_kalman_golden.py, tests/test_kalman.py), whole trajectories included - against the
+reference class run with only that step size changed to 1e-6.
 """
 import sys
 import types
