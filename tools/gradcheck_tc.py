@@ -1,6 +1,8 @@
 """Per-parameter gradient accuracy of the three precision modes against the CPU oracle (config C1 at full size):
-fraction of elements within rtol 1e-3 (+1e-4 of the tensor's largest entry) and the largest deviation relative to
-the largest entry.  GPU only.  Usage: python tools/gradcheck_tc.py"""
+fraction of elements within rtol 1e-3 + 1e-4 of the tensor's largest entry (the tests' rule, tests/util.py), the same
+fraction at PURE rtol 1e-3 (no floor: elements that sit near zero by cancellation fail it in any FP32 implementation,
+the fp32 column shows by how much), and the largest deviation relative to the largest entry.
+GPU only.  Usage: python tools/gradcheck_tc.py"""
 import sys, numpy as np, torch
 sys.path.insert(0, '.')
 from oracle import densefusion_oracle as DO
@@ -28,7 +30,14 @@ for prec in (ops.PREC_FP32, ops.PREC_BF16X2, ops.PREC_BF16X2_ALL):
     for k, v in net.named_parameters():
         g = v.grad.detach().cpu().numpy(); o = p[k].grad.numpy()
         atol = 1e-4 * float(np.abs(o).max())
-        res.setdefault(k, []).append((frac_close(g, o, 1e-3, atol), float(np.abs(g - o).max() / (np.abs(o).max() + 1e-30))))
+        res.setdefault(k, []).append((frac_close(g, o, 1e-3, atol), frac_close(g, o, 1e-3, 0.0),
+                                      float(np.abs(g - o).max() / (np.abs(o).max() + 1e-30))))
+    g = img.grad.detach().cpu().numpy(); o = oimg.grad.numpy()
+    res.setdefault("g_out_img", []).append((frac_close(g, o, 1e-3, 1e-4 * float(np.abs(o).max())), frac_close(g, o, 1e-3, 0.0),
+                                            float(np.abs(g - o).max() / (np.abs(o).max() + 1e-30))))
 for k, v in res.items():
     flag = "  <--" if min(x[0] for x in v) < 0.95 else ""
-    print("%-18s fp32 %.3f %.1e | bwd-tc %.3f %.1e | all-tc %.3f %.1e%s" % (k, v[0][0], v[0][1], v[1][0], v[1][1], v[2][0], v[2][1], flag))
+    print("%-18s fp32 %.3f (pure %.3f) %.1e | bwd-tc %.3f (pure %.3f) %.1e | all-tc %.3f (pure %.3f) %.1e%s"
+          % ((k,) + v[0] + v[1] + v[2] + (flag,)))
+worst = {m: min(v[i][0] for v in res.values()) for i, m in enumerate(("fp32", "bwd-tc", "all-tc"))}
+print("smallest with-floor fraction over all tensors:", {k: round(x, 4) for k, x in worst.items()})
