@@ -249,6 +249,13 @@ int plr2_split_bf16x2(const float *src, long long ld, long long rows, int cols, 
 int plr2_gemm_bf16x2(const void *A_planes, long long lda, long long a_plane, const void *W_planes,
                      long long ldw, long long w_plane, int M, int N, int K, const float *bias, int relu,
                      float *C, long long ldc, void *stream);
+/* The weight-gradient form of the same contraction (autograd of the Conv1d(k=1)/Linear layers of
+ * lib/network.py:54-63,107-121: dW = dY^T X, contraction over the points): C[M,N] (f32, ldc) = A^T B with
+ * A = split-bf16 planes [k_rows][lda] (M columns used), B = planes [k_rows][ldb] (N columns used), read
+ * MN-major by the tensor cores (no transposed copy).  k_rows is arbitrary; pitches multiples of 8 elements. */
+int plr2_gemm_bf16x2_tn(const void *A_planes, long long lda, long long a_plane, const void *B_planes,
+                        long long ldb, long long b_plane, int M, int N, int k_rows, float *C,
+                        long long ldc, void *stream);
 
 /* ---- (1)+(2) PoseNet / PoseRefineNet hot path ---------------------------------------------
  * Parameter tables: device pointers to the tensors of the reference's state dict, in this order

@@ -70,6 +70,7 @@ SIGNATURES.update({
     "plr2_gemm_f32": (_i, [C.POINTER(GemmDesc), _vp]),
     "plr2_split_bf16x2": (_i, [_vp, C.c_longlong, C.c_longlong, _i, _vp, C.c_longlong, C.c_longlong, _vp]),
     "plr2_gemm_bf16x2": (_i, [_vp, C.c_longlong, C.c_longlong, _vp, C.c_longlong, C.c_longlong, _i, _i, _i, _vp, _i, _vp, C.c_longlong, _vp]),
+    "plr2_gemm_bf16x2_tn": (_i, [_vp, C.c_longlong, C.c_longlong, _vp, C.c_longlong, C.c_longlong, _i, _i, _i, _vp, C.c_longlong, _vp]),
     "plr2_net_packed_floats": (_sz, [_i, _i]),
     "plr2_net_input_status": (_i, [_vp, C.POINTER(C.c_uint), _vp]),
     "plr2_net_workspace_bytes": (_sz, [_i] * 5),

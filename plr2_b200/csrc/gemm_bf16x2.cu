@@ -74,6 +74,7 @@ struct TcKernelArgs {
   float *pool;                   // [ceil(M/32)][2][N]
   const float *w4, *b4; const int64_t *obj; int num_obj;   // TC_OUT_HEAD
   float *pred_r, *pred_t, *pred_c;
+  int mn_major;                  // operands stored [k rows][mn columns] (TcGemm::mn_major)
   int fp16;                      // operand planes (and TC_OUT_BF16X2 outputs) are IEEE fp16 hi/lo instead of bf16 hi/lo
   int tma_store;                 // tile outputs leave through TMA stores (maps tmC_*)
   int debug;                     // PLR2_TC_DEBUG (timing experiments only): 1 = no global stores, 2 = no epilogue work
@@ -128,7 +129,8 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
   // and a half-width last n-tile would unbalance the units); each round still covers a contiguous tile range.
   auto tile_of = [&](int it) { return it * n_units + (unit + it) % n_units; };
   // Width of the MMA for n-tile `nt`: a last tile with at most BN/2 valid columns runs at N = BN/2
-  auto tile_nw = [&](int nt) { return (g.N - nt * BN <= BN / 2) ? BN / 2 : BN; };
+  // (MN-major operands arrive in 64-column blocks: always full width)
+  auto tile_nw = [&](int nt) { return (!g.mn_major && g.N - nt * BN <= BN / 2) ? BN / 2 : BN; };
 
   if (threadIdx.x == 0) {
     prefetch_tensormap(&tmA_hi); prefetch_tensormap(&tmA_lo);
@@ -161,7 +163,25 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
           uint8_t *sA = smem + stage * Cfg::STAGE_BYTES;
           uint8_t *sB = sA + Cfg::A_PLANES * Cfg::A_BYTES;
           const int ka = z * g.a_col_z + kb * TC_BK, kw = kb * TC_BK, rw = z * g.b_row_z + n0;
-          if (CG == 2) {
+          if (g.mn_major) {
+            // boxes of 64 mn-columns x 64 k-rows, one 8 KB block each: A columns [m0, +128), W columns [rw, +B_ROWS)
+            const uint32_t bar = CG == 2 ? mapa_u32(smem_u32(full_bar + stage), 0) : 0u;
+            if (CG == 2) { if (rank == 0) mbar_arrive_expect_tx(full_bar + stage, 2 * Cfg::STAGE_BYTES); }
+            else mbar_arrive_expect_tx(full_bar + stage, Cfg::STAGE_BYTES);
+            auto ld = [&](uint8_t *dst, const CUtensorMap *tm, int c, int r) {
+              if (CG == 2) tma_load_2d_cg2(dst, tm, bar, c, r); else tma_load_2d(dst, tm, full_bar + stage, c, r);
+            };
+#pragma unroll
+            for (int j = 0; j < TC_BM / 64; ++j) {
+              ld(sA + j * 8192, &tmA_hi, m0 + 64 * j, ka);
+              if (NPROD == 3) ld(sA + Cfg::A_BYTES + j * 8192, &tmA_lo, m0 + 64 * j, ka);
+            }
+#pragma unroll
+            for (int j = 0; j < Cfg::B_ROWS / 64; ++j) {
+              ld(sB + j * 8192, &tmB_hi, rw + 64 * j, ka);
+              if (NPROD != 1) ld(sB + Cfg::B_BYTES + j * 8192, &tmB_lo, rw + 64 * j, ka);
+            }
+          } else if (CG == 2) {
             const uint32_t bar = mapa_u32(smem_u32(full_bar + stage), 0);      // the leader's barrier
             if (rank == 0) mbar_arrive_expect_tx(full_bar + stage, 2 * Cfg::STAGE_BYTES);
             tma_load_2d_cg2(sA, &tmA_hi, bar, ka, m0);
@@ -183,8 +203,10 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
     // ===================== MMA issuer (leader CTA only) =====================
     if (lane == 0 && rank == 0) {
       // operand planes are bf16 (training scratch, stand-alone entry) or fp16 (inference activations / packed weights)
-      const uint32_t idesc_full = g.fp16 ? make_idesc_f16(TC_BM * CG, BN) : make_idesc_bf16(TC_BM * CG, BN);
-      const uint32_t idesc_half = g.fp16 ? make_idesc_f16(TC_BM * CG, BN / 2) : make_idesc_bf16(TC_BM * CG, BN / 2);
+      const uint32_t major = g.mn_major ? (IDESC_A_MN | IDESC_B_MN) : 0u;
+      const uint32_t idesc_full = (g.fp16 ? make_idesc_f16(TC_BM * CG, BN) : make_idesc_bf16(TC_BM * CG, BN)) | major;
+      const uint32_t idesc_half = (g.fp16 ? make_idesc_f16(TC_BM * CG, BN / 2) : make_idesc_bf16(TC_BM * CG, BN / 2)) | major;
+      const uint64_t k_adv = g.mn_major ? 2048 >> 4 : 32 >> 4;   // one MMA's 16 k: 16 rows of 128 B, or 32 B inside the atom
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
       for (int it = 0, t; (t = tile_of(it)) < num_tiles; ++it) {
@@ -197,11 +219,13 @@ gemm_bf16x2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_cons
           fence_after_sync();
           const uint32_t sA = smem_u32(smem + stage * Cfg::STAGE_BYTES);
           const uint32_t sB = sA + Cfg::A_PLANES * Cfg::A_BYTES;
-          const uint64_t a_hi = make_desc_k128(sA), a_lo = make_desc_k128(sA + Cfg::A_BYTES);
-          const uint64_t b_hi = make_desc_k128(sB), b_lo = make_desc_k128(sB + Cfg::B_BYTES);
+          const uint64_t a_hi = g.mn_major ? make_desc_mn128(sA) : make_desc_k128(sA);
+          const uint64_t a_lo = g.mn_major ? make_desc_mn128(sA + Cfg::A_BYTES) : make_desc_k128(sA + Cfg::A_BYTES);
+          const uint64_t b_hi = g.mn_major ? make_desc_mn128(sB) : make_desc_k128(sB);
+          const uint64_t b_lo = g.mn_major ? make_desc_mn128(sB + Cfg::B_BYTES) : make_desc_k128(sB + Cfg::B_BYTES);
 #pragma unroll
           for (int k = 0; k < TC_BK / 16; ++k) {          // small cross terms first, then hi*hi
-            const uint64_t adv = static_cast<uint64_t>(k * 2);   // 32 bytes >> 4 inside the swizzle atom
+            const uint64_t adv = static_cast<uint64_t>(k) * k_adv;
             if (CG == 2) {
               if (NPROD == 3) mma_f16_cg2(tmem_d, a_lo + adv, b_hi + adv, idesc, (kb | k) != 0);
               if (NPROD != 1) mma_f16_cg2(tmem_d, a_hi + adv, b_lo + adv, idesc, NPROD == 3 ? 1 : (kb | k) != 0);
@@ -680,6 +704,12 @@ static int make_map(CUtensorMap *m, const __nv_bfloat16 *base, long long cols, l
   return 0;
 }
 
+// MN-major operand: bf16 matrix [k_rows][mn] with row pitch ld; box = 64 mn-columns x 64 k-rows (one 8 KB block of
+// the shared-memory tile, make_desc_mn128).  Columns >= mn and rows >= k_rows read as zero.
+static int make_map_mn(CUtensorMap *m, const __nv_bfloat16 *base, long long mn, long long k_rows, long long ld) {
+  return make_map(m, base, mn, k_rows, ld, TC_BK);
+}
+
 // Row-major output matrix [rows][cols] (pitch ld elements) written in boxes of 16 columns x 32 rows from a
 // dense (unswizzled) shared-memory slab.
 static int make_store_map(CUtensorMap *m, void *base, bool f32, long long cols, long long rows, long long ld) {
@@ -740,10 +770,18 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   const long long a_cols = (long long)g.a_col_z * (g.batch - 1) + g.K;
   const long long w_rows = (long long)g.b_row_z * (g.batch - 1) + g.N;
   int rc;
+  if (g.mn_major) {
+    const long long k_rows = g.k_rows > 0 ? g.k_rows : a_cols;     // a_cols: k extent over all problems z
+    if ((rc = make_map_mn(&ma_hi, g.A, g.M, k_rows, g.lda))) return rc;
+    if ((rc = make_map_mn(&ma_lo, g.A + (NPROD == 3 ? g.a_plane : 0), g.M, k_rows, g.lda))) return rc;
+    if ((rc = make_map_mn(&mb_hi, g.W, w_rows, k_rows, g.ldw))) return rc;
+    if ((rc = make_map_mn(&mb_lo, g.W + (NPROD == 1 ? 0 : g.w_plane), w_rows, k_rows, g.ldw))) return rc;
+  } else {
   if ((rc = make_map(&ma_hi, g.A, a_cols, g.M, g.lda, TC_BM))) return rc;
   if ((rc = make_map(&ma_lo, g.A + (NPROD == 3 ? g.a_plane : 0), a_cols, g.M, g.lda, TC_BM))) return rc;
   if ((rc = make_map(&mb_hi, g.W, g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
   if ((rc = make_map(&mb_lo, g.W + (NPROD == 1 ? 0 : g.w_plane), g.K, w_rows, g.ldw, Cfg::B_ROWS))) return rc;
+  }
   // Output maps: TMA stores need 16-byte aligned base and pitch; with batch > 1 a partial last chunk would
   // spill into the next problem's columns, so N must then be a multiple of the chunk width.
   CUtensorMap mc_hi = ma_hi, mc_lo = ma_hi;
@@ -763,7 +801,7 @@ static int launch_tc(const TcGemm &g, cudaStream_t st) {
   }
   TcKernelArgs k{};
   k.tma_store = tma_store;
-  k.fp16 = g.fp16;
+  k.fp16 = g.fp16; k.mn_major = g.mn_major;
   k.M = g.M; k.N = g.N; k.K = g.K; k.batch = g.batch;
   k.m_tiles = (g.M + TC_BM * CG - 1) / (TC_BM * CG); k.n_tiles = (g.N + BN - 1) / BN;
   k.a_col_z = g.a_col_z; k.b_row_z = g.b_row_z; k.c_col_z = g.c_col_z; k.bias_z = g.bias_z;
@@ -829,6 +867,7 @@ int gemm_bf16x2(const TcGemm &g, cudaStream_t st) {
     return PLR2_E_UNSUPPORTED;
   }
   if ((g.out_mode == TC_OUT_POOL || g.out_mode == TC_OUT_HEAD || g.frame_bias) && g.rows_per_frame < TC_BM) { set_error("gemm_bf16x2: per-frame epilogues need rows_per_frame >= %d", TC_BM); return PLR2_E_UNSUPPORTED; }
+  if (g.mn_major && (g.out_mode != TC_OUT_F32 || g.a_hi_only || g.frame_bias)) { set_error("gemm_bf16x2: MN-major operands are for plain FP32-output products"); return PLR2_E_UNSUPPORTED; }
   const bool hi_only = g.a_hi_only != 0;
   if (g.w_hi_only && !hi_only) { set_error("gemm_bf16x2: w_hi_only needs a_hi_only (single product)"); return PLR2_E_UNSUPPORTED; }
   if (g.w_hi_only) {              // single product X_hi W_hi (large layers only: 256-wide tiles on CTA pairs)
@@ -865,6 +904,20 @@ extern "C" int plr2_gemm_bf16x2(const void *A_planes, long long lda, long long a
   g.A = (const __nv_bfloat16 *)A_planes; g.lda = lda; g.a_plane = a_plane;
   g.W = (const __nv_bfloat16 *)W_planes; g.ldw = ldw; g.w_plane = w_plane;
   g.M = M; g.N = N; g.K = K; g.bias = bias; g.relu = relu; g.out_mode = plr2::TC_OUT_F32; g.Cf = C; g.ldc = ldc;
+  return plr2::gemm_bf16x2(g, (cudaStream_t)stream);
+}
+
+// Weight-gradient form on MN-major planes: C[M][N] (ldc) = A^T B with A = planes [k_rows][lda] (M columns used),
+// B = planes [k_rows][ldb] (N columns used); k_rows need not be a multiple of 64 (the tail reads as zero).
+extern "C" int plr2_gemm_bf16x2_tn(const void *A_planes, long long lda, long long a_plane, const void *B_planes,
+                                   long long ldb, long long b_plane, int M, int N, int k_rows, float *C,
+                                   long long ldc, void *stream) {
+  if (k_rows <= 0) { plr2::set_error("plr2_gemm_bf16x2_tn: k_rows=%d", k_rows); return PLR2_E_SHAPE; }
+  plr2::TcGemm g;
+  g.A = (const __nv_bfloat16 *)A_planes; g.lda = lda; g.a_plane = a_plane;
+  g.W = (const __nv_bfloat16 *)B_planes; g.ldw = ldb; g.w_plane = b_plane;
+  g.M = M; g.N = N; g.K = (k_rows + 63) / 64 * 64; g.k_rows = k_rows; g.mn_major = 1;
+  g.out_mode = plr2::TC_OUT_F32; g.Cf = C; g.ldc = ldc;
   return plr2::gemm_bf16x2(g, (cudaStream_t)stream);
 }
 

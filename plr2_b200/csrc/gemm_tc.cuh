@@ -19,6 +19,10 @@ struct TcGemm {
   int relu = 0, out_mode = TC_OUT_F32;
   int a_hi_only = 0;          // 1: use only the hi plane of X (2 MMAs per MAC; for layers whose output is only pooled)
   int w_hi_only = 0;          // 1 (with a_hi_only): single product X_hi W_hi (1 MMA per MAC)
+  // 1: both operands are stored MN-major - A as [k rows][M columns] (pitch lda), W as [k rows][N columns] (pitch
+  // ldw): C = A^T W, the weight-gradient form.  Problem z reads k-rows [z*a_col_z, +K) of BOTH operands and W
+  // columns [z*b_row_z, +N); k_rows = number of valid k-rows in memory (rows beyond it read as zero), 0 = all.
+  int mn_major = 0; long long k_rows = 0;
   int fp16 = 0;               // operand planes and TC_OUT_BF16X2 outputs are IEEE fp16 (11-bit mantissa) instead of bf16; same layout
   float *Cf = nullptr; long long ldc = 0;
   __nv_bfloat16 *Cb = nullptr; long long ldcb = 0, c_plane = 0;

@@ -197,6 +197,23 @@ __device__ __forceinline__ uint64_t make_desc_k128(uint32_t smem_addr) {
   return d;
 }
 
+// The same tile shape read MN-major (the operand is stored with M or N contiguous, i.e. [k rows][mn columns]:
+// the transposed operands of a weight gradient dW = dY^T X).  A TMA box {64 mn-elements, 64 k-rows} with
+// SWIZZLE_128B writes 64 rows of 128 bytes: in 16-byte units the canonical layout is
+// ((8, n), (8, k)) : ((1, LBO), (8, SBO)) - 64 contiguous mn-elements, further 64-element mn blocks LBO apart
+// (one box each, 8192 B), the 8 k-rows of a swizzle atom 128 B apart, groups of 8 k-rows SBO = 1024 B apart.
+// One MMA (K = 16) consumes 16 k-rows = 2048 B of every block.
+__device__ __forceinline__ uint64_t make_desc_mn128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);        // [0,14)  start address
+  d |= static_cast<uint64_t>(8192 >> 4) << 16;                   // [16,30) leading byte offset: next 64-wide mn block
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;                   // [32,46) stride byte offset: next 8 k-rows
+  d |= static_cast<uint64_t>(1) << 46;                           // [46,48) descriptor version
+  d |= static_cast<uint64_t>(2) << 61;                           // [61,64) SWIZZLE_128B
+  return d;
+}
+constexpr uint32_t IDESC_A_MN = 1u << 15, IDESC_B_MN = 1u << 16;   // operand major bits of the instruction descriptor
+
 // Instruction descriptor, kind::f16: D=F32 (1<<4), A=BF16 (1<<7), B=BF16 (1<<10), both K-major,
 // N>>3 at bit 17, M>>4 at bit 24.
 __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
