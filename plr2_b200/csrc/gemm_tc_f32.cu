@@ -13,6 +13,7 @@
 // or passes through a ReLU mask, finishes with an element-wise combine out of a scratch C.
 // The packs cost 8 bytes per operand element of HBM traffic; at the training shapes (8 frames =
 // 8000 rows) every problem is launch/latency bound either way.
+#include <stdlib.h>
 #include "gemm.cuh"
 #include "gemm_tc.cuh"
 
@@ -206,6 +207,13 @@ relu_signsafe_kernel(GemmArgs g, const float *__restrict__ nx, const float *__re
   }
 }
 
+// PLR2_TC_WGRAD_MN=0 restores the transposing packs for the weight gradients (A/B experiments)
+static bool tc_wgrad_mn() {
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("PLR2_TC_WGRAD_MN"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
+
 bool gemm_tc_eligible(const GemmArgs &g) {
   // tiny N (conv1's 3 input channels as a weight-gradient N) and K stay on the SIMT kernel
   return g.M > 0 && g.N >= 16 && g.K >= 8 && !(g.relu && g.accumulate);
@@ -231,6 +239,44 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     return 0;
   }
   int rc;
+  // Weight-gradient layout (A m-contiguous, B n-contiguous: both operands are [k rows][columns] in memory): the
+  // tensor cores read such planes MN-major, so the split is a straight element-wise pass (float4 in, 8-byte stores
+  // out, no transpose through shared memory, no K padding - rows past K read as zero through the tensor map).
+  if (batch == 1 && g.sam == 1 && g.sbn == 1 && !g.relu && g.bias == nullptr && g.frame_bias == nullptr && tc_wgrad_mn()) {
+    const int Mp = (g.M + 63) / 64 * 64, Np = (g.N + 63) / 64 * 64;
+    if ((size_t)g.K * Mp <= S.elems && (size_t)g.K * Np <= S.elems) {
+      const long long tiles = (long long)((g.M + 255) / 256) * ((g.N + 127) / 128);
+      long long want = (74 + tiles - 1) / tiles;
+      if (want > g.K / 512) want = g.K / 512;
+      if (want > 32) want = 32;
+      while (want > 1 && (size_t)g.M * want * g.N > S.elems) --want;
+      int splits = (int)(want < 1 ? 1 : want);
+      const int Ks = ((g.K + splits - 1) / splits + 63) / 64 * 64;
+      splits = (g.K + Ks - 1) / Ks;
+      const bool need_ct = splits > 1 || g.accumulate || g.relu_mask != nullptr;
+      if (!need_ct || (size_t)g.M * splits * g.N <= S.elems) {
+        if ((rc = pack_pair(pack_desc(g.A, g.sak, 1, g.K, g.M, Mp, 1, S.pa, Mp, (long long)S.elems, 0),
+                            pack_desc(g.B, g.sbk, 1, g.K, g.N, Np, 1, S.pb, Np, (long long)S.elems, 0), st))) return rc;
+        TcGemm t;
+        t.A = S.pa; t.lda = Mp; t.a_plane = (long long)S.elems;
+        t.W = S.pb; t.ldw = Np; t.w_plane = (long long)S.elems;
+        t.M = g.M; t.N = g.N; t.K = Ks; t.batch = splits; t.a_col_z = Ks; t.b_row_z = 0;
+        t.mn_major = 1; t.k_rows = g.K;
+        t.out_mode = TC_OUT_F32;
+        if (need_ct) { t.Cf = S.ct; t.ldc = (long long)splits * g.N; t.c_col_z = g.N; }
+        else { t.Cf = g.C; t.ldc = g.ldc; t.c_col_z = 0; }
+        if ((rc = gemm_bf16x2(t, st))) return rc;
+        if (need_ct) {
+          const long long total = (long long)g.M * g.N;
+          const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+          combine_kernel<<<blocks, 256, 0, st>>>(S.ct, (long long)splits * g.N, splits, g.C, g.ldc, g.relu_mask, g.ldmask,
+                                                g.M, g.N, g.accumulate);
+          return check_launch("gemm_tc_f32: combine");
+        }
+        return 0;
+      }
+    }
+  }
   // Split-K: a contraction over the points (weight gradients, K = frames * num_points) with a handful of
   // output tiles would run on a handful of SMs.  Its K chunks become the batch dimension of the launch
   // (chunk z = columns [z*Ks, +Ks) of the packed A, row block z of the packed B) and the partial products
