@@ -20,6 +20,11 @@ struct GemmArgs {
   int relu = 0, accumulate = 0;
   int batch = 1; long long zA = 0, zB = 0, zC = 0, zbias = 0, zfb = 0, zmask = 0;
   int k_per_split = 0, splits = 1;   // filled by the launcher
+  // Tensor-core training path only: A's split planes may be taken from the scratch if the immediately preceding
+  // weight-gradient call on this stream packed the SAME matrix (dW = dY^T X then dX = dY W: dY is split once).
+  // A hint - honoured only when the scratch record matches pointer, shape and pitch; the caller guarantees that
+  // the matrix was not written in between.
+  int reuse_a_planes = 0;
 };
 
 // FP32 SIMT GEMM.  split_k > 1 adds partial sums atomically into C (needs accumulate=1, no relu/mask).

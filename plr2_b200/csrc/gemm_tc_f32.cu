@@ -119,6 +119,13 @@ static PackDesc pack_desc(const float *src, long long s_row, long long s_col, in
   return d;
 }
 
+// What the A scratch planes currently hold (per host thread: a forward/backward is issued by one thread).
+struct PlaneRecord {
+  const float *src = nullptr; long long s_row = 0; int rows = 0, cols = 0; long long pitch = 0;
+  const __nv_bfloat16 *dst = nullptr; cudaStream_t st = nullptr;
+};
+static thread_local PlaneRecord g_a_planes;
+
 static int pack_pair(const PackDesc &a, const PackDesc &b, cudaStream_t st) {
   const long long blocks = (long long)a.blocks + b.blocks;
   if (blocks <= 0 || blocks > 0x7fffffffLL) { set_error("pack_split: bad block count"); return PLR2_E_SHAPE; }
@@ -219,9 +226,62 @@ bool gemm_tc_eligible(const GemmArgs &g) {
   return g.M > 0 && g.N >= 16 && g.K >= 8 && !(g.relu && g.accumulate);
 }
 
+// Weight-gradient layout (A m-contiguous, B n-contiguous: both operands are [k rows][columns] in memory): the
+// tensor cores read such planes MN-major, so the split is a straight element-wise pass (float4 in, 8-byte stores
+// out, no transpose through shared memory, no K padding - rows past K read as zero through the tensor map).
+// `heads` > 1: stacked problems whose dY / X are adjacent column blocks of ONE matrix each (the r|t|c heads): the
+// matrices are split once, full width, and every head runs on its column range of the planes.
+// Returns -1 when the scratch cannot hold the problem (the caller falls back to the transposing path).
+static int wgrad_mn(const GemmArgs &g, int heads, const TcScratch &S, cudaStream_t st) {
+  const int Mt = g.M * heads, Nt = g.N * heads;
+  const int Mp = (Mt + 63) / 64 * 64, Np = (Nt + 63) / 64 * 64;
+  if ((size_t)g.K * Mp > S.elems || (size_t)g.K * Np > S.elems) return -1;
+  const long long tiles = (long long)((g.M + 255) / 256) * ((g.N + 127) / 128) * heads;
+  long long want = (74 + tiles - 1) / tiles;
+  if (want > g.K / 512) want = g.K / 512;
+  if (want > 32) want = 32;
+  while (want > 1 && (size_t)Mt * want * g.N > S.elems) --want;
+  int splits = (int)(want < 1 ? 1 : want);
+  const int Ks = ((g.K + splits - 1) / splits + 63) / 64 * 64;
+  splits = (g.K + Ks - 1) / Ks;
+  const bool need_ct = splits > 1 || g.accumulate || g.relu_mask != nullptr;
+  if (need_ct && (size_t)Mt * splits * g.N > S.elems) return -1;
+  int rc;
+  if ((rc = pack_pair(pack_desc(g.A, g.sak, 1, g.K, Mt, Mp, 1, S.pa, Mp, (long long)S.elems, 0),
+                      pack_desc(g.B, g.sbk, 1, g.K, Nt, Np, 1, S.pb, Np, (long long)S.elems, 0), st))) return rc;
+  // dY as [rows][Mp] planes is also the K-major A operand of the input gradient that follows
+  g_a_planes.src = g.A; g_a_planes.s_row = g.sak; g_a_planes.rows = g.K; g_a_planes.cols = Mt;
+  g_a_planes.pitch = Mp; g_a_planes.dst = S.pa; g_a_planes.st = st;
+  for (int z = 0; z < heads; ++z) {
+    float *ct = S.ct + (size_t)z * g.M * splits * g.N;
+    float *C = g.C + z * g.zC;
+    TcGemm t;
+    t.A = S.pa + (size_t)z * g.M; t.lda = Mp; t.a_plane = (long long)S.elems;
+    t.W = S.pb + (size_t)z * g.N; t.ldw = Np; t.w_plane = (long long)S.elems;
+    t.M = g.M; t.N = g.N; t.K = Ks; t.batch = splits; t.a_col_z = Ks; t.b_row_z = 0;
+    t.mn_major = 1; t.k_rows = g.K;
+    t.out_mode = TC_OUT_F32;
+    if (need_ct) { t.Cf = ct; t.ldc = (long long)splits * g.N; t.c_col_z = g.N; }
+    else { t.Cf = C; t.ldc = g.ldc; t.c_col_z = 0; }
+    if ((rc = gemm_bf16x2(t, st))) return rc;
+    if (need_ct) {
+      const long long total = (long long)g.M * g.N;
+      const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+      combine_kernel<<<blocks, 256, 0, st>>>(ct, (long long)splits * g.N, splits, C, g.ldc,
+                                            g.relu_mask ? g.relu_mask + z * g.zmask : nullptr, g.ldmask, g.M, g.N, g.accumulate);
+    }
+  }
+  return need_ct ? check_launch("gemm_tc_f32: combine", heads) : 0;
+}
+
 int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
   const int batch = g.batch < 1 ? 1 : g.batch;
   const int Kp = (g.K + 63) / 64 * 64;
+  if (g.sam == 1 && g.sbn == 1 && !g.relu && g.bias == nullptr && g.frame_bias == nullptr && tc_wgrad_mn() &&
+      (batch == 1 || (g.zA == g.M && g.zB == g.N && g.M % 8 == 0 && g.N % 8 == 0))) {
+    const int rc = wgrad_mn(g, batch, S, st);
+    if (rc >= 0) return rc;
+  }
   // One launch serves the whole batch when problem z differs by a COLUMN offset of C (the r/t/c heads of
   // the forward and of the input gradient); stacked weight gradients (z advances whole matrices) are looped.
   const bool one = batch == 1 || (g.frame_bias == nullptr && g.zC >= g.N && g.zC * (batch - 1) + g.N <= g.ldc && g.N % 16 == 0);
@@ -239,44 +299,6 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     return 0;
   }
   int rc;
-  // Weight-gradient layout (A m-contiguous, B n-contiguous: both operands are [k rows][columns] in memory): the
-  // tensor cores read such planes MN-major, so the split is a straight element-wise pass (float4 in, 8-byte stores
-  // out, no transpose through shared memory, no K padding - rows past K read as zero through the tensor map).
-  if (batch == 1 && g.sam == 1 && g.sbn == 1 && !g.relu && g.bias == nullptr && g.frame_bias == nullptr && tc_wgrad_mn()) {
-    const int Mp = (g.M + 63) / 64 * 64, Np = (g.N + 63) / 64 * 64;
-    if ((size_t)g.K * Mp <= S.elems && (size_t)g.K * Np <= S.elems) {
-      const long long tiles = (long long)((g.M + 255) / 256) * ((g.N + 127) / 128);
-      long long want = (74 + tiles - 1) / tiles;
-      if (want > g.K / 512) want = g.K / 512;
-      if (want > 32) want = 32;
-      while (want > 1 && (size_t)g.M * want * g.N > S.elems) --want;
-      int splits = (int)(want < 1 ? 1 : want);
-      const int Ks = ((g.K + splits - 1) / splits + 63) / 64 * 64;
-      splits = (g.K + Ks - 1) / Ks;
-      const bool need_ct = splits > 1 || g.accumulate || g.relu_mask != nullptr;
-      if (!need_ct || (size_t)g.M * splits * g.N <= S.elems) {
-        if ((rc = pack_pair(pack_desc(g.A, g.sak, 1, g.K, g.M, Mp, 1, S.pa, Mp, (long long)S.elems, 0),
-                            pack_desc(g.B, g.sbk, 1, g.K, g.N, Np, 1, S.pb, Np, (long long)S.elems, 0), st))) return rc;
-        TcGemm t;
-        t.A = S.pa; t.lda = Mp; t.a_plane = (long long)S.elems;
-        t.W = S.pb; t.ldw = Np; t.w_plane = (long long)S.elems;
-        t.M = g.M; t.N = g.N; t.K = Ks; t.batch = splits; t.a_col_z = Ks; t.b_row_z = 0;
-        t.mn_major = 1; t.k_rows = g.K;
-        t.out_mode = TC_OUT_F32;
-        if (need_ct) { t.Cf = S.ct; t.ldc = (long long)splits * g.N; t.c_col_z = g.N; }
-        else { t.Cf = g.C; t.ldc = g.ldc; t.c_col_z = 0; }
-        if ((rc = gemm_bf16x2(t, st))) return rc;
-        if (need_ct) {
-          const long long total = (long long)g.M * g.N;
-          const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-          combine_kernel<<<blocks, 256, 0, st>>>(S.ct, (long long)splits * g.N, splits, g.C, g.ldc, g.relu_mask, g.ldmask,
-                                                g.M, g.N, g.accumulate);
-          return check_launch("gemm_tc_f32: combine");
-        }
-        return 0;
-      }
-    }
-  }
   // Split-K: a contraction over the points (weight gradients, K = frames * num_points) with a handful of
   // output tiles would run on a handful of SMs.  Its K chunks become the batch dimension of the launch
   // (chunk z = columns [z*Ks, +Ks) of the packed A, row block z of the packed B) and the partial products
@@ -295,6 +317,7 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     splits = (g.K + Ks - 1) / Ks;
     const size_t kp_all = (size_t)splits * Ks;
     if ((size_t)g.M * kp_all > S.elems || (size_t)g.N * kp_all > S.elems) return gemm_f32(g, 1, st);
+    g_a_planes.src = nullptr;
     if ((rc = pack_pair(pack_desc(g.A, g.sam, g.sak, g.M, g.K, (int)kp_all, 1, S.pa, (long long)kp_all, (long long)S.elems, 0),
                         pack_desc(g.B, g.sbn, g.sbk, g.N, g.K, Ks, splits, S.pb, Ks, (long long)S.elems, (long long)g.N * Ks), st))) return rc;
     TcGemm t;
@@ -313,8 +336,16 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
   const bool need_ct = g.accumulate || g.relu_mask != nullptr;
   const size_t a_elems = (size_t)g.M * batch * Kp, b_elems = (size_t)g.N * batch * Kp, c_elems = (size_t)g.M * batch * g.N;
   if (a_elems > S.elems || b_elems > S.elems || (need_ct && c_elems > S.elems)) return gemm_f32(g, 1, st);
+  const PlaneRecord &R = g_a_planes;
+  // (batched: problem z reads columns [z*zA, +K) of ONE matrix; its planes line up when the blocks are unpadded)
+  const bool reuse_a = g.reuse_a_planes && g.sak == 1 && R.src == g.A && R.s_row == g.sam && R.rows == g.M &&
+                       R.cols == batch * g.K && R.pitch == (long long)batch * Kp && R.dst == S.pa && R.st == st &&
+                       (batch == 1 || (g.zA == g.K && g.K == Kp));
+  if (!reuse_a) g_a_planes.src = nullptr;
   for (int z = 0; z < batch; ++z) {
-    if ((rc = pack_pair(pack_desc(g.A + z * g.zA, g.sam, g.sak, g.M, g.K, Kp, 1, S.pa + (size_t)z * Kp, (long long)batch * Kp, (long long)S.elems, 0),
+    PackDesc pa_d = pack_desc(g.A + z * g.zA, g.sam, g.sak, g.M, g.K, Kp, 1, S.pa + (size_t)z * Kp, (long long)batch * Kp, (long long)S.elems, 0);
+    if (reuse_a) pa_d.blocks = 0;                     // the planes of the weight gradient before are still in place
+    if ((rc = pack_pair(pa_d,
                         pack_desc(g.B + z * g.zB, g.sbn, g.sbk, g.N, g.K, Kp, 1, S.pb + (size_t)z * g.N * Kp, Kp, (long long)S.elems, 0), st))) return rc;
   }
   TcGemm t;

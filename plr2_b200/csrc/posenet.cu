@@ -236,7 +236,7 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
   RC(wgrad(gemm_tn(W.x6, 1024, W.x5, 512, gp + L.c6w, 512, 1024, 512, R), cx, st));
   RC(bgrad(W.x6, 1024, R, 1024, gp + L.c6b, W.red, st));
   GemmArgs g = gemm_nn(W.x6, 1024, pk + L.c6w, 512, W.x5, 512, R, 512, 1024);     // dx5 (in place)
-  g.relu_mask = W.x5; g.ldmask = 512;
+  g.relu_mask = W.x5; g.ldmask = 512; g.reuse_a_planes = 1;
   RC(gemm_run(g, 1, cx, st));
   const float *a5 = L.c5k == 256 ? W.pf + 128 : W.pf;
   RC(wgrad(gemm_tn(W.x5, 512, a5, 384, gp + L.c5w, L.c5k, 512, L.c5k, R), cx, st));
@@ -244,11 +244,11 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
   const int off2 = L.c5k == 256 ? 0 : 128;    // column of pointfeat_2 inside conv5's input
   if (L.c5k == 384) {                         // refiner: conv5 also reads pointfeat_1
     g = gemm_nn(W.x5, 512, pk + L.c5w, 384, W.dpf, 384, R, 128, 512);
-    g.accumulate = dpf_has_heads ? 1 : 0;
+    g.accumulate = dpf_has_heads ? 1 : 0; g.reuse_a_planes = 1;
     RC(gemm_run(g, 1, cx, st));
   }
   g = gemm_nn(W.x5, 512, pk + L.c5w + off2, L.c5k, W.dpf + 128, 384, R, 256, 512);  // d pointfeat_2
-  g.accumulate = dpf_has_heads ? 1 : 0;
+  g.accumulate = dpf_has_heads ? 1 : 0; g.reuse_a_planes = 1;
   g.relu_mask = W.pf + 128; g.ldmask = 384;
   RC(gemm_run(g, 1, cx, st));
   // conv2 / e_conv2
@@ -258,7 +258,7 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
     RC(wgrad(gemm_tn(W.dpf + cout, 384, W.pf + cin, 384, gp + wo, 64, 128, 64, R), cx, st));
     RC(bgrad(W.dpf + cout, 384, R, 128, gp + bo, W.red, st));
     g = gemm_nn(W.dpf + cout, 384, pk + wo, 64, W.dpf + cin, 384, R, 64, 128);
-    g.accumulate = 1; g.relu_mask = W.pf + cin; g.ldmask = 384;
+    g.accumulate = 1; g.relu_mask = W.pf + cin; g.ldmask = 384; g.reuse_a_planes = 1;
     RC(gemm_run(g, 1, cx, st));
   }
   // conv1 (3 -> 64) and e_conv1 (32 -> 64)
@@ -440,7 +440,7 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
     RC(wgrad(gemm_tn(W.out + L.oc[h], L.ldo, W.h3 + h * 128, 384, gp + L.h4w + row * 128, 128, L.on[h], 128, R), cx, st));
     RC(bgrad(W.out + L.oc[h], L.ldo, R, L.on[h], gp + L.h4b + row, W.red, st));
     GemmArgs g = gemm_nn(W.out + L.oc[h], L.ldo, pk + L.h4w + row * 128, 128, W.h3 + h * 128, 384, R, 128, L.on[h]);
-    g.relu_mask = W.h3 + h * 128; g.ldmask = 384;
+    g.relu_mask = W.h3 + h * 128; g.ldmask = 384; g.reuse_a_planes = 1;
     RC(gemm_run(g, 1, cx, st));
     row += L.on[h];
   }
@@ -451,6 +451,7 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   RC(bgrad(W.h3, 384, R, 384, gp + L.h3b, W.red, st));
   g = gemm_nn(W.h3, 384, pk + L.h3w, 256, W.h2, 768, R, 256, 128);
   g.batch = 3; g.zA = 128; g.zB = 128 * 256; g.zC = 256; g.relu_mask = W.h2; g.ldmask = 768; g.zmask = 256;
+  g.reuse_a_planes = 1;
   RC(gemm_run(g, 1, cx, st));
   // conv2_*
   g = gemm_tn(W.h2, 768, W.h1, 1920, gp + L.h2w, 640, 256, 640, R);
@@ -459,9 +460,15 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   RC(bgrad(W.h2, 768, R, 768, gp + L.h2b, W.red, st));
   g = gemm_nn(W.h2, 768, pk + L.h2w, 640, W.h1, 1920, R, 640, 256);
   g.batch = 3; g.zA = 256; g.zB = 256 * 640; g.zC = 640; g.relu_mask = W.h1; g.ldmask = 1920; g.zmask = 640;
+  g.reuse_a_planes = 1;
   RC(gemm_run(g, 1, cx, st));
   // conv1_*: per-point part, per-frame (pooled) part, bias
   RC(wgrad(gemm_tn(W.h1, 1920, W.pf, 384, gp + L.h1pf, 384, 1920, 384, R), cx, st));
+  {  // d pf (head part) straight after the weight gradient: both read the same split of d h1
+    GemmArgs gd = gemm_nn(W.h1, 1920, pk + L.h1pf, 384, W.dpf, 384, R, 384, 1920);
+    gd.reuse_a_planes = 1;
+    RC(gemm_run(gd, 1, cx, st));
+  }
   RC(segment_colsum(W.h1, 1920, F, N, 1920, 1.0f, W.dhb, 1920, st));
   RC(bgrad(W.dhb, 1920, F, 1920, gp + L.h1b, W.red, st));
   RC(gemm_run(gemm_tn(W.dhb, 1920, W.ap, 1024, gp + L.h1ap, 1024, 1920, 1024, F), 1, cx, st));
@@ -472,7 +479,6 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
     ga.accumulate = 1;
     RC(gemm_run(ga, auto_split(F, 1024, 1, 1920), cx, st));
   }
-  RC(gemm_run(gemm_nn(W.h1, 1920, pk + L.h1pf, 384, W.dpf, 384, R, 384, 1920), 1, cx, st));
   // every head-weight gradient (packed region [h1pf, c1b)) is final here: a caller that overlaps its gradient
   // all-reduce with the trunk backward waits on this event (plr2_set_backward_stage_event, one-shot)
   if (g_stage_event != nullptr) {
