@@ -135,20 +135,59 @@ static int pack_pair(const PackDesc &a, const PackDesc &b, cudaStream_t st) {
 
 // C = ((accumulate ? C : 0) + sum_z Ct[:, z*N + n]) * (mask > 0)   (the epilogue order of gemm_f32_kernel;
 // nsum > 1: partial products of a split-K problem, summed in chunk order)
+// VEC: four consecutive columns per thread through 16-byte accesses (N, the pitches and the bases allow it).
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 combine_kernel(const float *__restrict__ ct, long long ldct, int nsum, float *C, long long ldc, const float *mask,
                long long ldmask, int M, int N, int accumulate) {
-  const long long total = (long long)M * N;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / N;
-    const int n = (int)(i - r * N);
-    float v = ct[r * ldct + n];
-    for (int z = 1; z < nsum; ++z) v += ct[r * ldct + (long long)z * N + n];
+  constexpr int W = VEC ? 4 : 1;
+  const unsigned ncw = (unsigned)(N / W);
+  const unsigned total = (unsigned)M * ncw;                    // < 2^31 (checked by the launcher)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned r = i / ncw;
+    const int n = (int)(i - r * ncw) * W;
+    const float *src = ct + r * ldct + n;
     float *c = C + r * ldc + n;
-    if (accumulate) v += *c;
-    if (mask != nullptr && !(mask[r * ldmask + n] > 0.f)) v = 0.f;   // mask may alias C: same thread, same element
-    *c = v;
+    float v[W];
+    if (VEC) {
+      float4 q = __ldg(reinterpret_cast<const float4 *>(src));
+      for (int z = 1; z < nsum; ++z) {
+        const float4 p = __ldg(reinterpret_cast<const float4 *>(src + (long long)z * N));
+        q.x += p.x; q.y += p.y; q.z += p.z; q.w += p.w;
+      }
+      v[0] = q.x; v[1 % W] = q.y; v[2 % W] = q.z; v[3 % W] = q.w;
+      if (accumulate) {
+        const float4 p = *reinterpret_cast<const float4 *>(c);
+        v[0] += p.x; v[1 % W] += p.y; v[2 % W] += p.z; v[3 % W] += p.w;
+      }
+      if (mask != nullptr) {                                   // mask may alias C: same thread, same elements
+        const float4 m = *reinterpret_cast<const float4 *>(mask + r * ldmask + n);
+        if (!(m.x > 0.f)) v[0] = 0.f;
+        if (!(m.y > 0.f)) v[1 % W] = 0.f;
+        if (!(m.z > 0.f)) v[2 % W] = 0.f;
+        if (!(m.w > 0.f)) v[3 % W] = 0.f;
+      }
+      *reinterpret_cast<float4 *>(c) = make_float4(v[0], v[1 % W], v[2 % W], v[3 % W]);
+    } else {
+      v[0] = src[0];
+      for (int z = 1; z < nsum; ++z) v[0] += src[(long long)z * N];
+      if (accumulate) v[0] += *c;
+      if (mask != nullptr && !(mask[r * ldmask + n] > 0.f)) v[0] = 0.f;
+      *c = v[0];
+    }
   }
+}
+
+static int combine(const float *ct, long long ldct, int nsum, float *C, long long ldc, const float *mask, long long ldmask,
+                   int M, int N, int accumulate, cudaStream_t st) {
+  if ((long long)M * N >= 0x7fffffffLL) { set_error("gemm_tc_f32: combine: %d x %d elements", M, N); return PLR2_E_SHAPE; }
+  auto al = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool vec = N % 4 == 0 && ldct % 4 == 0 && ldc % 4 == 0 && al(ct) && al(C) && (mask == nullptr || (ldmask % 4 == 0 && al(mask)));
+  const long long items = (long long)M * (vec ? N / 4 : N);
+  const int blocks = (int)((items + 255) / 256 < 148 * 8 ? (items + 255) / 256 : 148 * 8);
+  if (vec) combine_kernel<true><<<blocks, 256, 0, st>>>(ct, ldct, nsum, C, ldc, mask, ldmask, M, N, accumulate);
+  else combine_kernel<false><<<blocks, 256, 0, st>>>(ct, ldct, nsum, C, ldc, mask, ldmask, M, N, accumulate);
+  return 0;
 }
 
 // ---- sign-safe ReLU of a training forward --------------------------------------------------
@@ -174,6 +213,8 @@ row_norm_kernel(const float *__restrict__ src, long long s_row, long long s_col,
 
 // C (pre-activation, written by the tensor-core launch without ReLU) -> relu(C), with the elements inside the
 // error bound recomputed from the FP32 operands.  blockIdx.y = problem z of a batched launch.
+// W = 4: four consecutive columns per lane through 16-byte accesses (N, ldc and the bases allow it).
+template <int W>
 __global__ void __launch_bounds__(256)
 relu_signsafe_kernel(GemmArgs g, const float *__restrict__ nx, const float *__restrict__ nw) {
   const int z = blockIdx.y;
@@ -183,34 +224,48 @@ relu_signsafe_kernel(GemmArgs g, const float *__restrict__ nx, const float *__re
   const float *fb = g.frame_bias ? g.frame_bias + z * g.zfb : nullptr;
   nx += (size_t)z * g.M;
   nw += (size_t)z * g.N;
-  const long long total = (long long)g.M * g.N;
-  const int lane = threadIdx.x & 31;
+  const unsigned ncw = (unsigned)(g.N / W);
+  const unsigned total = (unsigned)g.M * ncw;                  // < 2^31 (checked by the launcher)
+  const unsigned lane = threadIdx.x & 31;
   // warp-uniform trip count: every lane stays in the loop so that flagged elements can be recomputed by the
   // whole warp (coalesced reads along k, butterfly sum) instead of by one lane walking K serially
-  for (long long base = (blockIdx.x * (long long)blockDim.x + threadIdx.x) - lane; base < total;
-       base += (long long)gridDim.x * blockDim.x) {
-    const long long i = base + lane;
+  for (unsigned base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < total; base += gridDim.x * blockDim.x) {
+    const unsigned i = base + lane;
     const bool live = i < total;
-    const int r = live ? (int)(i / g.N) : 0;
-    const int n = live ? (int)(i - (long long)r * g.N) : 0;
-    float y = live ? C[(long long)r * g.ldc + n] : 1.f;
-    const bool flag = live && fabsf(y) < SIGN_TAU * nx[r] * nw[n];
-    unsigned todo = __ballot_sync(0xffffffffu, flag);
-    while (todo) {
-      const int src = __ffs(todo) - 1;
-      todo &= todo - 1;
-      const int rr = __shfl_sync(0xffffffffu, r, src), nn = __shfl_sync(0xffffffffu, n, src);
-      const float *a = A + (long long)rr * g.sam, *b = B + (long long)nn * g.sbn;
-      float acc = 0.f;
-      for (int k = lane; k < g.K; k += 32) acc = fmaf(__ldg(a + (long long)k * g.sak), __ldg(b + (long long)k * g.sbk), acc);
-      acc = warp_sum(acc);
-      if (lane == src) {
-        if (bias) acc += bias[nn];
-        if (fb) acc += fb[(long long)(rr / g.rows_per_frame) * g.ldfb + nn];
-        y = acc;
+    const int r = live ? (int)(i / ncw) : 0;
+    const int n = live ? (int)(i - (unsigned)r * ncw) * W : 0;
+    float *cp = C + (long long)r * g.ldc + n;
+    float y[W];
+    if (W == 4) {
+      const float4 q = live ? *reinterpret_cast<const float4 *>(cp) : make_float4(1.f, 1.f, 1.f, 1.f);
+      y[0] = q.x; y[1 % W] = q.y; y[2 % W] = q.z; y[3 % W] = q.w;
+    } else {
+      y[0] = live ? *cp : 1.f;
+    }
+    const float bound = live ? SIGN_TAU * nx[r] : 0.f;
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      const bool flag = live && fabsf(y[j]) < bound * nw[n + j];
+      unsigned todo = __ballot_sync(0xffffffffu, flag);
+      while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int rr = __shfl_sync(0xffffffffu, r, src), nn = __shfl_sync(0xffffffffu, n, src) + j;
+        const float *a = A + (long long)rr * g.sam, *b = B + (long long)nn * g.sbn;
+        float acc = 0.f;
+        for (int k = lane; k < g.K; k += 32) acc = fmaf(__ldg(a + (long long)k * g.sak), __ldg(b + (long long)k * g.sbk), acc);
+        acc = warp_sum(acc);
+        if ((int)lane == src) {
+          if (bias) acc += bias[nn];
+          if (fb) acc += fb[(long long)(rr / g.rows_per_frame) * g.ldfb + nn];
+          y[j] = acc;
+        }
       }
     }
-    if (live) C[(long long)r * g.ldc + n] = fmaxf(y, 0.f);
+    if (live) {
+      if (W == 4) *reinterpret_cast<float4 *>(cp) = make_float4(fmaxf(y[0], 0.f), fmaxf(y[1 % W], 0.f), fmaxf(y[2 % W], 0.f), fmaxf(y[3 % W], 0.f));
+      else *cp = fmaxf(y[0], 0.f);
+    }
   }
 }
 
@@ -265,10 +320,8 @@ static int wgrad_mn(const GemmArgs &g, int heads, const TcScratch &S, cudaStream
     else { t.Cf = C; t.ldc = g.ldc; t.c_col_z = 0; }
     if ((rc = gemm_bf16x2(t, st))) return rc;
     if (need_ct) {
-      const long long total = (long long)g.M * g.N;
-      const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-      combine_kernel<<<blocks, 256, 0, st>>>(ct, (long long)splits * g.N, splits, C, g.ldc,
-                                            g.relu_mask ? g.relu_mask + z * g.zmask : nullptr, g.ldmask, g.M, g.N, g.accumulate);
+      if ((rc = combine(ct, (long long)splits * g.N, splits, C, g.ldc, g.relu_mask ? g.relu_mask + z * g.zmask : nullptr,
+                        g.ldmask, g.M, g.N, g.accumulate, st))) return rc;
     }
   }
   return need_ct ? check_launch("gemm_tc_f32: combine", heads) : 0;
@@ -327,10 +380,7 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     t.a_col_z = Ks; t.b_row_z = g.N;
     t.out_mode = TC_OUT_F32; t.Cf = S.ct; t.ldc = (long long)splits * g.N; t.c_col_z = g.N;
     if ((rc = gemm_bf16x2(t, st))) return rc;
-    const long long total = (long long)g.M * g.N;
-    const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-    combine_kernel<<<blocks, 256, 0, st>>>(S.ct, (long long)splits * g.N, splits, g.C, g.ldc, g.relu_mask, g.ldmask,
-                                          g.M, g.N, g.accumulate);
+    if ((rc = combine(S.ct, (long long)splits * g.N, splits, g.C, g.ldc, g.relu_mask, g.ldmask, g.M, g.N, g.accumulate, st))) return rc;
     return check_launch("gemm_tc_f32: combine");
   }
   const bool need_ct = g.accumulate || g.relu_mask != nullptr;
@@ -366,19 +416,20 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     float *nx = S.ct, *nw = S.ct + (size_t)batch * g.M;
     row_norm_kernel<<<dim3((g.M + 7) / 8, batch), 256, 0, st>>>(g.A, g.sam, g.sak, g.zA, g.M, g.K, nx);
     row_norm_kernel<<<dim3((g.N + 7) / 8, batch), 256, 0, st>>>(g.B, g.sbn, g.sbk, g.zB, g.N, g.K, nw);
-    const long long total = (long long)g.M * g.N;
-    const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    if ((long long)g.M * g.N >= 0x7fffffffLL) { set_error("gemm_tc_f32: sign-safe relu: %d x %d elements", g.M, g.N); return PLR2_E_SHAPE; }
+    const bool vec = g.N % 4 == 0 && g.ldc % 4 == 0 && g.zC % 4 == 0 && (reinterpret_cast<uintptr_t>(g.C) & 15) == 0;
+    const long long items = (long long)g.M * (vec ? g.N / 4 : g.N);
+    const int blocks = (int)((items + 255) / 256 < 148 * 16 ? (items + 255) / 256 : 148 * 16);
     GemmArgs gs = g;
     gs.batch = batch;
-    relu_signsafe_kernel<<<dim3(blocks, batch), 256, 0, st>>>(gs, nx, nw);
+    if (vec) relu_signsafe_kernel<4><<<dim3(blocks, batch), 256, 0, st>>>(gs, nx, nw);
+    else relu_signsafe_kernel<1><<<dim3(blocks, batch), 256, 0, st>>>(gs, nx, nw);
     if ((rc = check_launch("gemm_tc_f32: sign-safe relu", 3))) return rc;
   }
   if (need_ct) {
     for (int z = 0; z < batch; ++z) {
-      const long long total = (long long)g.M * g.N;
-      const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-      combine_kernel<<<blocks, 256, 0, st>>>(S.ct + (size_t)z * g.N, (long long)batch * g.N, 1, g.C + z * g.zC, g.ldc,
-                                            g.relu_mask ? g.relu_mask + z * g.zmask : nullptr, g.ldmask, g.M, g.N, g.accumulate);
+      if ((rc = combine(S.ct + (size_t)z * g.N, (long long)batch * g.N, 1, g.C + z * g.zC, g.ldc,
+                        g.relu_mask ? g.relu_mask + z * g.zmask : nullptr, g.ldmask, g.M, g.N, g.accumulate, st))) return rc;
     }
     if ((rc = check_launch("gemm_tc_f32: combine", batch))) return rc;
   }
