@@ -302,6 +302,10 @@ int plr2_net_pack(int net, const plr2_param_table *params, int num_obj, float *p
 /* Scatter a packed gradient buffer back into per-parameter tensors (overwrites them). */
 int plr2_net_unpack_grads(int net, const float *packed_grad, const plr2_param_table *grads, int num_obj,
                           void *stream);
+/* The same scatter ADDED onto the tensors (autograd's AccumulateGrad for all parameters of a network in one launch
+ * instead of one element-wise add per parameter: tools/train.py:150-155 accumulates 8 frames before a step). */
+int plr2_net_accumulate_grads(int net, const float *packed_grad, const plr2_param_table *grads, int num_obj,
+                              void *stream);
 
 /* Input-range status of the LAST plr2_posenet_forward / plr2_refiner_forward that used `workspace`.  torch.gather
  * (lib/network.py:102) and index_select (lib/network.py:123-126, 202-204) raise on an out-of-range index; a kernel

@@ -76,6 +76,7 @@ SIGNATURES.update({
     "plr2_net_workspace_bytes": (_sz, [_i] * 5),
     "plr2_net_pack": (_i, [_i, _pp, _i, _vp, _i, _vp]),
     "plr2_net_unpack_grads": (_i, [_i, _vp, _pp, _i, _vp]),
+    "plr2_net_accumulate_grads": (_i, [_i, _vp, _pp, _i, _vp]),
     "plr2_posenet_forward": (_i, [_vp] * 5 + [_i] * 4 + [_vp, _sz] + [_vp] * 4 + [_i, _i, _vp]),
     "plr2_posenet_backward": (_i, [_vp] * 4 + [_i] * 4 + [_vp, _sz] + [_vp] * 5 + [_i, _vp]),
     "plr2_refiner_forward": (_i, [_vp] * 4 + [_i] * 3 + [_vp, _sz] + [_vp] * 2 + [_i, _i, _vp]),

@@ -198,17 +198,21 @@ static int combine(const float *ct, long long ldct, int nsum, float *C, long lon
 // sequential FP32 dot product before the ReLU; everywhere else the tensor-core sign is provably the true one.
 constexpr float SIGN_TAU = 6.103515625e-05f;   // 2^-14
 
-// out[z][r] = || src_z[r, 0:cols] ||_2, one warp per row (rows contiguous along k for both operands of a forward)
+// out[z][r] = || src_z[r, 0:cols] ||_2, one warp per row (rows contiguous along k for both operands of a forward).
+// One launch serves both operands: blocks [0, a.blocks) take the activations' rows, the rest the weights' rows.
+struct NormDesc { const float *src; long long s_row, s_col, z_stride; int rows, cols, blocks; float *out; };
 __global__ void __launch_bounds__(256)
-row_norm_kernel(const float *__restrict__ src, long long s_row, long long s_col, long long z_stride, int rows,
-                int cols, float *__restrict__ out) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= rows) return;
-  const float *p = src + blockIdx.y * z_stride + (long long)warp * s_row;
-  float a = 0.f;
-  for (int k = lane; k < cols; k += 32) { const float v = __ldg(p + (long long)k * s_col); a = fmaf(v, v, a); }
-  a = warp_sum(a);
-  if (lane == 0) out[(size_t)blockIdx.y * rows + warp] = sqrtf(a);
+row_norm_kernel(NormDesc a, NormDesc b) {
+  const bool second = (int)blockIdx.x >= a.blocks;
+  const NormDesc &d = second ? b : a;
+  const int bid = second ? blockIdx.x - a.blocks : blockIdx.x;
+  const int warp = (bid * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= d.rows) return;
+  const float *p = d.src + blockIdx.y * d.z_stride + (long long)warp * d.s_row;
+  float acc = 0.f;
+  for (int k = lane; k < d.cols; k += 32) { const float v = __ldg(p + (long long)k * d.s_col); acc = fmaf(v, v, acc); }
+  acc = warp_sum(acc);
+  if (lane == 0) d.out[(size_t)blockIdx.y * d.rows + warp] = sqrtf(acc);
 }
 
 // C (pre-activation, written by the tensor-core launch without ReLU) -> relu(C), with the elements inside the
@@ -414,8 +418,8 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
   if ((rc = gemm_bf16x2(t, st))) return rc;
   if (sign_safe) {
     float *nx = S.ct, *nw = S.ct + (size_t)batch * g.M;
-    row_norm_kernel<<<dim3((g.M + 7) / 8, batch), 256, 0, st>>>(g.A, g.sam, g.sak, g.zA, g.M, g.K, nx);
-    row_norm_kernel<<<dim3((g.N + 7) / 8, batch), 256, 0, st>>>(g.B, g.sbn, g.sbk, g.zB, g.N, g.K, nw);
+    const NormDesc na{g.A, g.sam, g.sak, g.zA, g.M, g.K, (g.M + 7) / 8, nx}, nb{g.B, g.sbn, g.sbk, g.zB, g.N, g.K, (g.N + 7) / 8, nw};
+    row_norm_kernel<<<dim3(na.blocks + nb.blocks, batch), 256, 0, st>>>(na, nb);
     if ((long long)g.M * g.N >= 0x7fffffffLL) { set_error("gemm_tc_f32: sign-safe relu: %d x %d elements", g.M, g.N); return PLR2_E_SHAPE; }
     const bool vec = g.N % 4 == 0 && g.ldc % 4 == 0 && g.zC % 4 == 0 && (reinterpret_cast<uintptr_t>(g.C) & 15) == 0;
     const long long items = (long long)g.M * (vec ? g.N / 4 : g.N);
@@ -424,7 +428,7 @@ int gemm_tc_f32(const GemmArgs &g, const TcScratch &S, cudaStream_t st) {
     gs.batch = batch;
     if (vec) relu_signsafe_kernel<4><<<dim3(blocks, batch), 256, 0, st>>>(gs, nx, nw);
     else relu_signsafe_kernel<1><<<dim3(blocks, batch), 256, 0, st>>>(gs, nx, nw);
-    if ((rc = check_launch("gemm_tc_f32: sign-safe relu", 3))) return rc;
+    if ((rc = check_launch("gemm_tc_f32: sign-safe relu", 2))) return rc;
   }
   if (need_ct) {
     for (int z = 0; z < batch; ++z) {

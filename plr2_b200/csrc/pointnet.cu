@@ -353,6 +353,7 @@ struct CopyTable {
   __nv_bfloat16 *planes;        // split hi/lo planes of the same layout (bf16 or fp16 bits), or nullptr
   long long plane_stride;
   int fp16;
+  int accumulate;               // dst += src (gradient unpack onto existing .grad tensors)
 };
 
 __global__ void __launch_bounds__(256) copy_blocks_kernel(const __grid_constant__ CopyTable T) {
@@ -360,7 +361,8 @@ __global__ void __launch_bounds__(256) copy_blocks_kernel(const __grid_constant_
   const size_t total = (size_t)E.rows * E.cols;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const size_t r = i / E.cols, c = i % E.cols;
-    const float v = E.src[r * E.src_ld + c];
+    float v = E.src[r * E.src_ld + c];
+    if (T.accumulate) v += E.dst[r * E.dst_ld + c];
     E.dst[r * E.dst_ld + c] = v;
     if (E.round && T.planes != nullptr) {     // split-bf16 copy for the tensor-core layers
       const long long off = (E.dst - T.base) + (long long)(r * E.dst_ld + c);
@@ -434,8 +436,9 @@ static int build_table(const NetLayout &L, const plr2_param_table *P, float *pac
 }
 
 int net_copy_params(const NetLayout &L, const plr2_param_table *P, float *packed, bool to_packed, int round,
-                    cudaStream_t st) {
+                    cudaStream_t st, int accumulate) {
   CopyTable T;
+  T.accumulate = accumulate;
   int rc = build_table(L, P, packed, to_packed, round, T);
   if (rc) return rc;
   T.base = packed;

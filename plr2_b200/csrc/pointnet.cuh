@@ -31,6 +31,6 @@ int frame_linear(const float *X, long long ldx, const float *W, long long ldw, c
 int head_out(const float *H, long long ldh, const float *W4, const float *b4, const int64_t *obj, int num_obj,
              int frames, int rows_per_frame, float *pred_r, float *pred_t, float *pred_c, cudaStream_t st);
 int net_copy_params(const NetLayout &L, const plr2_param_table *P, float *packed, bool to_packed, int round,
-                    cudaStream_t st);
+                    cudaStream_t st, int accumulate = 0);
 
 }  // namespace plr2

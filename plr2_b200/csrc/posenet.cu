@@ -324,6 +324,14 @@ extern "C" int plr2_net_unpack_grads(int net, const float *packed_grad, const pl
                          (cudaStream_t)stream);
 }
 
+extern "C" int plr2_net_accumulate_grads(int net, const float *packed_grad, const plr2_param_table *grads, int num_obj,
+                                         void *stream) {
+  if (!grads || !packed_grad) { set_error("plr2_net_accumulate_grads: null pointer"); return PLR2_E_NULLPTR; }
+  if (num_obj <= 0 || (net != PLR2_NET_POSENET && net != PLR2_NET_REFINER)) { set_error("plr2_net_accumulate_grads: bad net/num_obj"); return PLR2_E_SHAPE; }
+  return net_copy_params(make_layout(net, num_obj), grads, const_cast<float *>(packed_grad), false, 0,
+                         (cudaStream_t)stream, 1);
+}
+
 extern "C" int plr2_posenet_forward(const float *packed, const float *out_img, const int64_t *choose,
                                     const float *x, const int64_t *obj, int frames, int n_points, int hw,
                                     int num_obj, void *workspace, size_t workspace_bytes, float *pred_r,

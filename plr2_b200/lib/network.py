@@ -87,6 +87,15 @@ class _HotPathMixin:
     def check_inputs(self, value):
         self._state.check_inputs = bool(value)
 
+    def accumulate_grads_in_place(self, enable=True):
+        """Opt-in for training loops that keep dense `.grad` tensors alive between steps (gradient accumulation as in
+        tools/train.py:150-155, or a flat all-reduce bucket): the backward adds its parameter gradients onto `.grad`
+        with one kernel and returns None to autograd instead of 36 tensors that AccumulateGrad adds one by one.
+        Parameter hooks do not fire on this path and torch.autograd.grad() sees no parameter gradients; parameters
+        without a `.grad` fall back to the ordinary path."""
+        self._state.grads_in_place = bool(enable)
+        return self
+
     def invalidate_packed_weights(self):
         """Call after updating parameters through `.data` (which does not bump the tensors' version counters the
         packed-weight cache is keyed on); in-place ops on the parameters themselves are detected automatically."""

@@ -238,6 +238,23 @@ def _unpack_grads(net, num_obj, gpacked, params, dev):
     return views
 
 
+def _deliver_grads(state, net, gpacked, params, dev):
+    """Parameter gradients of a backward: fresh tensors for autograd to accumulate (default), or - when the module
+    opted in (`accumulate_grads_in_place`) and every parameter already has a dense `.grad` - added onto those tensors by
+    ONE kernel, autograd receiving None (one launch instead of an element-wise add per parameter)."""
+    if getattr(state, "grads_in_place", False):
+        gs = [p.grad for p in params]
+        if all(g is not None and g.dtype == torch.float32 and g.is_contiguous() and g.device == dev and
+               g.shape == p.shape for g, p in zip(gs, params)):
+            pairs = [(gs[2 * i], gs[2 * i + 1]) for i in range(len(gs) // 2)]
+            with torch.cuda.device(dev):
+                rc = _cabi.lib().plr2_net_accumulate_grads(net, _cabi.ptr(gpacked), _param_table(pairs), state.num_obj,
+                                                           _cabi.stream_ptr(dev))
+            _cabi.check(rc, "plr2_net_accumulate_grads")
+            return (None,) * len(params)
+    return tuple(_unpack_grads(net, state.num_obj, gpacked, params, dev))
+
+
 def _check_backward_state(ctx, what):
     """The backward overwrites the activations kept in the workspace in place and reads the weights packed by the
     forward: a second backward through the same graph, or parameters modified in between, cannot be honoured."""
@@ -312,9 +329,9 @@ class PoseNetFn(torch.autograd.Function):
             # gradient all-reduce inside the op: the head weights (most of the bytes) go out on a side stream as soon
             # as they are final, while the trunk backward launched above is still running on this stream
             sync.reduce(gp, *grad_regions(NET_POSENET, state.num_obj))
-        grads = _unpack_grads(NET_POSENET, state.num_obj, gp, ctx.params, dev)
+        grads = _deliver_grads(state, NET_POSENET, gp, ctx.params, dev)
         ctx.saved = None
-        return (None, None, None, g_img, None, None, None) + tuple(grads)
+        return (None, None, None, g_img, None, None, None) + grads
 
 
 _REGIONS = {}
@@ -384,9 +401,9 @@ class RefinerFn(torch.autograd.Function):
                 _cabi.ptr(ws), nbytes, _cabi.ptr(g_r), _cabi.ptr(g_t), _cabi.ptr(gp), ctx.precision,
                 _cabi.stream_ptr(dev))
         _cabi.check(rc, "plr2_refiner_backward")
-        grads = _unpack_grads(NET_REFINER, state.num_obj, gp, ctx.params, dev)
+        grads = _deliver_grads(state, NET_REFINER, gp, ctx.params, dev)
         ctx.saved = None
-        return (None, None, None, None, None, None) + tuple(grads)
+        return (None, None, None, None, None, None) + grads
 
 
 def pose_compose_(pose_acc, pose_delta):

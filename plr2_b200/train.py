@@ -49,6 +49,7 @@ class C5TrainStep:
         self.crit = Loss(shape.num_mesh, list(shape.sym_list), knn_mode)
         self.params = self.net.hot_path_parameters()
         self.bucket = parallel.GradBucket(self.params)
+        self.net.accumulate_grads_in_place(True)      # the bucket's views are the .grad tensors: one kernel adds into them
         self.in_op = parallel.InOpGradSync(average=True).attach(self.net) if (overlap and world > 1) else None
         self.cuda_graph = bool(cuda_graph)
         self.opt = torch.optim.Adam(self.params, lr=lr, fused=True, capturable=self.cuda_graph)

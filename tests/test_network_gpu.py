@@ -426,6 +426,31 @@ def test_packed_weight_cache_and_backward_guards():
         (pr.sum() + pt.sum() + pc.sum()).backward()
 
 
+def test_in_place_gradient_accumulation_equals_autograd_accumulation():
+    """accumulate_grads_in_place: ONE kernel adds the packed gradient onto the existing .grad tensors; same bits as
+    autograd's per-parameter AccumulateGrad, over two backward passes (tools/train.py:150-155 accumulates frames)."""
+    shp = synth.Shape(256, 21, 50, 20, 20, tuple(synth.YCB_SYM))
+    img, pts, ch, ob = _small_posenet_inputs(shp)
+    grads = []
+    for in_place in (False, True):
+        net = build_posenet(shp, 7, ops.PREC_BF16X2)
+        net.accumulate_grads_in_place(in_place)
+        params = net.hot_path_parameters()
+        for p in params:
+            p.grad = torch.full_like(p, 0.125)       # something already accumulated
+        for rep in range(2):
+            pr, pt, pc, _ = net(img, pts, ch, ob)
+            (pr.sum() * (1 + rep) + pt.sum() - pc.sum()).backward()
+        grads.append([p.grad.clone() for p in params])
+    for a, b in zip(*grads):
+        assert torch.equal(a, b)
+    # parameters without a .grad fall back to the ordinary path
+    net = build_posenet(shp, 7, ops.PREC_BF16X2).accumulate_grads_in_place(True)
+    pr, pt, pc, _ = net(img, pts, ch, ob)
+    (pr.sum() + pt.sum() - pc.sum()).backward()
+    assert all(p.grad is not None for p in net.hot_path_parameters())
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
 def test_one_process_two_devices():
     """Function attributes (232 KB of dynamic shared memory for the tcgen05 GEMM, the k-NN tile) and occupancy figures
