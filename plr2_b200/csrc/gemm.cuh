@@ -25,6 +25,10 @@ struct GemmArgs {
   // A hint - honoured only when the scratch record matches pointer, shape and pitch; the caller guarantees that
   // the matrix was not written in between.
   int reuse_a_planes = 0;
+  // Weight gradients on the tensor-core path: column sums of A (= dY: the bias gradient) per 32-row tile, written by
+  // the pass that splits dY - colsum_part [tiles][M * batch] (capacity colsum_cap floats); *colsum_tiles is set to the
+  // number of tiles when the partials were written (left untouched otherwise: the caller then sums dY itself).
+  float *colsum_part = nullptr; long long colsum_cap = 0; int *colsum_tiles = nullptr;
 };
 
 // FP32 SIMT GEMM.  split_k > 1 adds partial sums atomically into C (needs accumulate=1, no relu/mask).

@@ -34,6 +34,7 @@ struct PackDesc {
   __nv_bfloat16 *dst; long long ldd, plane, dst_z;
   int trans, vec;
   int tiles_x, tiles_y, blocks;
+  float *colsum; long long colsum_ld;   // straight packs only: colsum[row tile][column] = sum of the tile's 32 rows
 };
 
 __device__ __forceinline__ void split_store4(__nv_bfloat16 *hi_p, __nv_bfloat16 *lo_p, const float (&v)[4]) {
@@ -77,6 +78,7 @@ __device__ __forceinline__ void pack_tile(const PackDesc &d, int local, float (*
     return;
   }
   const int kk = bx * (4 * PACK_TILE) + 4 * tx;      // cols_z is a multiple of 64: kk < cols_z covers kk..kk+3
+  float cs[4] = {0.f, 0.f, 0.f, 0.f};                // column sums over this thread's rows (fixed order)
 #pragma unroll
   for (int j = 0; j < PACK_TILE / 8; ++j) {
     const int r = r0 + ty + 8 * j;
@@ -92,6 +94,24 @@ __device__ __forceinline__ void pack_tile(const PackDesc &d, int local, float (*
       }
       __nv_bfloat16 *o = dst + (long long)r * d.ldd + kk;
       split_store4(o, o + d.plane, v);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) cs[e] += v[e];
+    }
+  }
+  if (d.colsum != nullptr) {                          // block-uniform; the tile array is free on this path
+    float *part = &tile[0][0];                        // [8 row lanes][128 columns]
+#pragma unroll
+    for (int e = 0; e < 4; ++e) part[ty * (4 * PACK_TILE) + 4 * tx + e] = cs[e];
+    __syncthreads();
+    const int t = ty * PACK_TILE + tx;                // 256 threads, 128 columns: the lower half sums
+    if (t < 4 * PACK_TILE) {
+      const int c = bx * (4 * PACK_TILE) + t;
+      if (c < d.cols) {
+        float a = 0.f;
+#pragma unroll
+        for (int l = 0; l < 8; ++l) a += part[l * (4 * PACK_TILE) + t];
+        d.colsum[(long long)by * d.colsum_ld + c] = a;
+      }
     }
   }
 }
@@ -116,6 +136,7 @@ static PackDesc pack_desc(const float *src, long long s_row, long long s_col, in
   d.tiles_x = d.trans ? (cols_z + PACK_TILE - 1) / PACK_TILE : (cols_z + 4 * PACK_TILE - 1) / (4 * PACK_TILE);
   d.tiles_y = (rows + PACK_TILE - 1) / PACK_TILE;
   d.blocks = d.tiles_x * d.tiles_y * chunks;
+  d.colsum = nullptr; d.colsum_ld = 0;
   return d;
 }
 
@@ -306,8 +327,13 @@ static int wgrad_mn(const GemmArgs &g, int heads, const TcScratch &S, cudaStream
   const bool need_ct = splits > 1 || g.accumulate || g.relu_mask != nullptr;
   if (need_ct && (size_t)Mt * splits * g.N > S.elems) return -1;
   int rc;
-  if ((rc = pack_pair(pack_desc(g.A, g.sak, 1, g.K, Mt, Mp, 1, S.pa, Mp, (long long)S.elems, 0),
-                      pack_desc(g.B, g.sbk, 1, g.K, Nt, Np, 1, S.pb, Np, (long long)S.elems, 0), st))) return rc;
+  PackDesc da = pack_desc(g.A, g.sak, 1, g.K, Mt, Mp, 1, S.pa, Mp, (long long)S.elems, 0);
+  if (g.colsum_part != nullptr && (long long)da.tiles_y * Mt <= g.colsum_cap) {
+    // the bias gradient's first stage rides on the split of dY: per 32-row tile column sums, summed by the caller
+    da.colsum = g.colsum_part; da.colsum_ld = Mt;
+    if (g.colsum_tiles) *g.colsum_tiles = da.tiles_y;
+  }
+  if ((rc = pack_pair(da, pack_desc(g.B, g.sbk, 1, g.K, Nt, Np, 1, S.pb, Np, (long long)S.elems, 0), st))) return rc;
   // dY as [rows][Mp] planes is also the K-major A operand of the input gradient that follows
   g_a_planes.src = g.A; g_a_planes.s_row = g.sak; g_a_planes.rows = g.K; g_a_planes.cols = Mt;
   g_a_planes.pitch = Mp; g_a_planes.dst = S.pa; g_a_planes.st = st;

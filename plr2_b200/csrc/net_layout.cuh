@@ -59,6 +59,7 @@ inline NetLayout make_layout(int net, int O) {
 struct NetWorkspace {
   unsigned int *status;    // first 128 bytes of every network workspace: input-range flags of the last forward (PLR2_STATUS_*)
   float *pf, *x5, *x6, *ap, *hb, *h1, *h2, *h3, *out, *embT, *dpf, *dap, *dhb;
+  size_t red_cap = 0;      // floats in `red`
   float *red;              // training: [BGRAD_SLICES][BGRAD_MAX_COLS] partial column sums of the bias gradients
   // training: scratch of the tensor-core contractions (gemm_tc_f32.cu): split-bf16 planes of the two operands
   // (tc_pa, tc_pb: 2 planes x tc_elems bf16 each) and an FP32 output staging area (tc_ct: tc_elems floats)
@@ -90,7 +91,9 @@ inline NetWorkspace carve_workspace(const NetLayout &L, void *base, int frames, 
   W.embT = take(R * 32);
   if (training) {
     W.dpf = take(R * 384); W.dap = take(F * 1024); W.dhb = take(pn ? F * h1all : 0);
-    W.red = take((size_t)BGRAD_SLICES * BGRAD_MAX_COLS);
+    // (or one partial per 32-row tile when the tensor-core split of dY produces them: gemm.cuh colsum_part)
+    W.red_cap = (size_t)(BGRAD_SLICES > (R + 31) / 32 ? BGRAD_SLICES : (R + 31) / 32) * BGRAD_MAX_COLS;
+    W.red = take(W.red_cap);
     // largest operand / output of any contraction: 1920 columns (conv1_{r,t,c}) x rows padded to the K tile,
     // or the 1920 x 1024 per-frame weight block
     const size_t rp = (R + 63) / 64 * 64;

@@ -226,6 +226,18 @@ static int bgrad(const float *dY, long long ld, int rows, int ncols, float *db, 
   return segment_colsum(red, ncols, 1, slices, ncols, 1.0f, db, ncols, st);
 }
 
+// Weight and bias gradient of one layer (or of the stacked r|t|c heads): dW += dY^T X, db = column sums of dY.
+// On the tensor-core path the pass that splits dY leaves per-tile column sums in W.red, so only their sum is left
+// to do; otherwise dY is summed in two stages as before.
+static int wbgrad(GemmArgs g, const float *dY, long long ld, int rows, int ncols, float *db, const NetWorkspace &W,
+                  const GemmCtx &cx, cudaStream_t st) {
+  int tiles = 0;
+  g.colsum_part = W.red; g.colsum_cap = (long long)W.red_cap; g.colsum_tiles = &tiles;
+  RC(wgrad(g, cx, st));
+  if (tiles > 0) return segment_colsum(W.red, ncols, 1, tiles, ncols, 1.0f, db, ncols, st);
+  return bgrad(dY, ld, rows, ncols, db, W.red, st);
+}
+
 // From W.dap (d loss / d pooled feature) and W.dpf (head contributions to d pf, or undefined when
 // !dpf_has_heads) down to the first layer.  Leaves d e1 in W.dpf[:,64:128] and d emb in W.embT.
 static int feat_backward(const float *pk, float *gp, const NetLayout &L, const NetWorkspace &W, const float *x,
@@ -233,14 +245,12 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
   const int R = F * N;
   // AvgPool1d backward through conv6's ReLU: dx6 = (x6 > 0) * dap[frame] / N     (in place)
   RC(segment_bcast_mask(W.dap, W.x6, (size_t)R, N, 1024, 1.0f / (float)N, W.x6, st));
-  RC(wgrad(gemm_tn(W.x6, 1024, W.x5, 512, gp + L.c6w, 512, 1024, 512, R), cx, st));
-  RC(bgrad(W.x6, 1024, R, 1024, gp + L.c6b, W.red, st));
+  RC(wbgrad(gemm_tn(W.x6, 1024, W.x5, 512, gp + L.c6w, 512, 1024, 512, R), W.x6, 1024, R, 1024, gp + L.c6b, W, cx, st));
   GemmArgs g = gemm_nn(W.x6, 1024, pk + L.c6w, 512, W.x5, 512, R, 512, 1024);     // dx5 (in place)
   g.relu_mask = W.x5; g.ldmask = 512; g.reuse_a_planes = 1;
   RC(gemm_run(g, 1, cx, st));
   const float *a5 = L.c5k == 256 ? W.pf + 128 : W.pf;
-  RC(wgrad(gemm_tn(W.x5, 512, a5, 384, gp + L.c5w, L.c5k, 512, L.c5k, R), cx, st));
-  RC(bgrad(W.x5, 512, R, 512, gp + L.c5b, W.red, st));
+  RC(wbgrad(gemm_tn(W.x5, 512, a5, 384, gp + L.c5w, L.c5k, 512, L.c5k, R), W.x5, 512, R, 512, gp + L.c5b, W, cx, st));
   const int off2 = L.c5k == 256 ? 0 : 128;    // column of pointfeat_2 inside conv5's input
   if (L.c5k == 384) {                         // refiner: conv5 also reads pointfeat_1
     g = gemm_nn(W.x5, 512, pk + L.c5w, 384, W.dpf, 384, R, 128, 512);
@@ -255,8 +265,7 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
   for (int e = 0; e < 2; ++e) {
     const int cin = e * 64, cout = 128 + e * 128;
     const size_t wo = e ? L.e2w : L.c2w, bo = e ? L.e2b : L.c2b;
-    RC(wgrad(gemm_tn(W.dpf + cout, 384, W.pf + cin, 384, gp + wo, 64, 128, 64, R), cx, st));
-    RC(bgrad(W.dpf + cout, 384, R, 128, gp + bo, W.red, st));
+    RC(wbgrad(gemm_tn(W.dpf + cout, 384, W.pf + cin, 384, gp + wo, 64, 128, 64, R), W.dpf + cout, 384, R, 128, gp + bo, W, cx, st));
     g = gemm_nn(W.dpf + cout, 384, pk + wo, 64, W.dpf + cin, 384, R, 64, 128);
     g.accumulate = 1; g.relu_mask = W.pf + cin; g.ldmask = 384; g.reuse_a_planes = 1;
     RC(gemm_run(g, 1, cx, st));
@@ -264,8 +273,7 @@ static int feat_backward(const float *pk, float *gp, const NetLayout &L, const N
   // conv1 (3 -> 64) and e_conv1 (32 -> 64)
   RC(wgrad(gemm_tn(W.dpf, 384, x, 3, gp + L.c1w, 4, 64, 3, R), cx, st));
   RC(bgrad(W.dpf, 384, R, 64, gp + L.c1b, W.red, st));
-  RC(wgrad(gemm_tn(W.dpf + 64, 384, W.embT, 32, gp + L.e1w, 32, 64, 32, R), cx, st));
-  RC(bgrad(W.dpf + 64, 384, R, 64, gp + L.e1b, W.red, st));
+  RC(wbgrad(gemm_tn(W.dpf + 64, 384, W.embT, 32, gp + L.e1w, 32, 64, 32, R), W.dpf + 64, 384, R, 64, gp + L.e1b, W, cx, st));
   return 0;
 }
 
@@ -445,8 +453,8 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   RC(select_outputs_bwd(W.out, L, obj, N, (size_t)R, g_pred_r, g_pred_t, g_pred_c, st));
   size_t row = 0;
   for (int h = 0; h < 3; ++h) {               // conv4_*
-    RC(wgrad(gemm_tn(W.out + L.oc[h], L.ldo, W.h3 + h * 128, 384, gp + L.h4w + row * 128, 128, L.on[h], 128, R), cx, st));
-    RC(bgrad(W.out + L.oc[h], L.ldo, R, L.on[h], gp + L.h4b + row, W.red, st));
+    RC(wbgrad(gemm_tn(W.out + L.oc[h], L.ldo, W.h3 + h * 128, 384, gp + L.h4w + row * 128, 128, L.on[h], 128, R),
+              W.out + L.oc[h], L.ldo, R, L.on[h], gp + L.h4b + row, W, cx, st));
     GemmArgs g = gemm_nn(W.out + L.oc[h], L.ldo, pk + L.h4w + row * 128, 128, W.h3 + h * 128, 384, R, 128, L.on[h]);
     g.relu_mask = W.h3 + h * 128; g.ldmask = 384; g.reuse_a_planes = 1;
     RC(gemm_run(g, 1, cx, st));
@@ -455,8 +463,7 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   // conv3_*
   GemmArgs g = gemm_tn(W.h3, 384, W.h2, 768, gp + L.h3w, 256, 128, 256, R);
   g.batch = 3; g.zA = 128; g.zB = 256; g.zC = 128 * 256;
-  RC(wgrad(g, cx, st));
-  RC(bgrad(W.h3, 384, R, 384, gp + L.h3b, W.red, st));
+  RC(wbgrad(g, W.h3, 384, R, 384, gp + L.h3b, W, cx, st));
   g = gemm_nn(W.h3, 384, pk + L.h3w, 256, W.h2, 768, R, 256, 128);
   g.batch = 3; g.zA = 128; g.zB = 128 * 256; g.zC = 256; g.relu_mask = W.h2; g.ldmask = 768; g.zmask = 256;
   g.reuse_a_planes = 1;
@@ -464,8 +471,7 @@ extern "C" int plr2_posenet_backward(const float *packed, const int64_t *choose,
   // conv2_*
   g = gemm_tn(W.h2, 768, W.h1, 1920, gp + L.h2w, 640, 256, 640, R);
   g.batch = 3; g.zA = 256; g.zB = 640; g.zC = 256 * 640;
-  RC(wgrad(g, cx, st));
-  RC(bgrad(W.h2, 768, R, 768, gp + L.h2b, W.red, st));
+  RC(wbgrad(g, W.h2, 768, R, 768, gp + L.h2b, W, cx, st));
   g = gemm_nn(W.h2, 768, pk + L.h2w, 640, W.h1, 1920, R, 640, 256);
   g.batch = 3; g.zA = 256; g.zB = 256 * 640; g.zC = 640; g.relu_mask = W.h1; g.ldmask = 1920; g.zmask = 640;
   g.reuse_a_planes = 1;
