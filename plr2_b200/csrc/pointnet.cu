@@ -240,9 +240,39 @@ segment_colsum_kernel(const float *__restrict__ X, long long ld, int rows_per_se
   }
 }
 
+// One segment of a few hundred rows (the per-tile partials of a bias gradient): 32 row lanes per block instead
+// of 8, so that a thread's chain is rows/32 loads long.  Fixed summation order.
+__global__ void __launch_bounds__(1024)
+colsum_tall_kernel(const float *__restrict__ X, long long ld, int rows, int ncols, float scale, float *__restrict__ out) {
+  __shared__ float red[32][33];
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int rl = threadIdx.x >> 5;
+  float s0 = 0.f, s1 = 0.f;
+  if (c < ncols) {
+    int r = rl;
+    for (; r + 32 < rows; r += 64) { s0 += X[(size_t)r * ld + c]; s1 += X[(size_t)(r + 32) * ld + c]; }
+    if (r < rows) s0 += X[(size_t)r * ld + c];
+  }
+  red[rl][threadIdx.x & 31] = s0 + s1;
+  __syncthreads();
+  if (rl == 0 && c < ncols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) t += red[i][threadIdx.x];
+    out[c] = t * scale;
+  }
+}
+
+int colsum_tall(const float *X, long long ld, int rows, int ncols, float *out, cudaStream_t st) {
+  if (rows <= 0 || ncols <= 0) return 0;
+  colsum_tall_kernel<<<(ncols + 31) / 32, 1024, 0, st>>>(X, ld, rows, ncols, 1.0f, out);
+  return check_launch("colsum_tall");
+}
+
 int segment_colsum(const float *X, long long ld, int nseg, int rows_per_seg, int ncols, float scale, float *out,
                    long long ldo, cudaStream_t st) {
   if (nseg <= 0 || ncols <= 0) return 0;
+
   dim3 grid((ncols + 31) / 32, nseg);
   segment_colsum_kernel<<<grid, 256, 0, st>>>(X, ld, rows_per_seg, (size_t)nseg * rows_per_seg, ncols, scale, out, ldo);
   return check_launch("segment_colsum");

@@ -16,6 +16,8 @@ int scatter_emb_grad(const float *demb, const int64_t *choose, int frames, int N
                      cudaStream_t st);
 int segment_colsum(const float *X, long long ld, int nseg, int rows_per_seg, int ncols, float scale, float *out,
                    long long ldo, cudaStream_t st);
+// out[c] = sum over `rows` rows of X[r][c], one segment, 32 row lanes per block (partials of a bias gradient)
+int colsum_tall(const float *X, long long ld, int rows, int ncols, float *out, cudaStream_t st);
 int segment_colsum_ragged(const float *X, long long ld, int nseg, int rows_per_seg, size_t total_rows, int ncols, float *out,
                           long long ldo, cudaStream_t st);
 int segment_bcast_mask(const float *dseg, const float *X, size_t rows, int rows_per_seg, int ncols, float scale,

@@ -234,7 +234,7 @@ static int wbgrad(GemmArgs g, const float *dY, long long ld, int rows, int ncols
   int tiles = 0;
   g.colsum_part = W.red; g.colsum_cap = (long long)W.red_cap; g.colsum_tiles = &tiles;
   RC(wgrad(g, cx, st));
-  if (tiles > 0) return segment_colsum(W.red, ncols, 1, tiles, ncols, 1.0f, db, ncols, st);
+  if (tiles > 0) return colsum_tall(W.red, ncols, tiles, ncols, db, st);
   return bgrad(dY, ld, rows, ncols, db, W.red, st);
 }
 
