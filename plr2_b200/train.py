@@ -169,6 +169,7 @@ class C5TrainStep:
             "cuda_graph": graphed, "cuda_graph_error": self.graph_error,
             "allreduce_ms_per_step": (ar_ms / steps) if ar_ms is not None else None,
             "grad_bucket_mb": self.bucket.numel * 4 / 1e6,
+            "grad_delivery": "one accumulating scatter onto the bucket's .grad views (accumulate_grads_in_place)",
             "allreduce": ("inside the backward op, head weights overlapped with the trunk backward" if self.in_op
                           else "one flat bucket after the backward") if world > 1 else "none (1 GPU)",
             "sharding": "cost-aware deal of the global batch (symmetric frames round-robin)",
