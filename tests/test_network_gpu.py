@@ -180,14 +180,17 @@ def test_batched_frames_equal_single_frame_calls():
                 assert torch.equal(x[0], y[i])
 
 
-def test_batched_training_tensor_core_equals_fp32_path():
-    """Six frames of 200 points (1200 rows: K tail of the weight gradients, split-K, r/t/c head batches) through
-    forward + Loss + backward: gradients of the tensor-core training path against the FP32 SIMT path."""
+@pytest.mark.parametrize("frames,tc_prec", [(6, ops.PREC_BF16X2), (9, ops.PREC_BF16X2), (9, ops.PREC_BF16X2_ALL)])
+def test_batched_training_tensor_core_equals_fp32_path(frames, tc_prec):
+    """Six / nine frames of 200 points (1200 / 1800 rows: K tail of the weight gradients read MN-major, split-K,
+    r/t/c head batches split once, dY planes shared by dW and dX; nine frames put the K = frames contractions on the
+    tensor cores too) through forward + Loss + backward: gradients of the tensor-core training paths against the
+    FP32 SIMT path."""
     shp = synth.Shape(200, 21, 100, 24, 24, tuple(synth.YCB_SYM))
-    frs = [synth.make_frame(shp, 90 + i, obj=o) for i, o in enumerate([3, 12, 0, 20, 7, 15])]
+    frs = [synth.make_frame(shp, 90 + i, obj=o) for i, o in enumerate([3, 12, 0, 20, 7, 15, 1, 19, 5][:frames])]
     st = lambda key: tt(np.stack([f[key] for f in frs]), "cuda")
     grads = {}
-    for prec in (ops.PREC_FP32, ops.PREC_BF16X2):
+    for prec in (ops.PREC_FP32, tc_prec):
         net = build_posenet(shp, 9, prec)
         img = st("out_img").requires_grad_(True)
         pr, pt, pc, _ = net(img, st("points"), st("choose")[:, None], st("idx")[:, None])
@@ -196,12 +199,20 @@ def test_batched_training_tensor_core_equals_fp32_path():
         loss.mean().backward()
         grads[prec] = ({k: v.grad.detach().cpu().numpy() for k, v in net.named_parameters() if v.grad is not None},
                        img.grad.detach().cpu().numpy(), pr.detach().cpu().numpy())
-    ga, gb = grads[ops.PREC_FP32], grads[ops.PREC_BF16X2]
+    ga, gb = grads[ops.PREC_FP32], grads[tc_prec]
     assert_close(gb[2], ga[2], "pred_r")
     assert_close(gb[1], ga[1], "g_out_img", frac=0.99)
     assert set(ga[0]) == set(gb[0]) and len(ga[0]) >= 30
+    # Tensor-core FORWARD (PLR2_PREC_BF16X2_ALL): activations differ from the FP32 forward by ~1e-6 relative, so a
+    # handful of ReLUs whose pre-activation lies within that distance of zero take the other branch (the sign-safe
+    # pass guarantees the sign for the inputs it was given, not for the FP32 path's inputs).  ONE such unit moves the
+    # affected weight-gradient entries by ~1/rows (5.6e-4 at 1800 rows): measured 0.87-1.00 of the elements within
+    # rtol 1e-3 and at most 1.4e-3 of the tensor's largest entry; the FP32-forward mode is at 1.0000 / 1e-5.
+    frac, worst = (0.8, 4e-3) if tc_prec == ops.PREC_BF16X2_ALL else (0.999, 5e-5)
     for k in ga[0]:
-        assert_close(gb[0][k], ga[0][k], "grad " + k)
+        assert_close(gb[0][k], ga[0][k], "grad " + k, frac=frac)
+        dev = float(np.abs(gb[0][k] - ga[0][k]).max() / np.abs(ga[0][k]).max())
+        assert dev <= worst, (k, dev)
 
 
 def test_weight_update_is_picked_up():
